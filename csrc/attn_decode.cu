@@ -1,0 +1,296 @@
+// K9 attn_decode_paged: single-query attention against the paged KV cache, split-KV.
+//
+// Replaces the reference's decode-step attention (fp32 upcast, cuBLAS
+// batched QK^T, where-mask, softmax, cuBLAS PV on a [B,h,1,T] score tensor, plus the
+// G17 mask buffers and the H2D mask copy of quirk Q18).  Decode attention is pure
+// KV-bandwidth: every cached byte is read once per step, so the kernel is organised
+// around 16-byte streaming loads (ld.global.nc, no L1 allocation) with 2*U loads in
+// flight per lane, fp32 online softmax, and a split-KV grid so that small batches still
+// fill 148 SMs.  One CTA = (split, kv head x q-head tile, sequence); GQA/MQA heads that
+// share a KV head are processed from a single KV read (GT q heads per CTA).
+//
+// Layouts: q/out rows are strided views into the packed activation (ldq/ldo elements);
+// caches are [num_blocks, hkv, block_size, D]; partials live in caller-provided scratch.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kWarps = 4;
+constexpr int kThreads = kWarps * 32;
+
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+template <typename T, int D, int GT, int U>
+__global__ void __launch_bounds__(kThreads) attn_decode_kernel(
+    const T* __restrict__ q, int64_t ldq, const T* __restrict__ k_cache, const T* __restrict__ v_cache,
+    const int* __restrict__ block_tables, int max_blocks, const int* __restrict__ seq_lens, T* __restrict__ out,
+    int64_t ldo, float* __restrict__ part_o, float* __restrict__ part_ml, int hq, int hkv, int block_size,
+    float scale_log2, int num_splits) {
+  constexpr int LPT = D / 8;     // lanes per token row
+  constexpr int TPW = 32 / LPT;  // tokens per warp-wide load
+  static_assert(LPT >= 1 && LPT <= 32 && (32 % LPT) == 0, "head_dim must be 8..256, power of two");
+
+  __shared__ float sm_acc[kWarps][GT][D];
+  __shared__ float sm_ml[kWarps][GT][2];
+
+  const int split = blockIdx.x, b = blockIdx.z;
+  const int G = hq / hkv;
+  const int g_tiles = (G + GT - 1) / GT;
+  const int hk = blockIdx.y / g_tiles, g0 = (blockIdx.y % g_tiles) * GT;
+  const int gn = min(GT, G - g0);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int grp = lane / LPT, lig = lane % LPT;  // token group within the warp / lane in group
+
+  const int L = seq_lens[b];
+  const int chunk = (L + num_splits - 1) / num_splits;
+  const int t_begin = split * chunk;
+  const int t_end = min(L, t_begin + chunk);
+
+  // q fragment (pre-scaled into the log2 domain)
+  float qf[GT][8];
+#pragma unroll
+  for (int g = 0; g < GT; ++g) {
+    if (g < gn) {
+      unpack8<T>(*reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(hk * G + g0 + g) * D + lig * 8), qf[g]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) qf[g][i] *= scale_log2;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) qf[g][i] = 0.f;
+    }
+  }
+
+  float m[GT], l[GT], acc[GT][8];
+#pragma unroll
+  for (int g = 0; g < GT; ++g) {
+    m[g] = -INFINITY;
+    l[g] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[g][i] = 0.f;
+  }
+
+  const int* bt = block_tables + (int64_t)b * max_blocks;
+  const int64_t head_stride = (int64_t)block_size * D;
+  constexpr int TOK_PER_ITER = TPW * U;
+
+  for (int t0 = t_begin + warp * TOK_PER_ITER; t0 < t_end; t0 += kWarps * TOK_PER_ITER) {
+    uint4 kraw[U], vraw[U];
+    bool valid[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int t = t0 + u * TPW + grp;
+      valid[u] = t < t_end;
+      kraw[u] = make_uint4(0, 0, 0, 0);
+      vraw[u] = make_uint4(0, 0, 0, 0);
+      if (valid[u]) {
+        const int blk = __ldg(bt + t / block_size);
+        const int64_t off = ((int64_t)blk * hkv + hk) * head_stride + (int64_t)(t % block_size) * D + lig * 8;
+        kraw[u] = ldg_stream(k_cache + off);
+        vraw[u] = ldg_stream(v_cache + off);
+      }
+    }
+    float s[U][GT];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float kf[8];
+      unpack8<T>(kraw[u], kf);
+#pragma unroll
+      for (int g = 0; g < GT; ++g) {
+        float p = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p = fmaf(qf[g][i], kf[i], p);
+        s[u][g] = p;
+      }
+    }
+    // reduce partial dot products across the LPT lanes of each token group
+#pragma unroll
+    for (int o = LPT / 2; o > 0; o >>= 1) {
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int g = 0; g < GT; ++g) s[u][g] += __shfl_xor_sync(0xffffffffu, s[u][g], o);
+    }
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+      float mx = m[g];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!valid[u]) s[u][g] = -INFINITY;
+        mx = fmaxf(mx, s[u][g]);
+      }
+      const float corr = (mx == -INFINITY) ? 1.f : exp2f(m[g] - mx);
+      m[g] = mx;
+      l[g] *= corr;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[g][i] *= corr;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float p = valid[u] ? exp2f(s[u][g] - mx) : 0.f;
+        s[u][g] = p;
+        l[g] += p;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float vf[8];
+      unpack8<T>(vraw[u], vf);
+#pragma unroll
+      for (int g = 0; g < GT; ++g)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(s[u][g], vf[i], acc[g][i]);
+    }
+  }
+
+  // merge the TPW token groups of the warp
+#pragma unroll
+  for (int o = LPT; o < 32; o <<= 1) {
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+      const float mo = __shfl_xor_sync(0xffffffffu, m[g], o);
+      const float lo = __shfl_xor_sync(0xffffffffu, l[g], o);
+      const float mn = fmaxf(m[g], mo);
+      const float a = (m[g] == -INFINITY) ? 0.f : exp2f(m[g] - mn);
+      const float c = (mo == -INFINITY) ? 0.f : exp2f(mo - mn);
+      l[g] = l[g] * a + lo * c;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float ao = __shfl_xor_sync(0xffffffffu, acc[g][i], o);
+        acc[g][i] = acc[g][i] * a + ao * c;
+      }
+      m[g] = mn;
+    }
+  }
+  if (grp == 0) {
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sm_acc[warp][g][lig * 8 + i] = acc[g][i];
+      if (lig == 0) {
+        sm_ml[warp][g][0] = m[g];
+        sm_ml[warp][g][1] = l[g];
+      }
+    }
+  }
+  __syncthreads();
+
+  for (int it = threadIdx.x; it < gn * D; it += kThreads) {
+    const int g = it / D, c = it % D;
+    float mn = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) mn = fmaxf(mn, sm_ml[w][g][0]);
+    float lt = 0.f, at = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const float mw = sm_ml[w][g][0];
+      const float sc = (mw == -INFINITY) ? 0.f : exp2f(mw - mn);
+      lt += sm_ml[w][g][1] * sc;
+      at += sm_acc[w][g][c] * sc;
+    }
+    const int head = hk * G + g0 + g;
+    if (num_splits == 1) {
+      out[(int64_t)b * ldo + (int64_t)head * D + c] = from_f32<T>(lt > 0.f ? at / lt : 0.f);
+    } else {
+      const int64_t pidx = ((int64_t)b * hq + head) * num_splits + split;
+      part_o[pidx * D + c] = at;
+      if (c == 0) {
+        part_ml[pidx * 2] = mn;
+        part_ml[pidx * 2 + 1] = lt;
+      }
+    }
+  }
+}
+
+template <typename T, int D>
+__global__ void attn_decode_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
+                                           T* __restrict__ out, int64_t ldo, int hq, int num_splits) {
+  const int head = blockIdx.x, b = blockIdx.y;
+  const int64_t base = ((int64_t)b * hq + head) * num_splits;
+  float mn = -INFINITY;
+  for (int s = 0; s < num_splits; ++s) mn = fmaxf(mn, part_ml[(base + s) * 2]);
+  for (int c = threadIdx.x; c < D; c += blockDim.x) {
+    float lt = 0.f, at = 0.f;
+    for (int s = 0; s < num_splits; ++s) {
+      const float ms = part_ml[(base + s) * 2];
+      const float sc = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
+      lt += part_ml[(base + s) * 2 + 1] * sc;
+      at += part_o[(base + s) * D + c] * sc;
+    }
+    out[(int64_t)b * ldo + (int64_t)head * D + c] = from_f32<T>(lt > 0.f ? at / lt : 0.f);
+  }
+}
+
+template <typename T, int D, int GT>
+int launch_decode(const void* q, int64_t ldq, const void* kc, const void* vc, const int* bt, int max_blocks,
+                  const int* seq_lens, void* out, int64_t ldo, float* part_o, float* part_ml, int B, int hq, int hkv,
+                  int block_size, float scale, int num_splits, cudaStream_t stream) {
+  constexpr int U = (D >= 256) ? 4 : 4;
+  const int G = hq / hkv;
+  const int g_tiles = (G + GT - 1) / GT;
+  dim3 grid(num_splits, hkv * g_tiles, B);
+  const float scale_log2 = scale * 1.4426950408889634f;
+  attn_decode_kernel<T, D, GT, U><<<grid, kThreads, 0, stream>>>(
+      (const T*)q, ldq, (const T*)kc, (const T*)vc, bt, max_blocks, seq_lens, (T*)out, ldo, part_o, part_ml, hq, hkv,
+      block_size, scale_log2, num_splits);
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  if (num_splits > 1) {
+    attn_decode_combine_kernel<T, D><<<dim3(hq, B), (D < 128 ? D : 128), 0, stream>>>(part_o, part_ml, (T*)out, ldo, hq,
+                                                                                    num_splits);
+    LLMSS_CHECK_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+template <typename T, int D>
+int dispatch_gt(int G, const void* q, int64_t ldq, const void* kc, const void* vc, const int* bt, int max_blocks,
+                const int* seq_lens, void* out, int64_t ldo, float* part_o, float* part_ml, int B, int hq, int hkv,
+                int block_size, float scale, int num_splits, cudaStream_t stream) {
+#define LLMSS_GT(GT_)                                                                                              \
+  return launch_decode<T, D, GT_>(q, ldq, kc, vc, bt, max_blocks, seq_lens, out, ldo, part_o, part_ml, B, hq, hkv, \
+                                  block_size, scale, num_splits, stream)
+  if (G == 1) LLMSS_GT(1);
+  if (G == 2) LLMSS_GT(2);
+  if (D <= 128) LLMSS_GT(4);
+  LLMSS_GT(2);
+#undef LLMSS_GT
+}
+
+}  // namespace
+
+// Scratch (floats) needed when num_splits > 1.
+LLMSS_API int64_t llmss_attn_decode_scratch_floats(int B, int hq, int d, int num_splits) {
+  return num_splits > 1 ? (int64_t)B * hq * num_splits * (d + 2) : 0;
+}
+
+LLMSS_API int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                                const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
+                                float* scratch, int B, int hq, int hkv, int d, int block_size, float scale,
+                                int num_splits, int dtype, cudaStream_t stream) {
+  LLMSS_REQUIRE(hq % hkv == 0, "attn_decode: hq=%d not a multiple of hkv=%d", hq, hkv);
+  LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_decode: head_dim=%d unsupported (64/128/256)", d);
+  LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "attn_decode: dtype must be f16/bf16");
+  LLMSS_REQUIRE(num_splits >= 1 && (num_splits == 1 || scratch != nullptr), "attn_decode: scratch required for splits");
+  LLMSS_REQUIRE(ldq % 8 == 0 && ldo % 8 == 0, "attn_decode: row strides must be multiples of 8");
+  if (B == 0) return 0;
+  float* part_o = scratch;
+  float* part_ml = scratch ? scratch + (int64_t)B * hq * num_splits * d : nullptr;
+  const int G = hq / hkv;
+#define LLMSS_D(T_, D_)                                                                                           \
+  return dispatch_gt<T_, D_>(G, q, ldq, k_cache, v_cache, block_tables, max_blocks, seq_lens, out, ldo, part_o, \
+                             part_ml, B, hq, hkv, block_size, scale, num_splits, stream)
+  if (dtype == LLMSS_F16) {
+    if (d == 64) LLMSS_D(__half, 64);
+    if (d == 128) LLMSS_D(__half, 128);
+    LLMSS_D(__half, 256);
+  } else {
+    if (d == 64) LLMSS_D(__nv_bfloat16, 64);
+    if (d == 128) LLMSS_D(__nv_bfloat16, 128);
+    LLMSS_D(__nv_bfloat16, 256);
+  }
+#undef LLMSS_D
+}

@@ -1,0 +1,329 @@
+// comm runtime + K4 collectives over NVLink 5 / NVSwitch peer memory.
+//
+// The reference issues every collective as a separate blocking NCCL launch through c10d
+// (SURVEY.md sections 2.4/2.5; layers.py:125,133,178,213).  Here each rank owns one
+// symmetric region (cudaMalloc + CUDA IPC, mapped into every peer once at start-up) and
+// the collectives are plain kernels that store straight into peer memory and synchronise
+// with system-scope release/acquire flags.  No host involvement, fixed addresses ->
+// CUDA-graph capturable.  The same region/protocol is used from the epilogue of the fused
+// GEMM -> all-reduce kernel (gemm_tcgen05.cu).
+//
+// Protocol (shared by all kernels on a workspace):
+//   * epoch: device-local counter; a call uses e = *epoch + 1, the last CTA to finish
+//     (ticket counter) publishes *epoch = e, so the next kernel in stream order sees it.
+//   * data buffers are double-buffered by epoch parity.  A peer can only run one call
+//     ahead (it cannot finish call n+1 without this rank's call-n+1 pushes), so the buffer
+//     of call n is never overwritten before call n has been fully consumed.
+//   * flag[slot][src_rank] on the destination holds the epoch of the latest push for that
+//     CTA slot; consumers wait for (flag - e) >= 0.  Every CTA pushes before it waits and
+//     grids never exceed one resident wave, so there is no cross-GPU deadlock.
+//   * bounded spins (common.cuh) trap instead of hanging if a peer dies.
+#include "common.cuh"
+#include "symm.cuh"
+
+#include <stdarg.h>
+#include <string.h>
+
+// ---------------------------------------------------------------- error string
+static thread_local char g_err[1024] = "";
+void llmss_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+LLMSS_API const char* llmss_last_error() { return g_err; }
+LLMSS_API int llmss_version() { return 100; }
+
+// ---------------------------------------------------------------- symmetric memory plumbing
+LLMSS_API int llmss_symm_alloc(size_t bytes, void** ptr) {
+  LLMSS_CHECK_CUDA(cudaMalloc(ptr, bytes));
+  LLMSS_CHECK_CUDA(cudaMemset(*ptr, 0, bytes));
+  LLMSS_CHECK_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+LLMSS_API int llmss_symm_free(void* ptr) {
+  LLMSS_CHECK_CUDA(cudaFree(ptr));
+  return 0;
+}
+LLMSS_API int llmss_ipc_get_handle(void* ptr, unsigned char* out64) {
+  cudaIpcMemHandle_t h;
+  LLMSS_CHECK_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(out64, &h, 64);
+  return 0;
+}
+LLMSS_API int llmss_ipc_open_handle(const unsigned char* in64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, in64, 64);
+  LLMSS_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+LLMSS_API int llmss_ipc_close(void* ptr) {
+  LLMSS_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+LLMSS_API size_t llmss_symm_region_bytes(size_t buf_bytes) { return kSymmDataOffset + 2 * buf_bytes; }
+
+// Build the by-value descriptor the kernels take.  `peer_bases[r]` is the mapping of rank
+// r's region in this process (peer_bases[rank] = the local allocation).
+LLMSS_API int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, SymmWs** out) {
+  LLMSS_REQUIRE(nranks >= 1 && nranks <= kSymmMaxRanks, "symm_create: nranks=%d unsupported (max %d)", nranks,
+                kSymmMaxRanks);
+  SymmWs* ws = new SymmWs();
+  memset(ws, 0, sizeof(*ws));
+  for (int r = 0; r < nranks; ++r) ws->peer_base[r] = (char*)peer_bases[r];
+  ws->rank = rank;
+  ws->nranks = nranks;
+  ws->buf_bytes = buf_bytes;
+  uint32_t* ctl = nullptr;
+  LLMSS_CHECK_CUDA(cudaMalloc(&ctl, 256));
+  LLMSS_CHECK_CUDA(cudaMemset(ctl, 0, 256));
+  ws->epoch = ctl;
+  ws->ticket = ctl + 32;
+  LLMSS_CHECK_CUDA(cudaDeviceSynchronize());
+  *out = ws;
+  return 0;
+}
+LLMSS_API int llmss_symm_destroy(SymmWs* ws) {
+  if (ws) {
+    cudaFree(ws->epoch);
+    delete ws;
+  }
+  return 0;
+}
+LLMSS_API int llmss_symm_epoch(SymmWs* ws, uint32_t* out) {
+  LLMSS_CHECK_CUDA(cudaMemcpy(out, ws->epoch, 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ uint4 ld_cg_v4(const void* p) {  // L2-only load: peers write these lines
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+template <typename T>
+__device__ __forceinline__ void accum8(float (&acc)[8], const uint4& raw) {
+  float f[8];
+  unpack8<T>(raw, f);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] += f[i];
+}
+template <>
+__device__ __forceinline__ void accum8<float>(float (&acc)[8], const uint4& raw) {
+  acc[0] += __uint_as_float(raw.x);
+  acc[1] += __uint_as_float(raw.y);
+  acc[2] += __uint_as_float(raw.z);
+  acc[3] += __uint_as_float(raw.w);
+}
+
+// ---- one-shot all-reduce: every rank pushes its whole input to every peer, then sums locally.
+// Latency-optimal for decode-size messages (one NVLink round trip).  `nvec` = 16-byte vectors.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(SymmWs ws, const uint4* __restrict__ in,
+                                                                     uint4* __restrict__ out, int64_t nvec) {
+  const uint32_t e = *ws.epoch + 1;
+  const int par = e & 1;
+  const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
+  const int64_t v0 = (int64_t)blockIdx.x * per_cta, v1 = min(nvec, v0 + per_cta);
+
+  // push my chunk into slot [rank] of every peer's buffer
+  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
+    const uint4 val = in[v];
+#pragma unroll 1
+    for (int p = 1; p < ws.nranks; ++p) {
+      const int peer = (ws.rank + p) % ws.nranks;
+      symm_buf<uint4>(ws, peer, par)[(int64_t)ws.rank * nvec + v] = val;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < ws.nranks && threadIdx.x != ws.rank)
+    st_release_sys(symm_flag(ws, threadIdx.x, 0, blockIdx.x) + ws.rank, e);
+  if (threadIdx.x < ws.nranks && threadIdx.x != ws.rank)
+    wait_flag_ge(symm_flag(ws, ws.rank, 0, blockIdx.x) + threadIdx.x, e, 1);
+  __syncthreads();
+
+  const uint4* mine = symm_buf<uint4>(ws, ws.rank, par);
+  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int r = 0; r < ws.nranks; ++r) {  // fixed order -> bit-identical on all ranks
+      const uint4 raw = (r == ws.rank) ? in[v] : ld_cg_v4(mine + (int64_t)r * nvec + v);
+      accum8<T>(acc, raw);
+    }
+    uint4 o;
+    if constexpr (std::is_same<T, float>::value) {
+      o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+    } else {
+      o = pack8<T>(acc);
+    }
+    out[v] = o;
+  }
+  symm_finish(ws, e);
+}
+
+// ---- two-shot all-reduce: reduce-scatter (each rank owns nvec/nranks vectors) + all-gather.
+// Per-GPU NVLink traffic 2*(t-1)/t * bytes instead of (t-1) * bytes: the bandwidth regime.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(SymmWs ws, const uint4* __restrict__ in,
+                                                                     uint4* __restrict__ out, int64_t nvec) {
+  const uint32_t e = *ws.epoch + 1;
+  const int par = e & 1;
+  const int n = ws.nranks;
+  const int64_t chunk = nvec / n;  // host guarantees divisibility
+  const int64_t per_cta = (chunk + gridDim.x - 1) / gridDim.x;
+  const int64_t c0 = (int64_t)blockIdx.x * per_cta, c1 = min(chunk, c0 + per_cta);
+  // buffer layout per parity: [n][chunk] partials (phase 1)  then  [n][chunk] results (phase 2)
+
+  // phase 1: send sub-chunk of chunk `peer` to its owner
+  for (int64_t c = c0 + threadIdx.x; c < c1; c += kThreads) {
+#pragma unroll 1
+    for (int p = 1; p < n; ++p) {
+      const int peer = (ws.rank + p) % n;
+      symm_buf<uint4>(ws, peer, par)[(int64_t)ws.rank * chunk + c] = in[(int64_t)peer * chunk + c];
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < n && threadIdx.x != ws.rank) st_release_sys(symm_flag(ws, threadIdx.x, 0, blockIdx.x) + ws.rank, e);
+  if (threadIdx.x < n && threadIdx.x != ws.rank) wait_flag_ge(symm_flag(ws, ws.rank, 0, blockIdx.x) + threadIdx.x, e, 2);
+  __syncthreads();
+
+  // phase 2: reduce my chunk, broadcast the result
+  const uint4* mine = symm_buf<uint4>(ws, ws.rank, par);
+  for (int64_t c = c0 + threadIdx.x; c < c1; c += kThreads) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int r = 0; r < n; ++r) {
+      const uint4 raw = (r == ws.rank) ? in[(int64_t)ws.rank * chunk + c] : ld_cg_v4(mine + (int64_t)r * chunk + c);
+      accum8<T>(acc, raw);
+    }
+    uint4 o;
+    if constexpr (std::is_same<T, float>::value) {
+      o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+    } else {
+      o = pack8<T>(acc);
+    }
+    out[(int64_t)ws.rank * chunk + c] = o;
+#pragma unroll 1
+    for (int p = 1; p < n; ++p) {
+      const int peer = (ws.rank + p) % n;
+      symm_buf<uint4>(ws, peer, par)[(int64_t)(n + ws.rank) * chunk + c] = o;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < n && threadIdx.x != ws.rank) st_release_sys(symm_flag(ws, threadIdx.x, 1, blockIdx.x) + ws.rank, e);
+  if (threadIdx.x < n && threadIdx.x != ws.rank) wait_flag_ge(symm_flag(ws, ws.rank, 1, blockIdx.x) + threadIdx.x, e, 3);
+  __syncthreads();
+
+  // phase 3: collect the other owners' results
+  for (int64_t c = c0 + threadIdx.x; c < c1; c += kThreads) {
+#pragma unroll 1
+    for (int p = 1; p < n; ++p) {
+      const int r = (ws.rank + p) % n;
+      out[(int64_t)r * chunk + c] = ld_cg_v4(mine + (int64_t)(n + r) * chunk + c);
+    }
+  }
+  symm_finish(ws, e);
+}
+
+// ---- all-gather: out[r] = rank r's input (used for the vocab-parallel logits, reference N3)
+__global__ void __launch_bounds__(kThreads) allgather_kernel(SymmWs ws, const uint4* __restrict__ in,
+                                                             uint4* __restrict__ out, int64_t nvec) {
+  const uint32_t e = *ws.epoch + 1;
+  const int par = e & 1;
+  const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
+  const int64_t v0 = (int64_t)blockIdx.x * per_cta, v1 = min(nvec, v0 + per_cta);
+  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
+    const uint4 val = in[v];
+    out[(int64_t)ws.rank * nvec + v] = val;
+#pragma unroll 1
+    for (int p = 1; p < ws.nranks; ++p) {
+      const int peer = (ws.rank + p) % ws.nranks;
+      symm_buf<uint4>(ws, peer, par)[(int64_t)ws.rank * nvec + v] = val;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < ws.nranks && threadIdx.x != ws.rank)
+    st_release_sys(symm_flag(ws, threadIdx.x, 0, blockIdx.x) + ws.rank, e);
+  if (threadIdx.x < ws.nranks && threadIdx.x != ws.rank)
+    wait_flag_ge(symm_flag(ws, ws.rank, 0, blockIdx.x) + threadIdx.x, e, 4);
+  __syncthreads();
+  const uint4* mine = symm_buf<uint4>(ws, ws.rank, par);
+  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
+#pragma unroll 1
+    for (int p = 1; p < ws.nranks; ++p) {
+      const int r = (ws.rank + p) % ws.nranks;
+      out[(int64_t)r * nvec + v] = ld_cg_v4(mine + (int64_t)r * nvec + v);
+    }
+  }
+  symm_finish(ws, e);
+}
+
+int pick_grid(int64_t nvec, int max_ctas) {
+  int64_t g = (nvec + kThreads - 1) / kThreads;  // one 16-byte vector per thread per pass
+  if (g < 1) g = 1;
+  if (g > max_ctas) g = max_ctas;
+  return (int)g;
+}
+
+}  // namespace
+
+// algo: 0 = auto, 1 = one-shot, 2 = two-shot.  `n` = element count.
+LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, int dtype, int algo,
+                              cudaStream_t stream) {
+  const int esz = (dtype == LLMSS_F32) ? 4 : 2;
+  const int64_t bytes = n * esz;
+  LLMSS_REQUIRE(bytes % 16 == 0, "allreduce: byte size %lld must be a multiple of 16", (long long)bytes);
+  LLMSS_REQUIRE(((uintptr_t)in % 16 == 0) && ((uintptr_t)out % 16 == 0), "allreduce: pointers must be 16-byte aligned");
+  const int64_t nvec = bytes / 16;
+  if (ws->nranks == 1) {
+    if (in != out) LLMSS_CHECK_CUDA(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice, stream));
+    return 0;
+  }
+  if (algo == 0) algo = (bytes <= (int64_t)(1 << 20) || nvec % ws->nranks != 0) ? 1 : 2;
+  if (algo == 2 && nvec % ws->nranks != 0) algo = 1;
+  const int64_t need = (algo == 1) ? bytes * ws->nranks : bytes * 2;
+  LLMSS_REQUIRE((size_t)need <= ws->buf_bytes, "allreduce: message of %lld bytes needs %lld bytes of workspace (have %zu)",
+                (long long)bytes, (long long)need, ws->buf_bytes);
+  SymmWs w = *ws;
+  if (algo == 1) {
+    const int grid = pick_grid(nvec, 128);
+    if (dtype == LLMSS_F16) allreduce_oneshot_kernel<__half><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+    else if (dtype == LLMSS_BF16) allreduce_oneshot_kernel<__nv_bfloat16><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+    else allreduce_oneshot_kernel<float><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+  } else {
+    const int grid = pick_grid(nvec / ws->nranks, 144);
+    if (dtype == LLMSS_F16) allreduce_twoshot_kernel<__half><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+    else if (dtype == LLMSS_BF16) allreduce_twoshot_kernel<__nv_bfloat16><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+    else allreduce_twoshot_kernel<float><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+  }
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// out must hold nranks * bytes; slot r receives rank r's input.
+LLMSS_API int llmss_allgather(SymmWs* ws, const void* in, void* out, int64_t bytes, cudaStream_t stream) {
+  LLMSS_REQUIRE(bytes % 16 == 0, "allgather: byte size %lld must be a multiple of 16", (long long)bytes);
+  LLMSS_REQUIRE(((uintptr_t)in % 16 == 0) && ((uintptr_t)out % 16 == 0), "allgather: pointers must be 16-byte aligned");
+  if (ws->nranks == 1) {
+    if (in != out) LLMSS_CHECK_CUDA(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice, stream));
+    return 0;
+  }
+  LLMSS_REQUIRE((size_t)(bytes * ws->nranks) <= ws->buf_bytes, "allgather: %lld bytes x %d ranks exceeds workspace %zu",
+                (long long)bytes, ws->nranks, ws->buf_bytes);
+  const int64_t nvec = bytes / 16;
+  allgather_kernel<<<pick_grid(nvec, 128), kThreads, 0, stream>>>(*ws, (const uint4*)in, (uint4*)out, nvec);
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

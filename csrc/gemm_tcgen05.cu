@@ -1,0 +1,539 @@
+// K5 / K1 / K2: tcgen05 GEMM for every linear layer, with the tensor-parallel all-reduce
+// fused into the epilogue over NVLink peer memory.
+//
+//   out[M, N] = epilogue( x[M, K] @ w[N, K]^T )          (w in HF nn.Linear layout)
+//
+// Replaces the reference's cuBLAS `F.linear` call sites (SURVEY.md G3, G4, G9, G10, G12,
+// G14; layers.py:62,123) and, for row-parallel layers, the separate blocking NCCL
+// all-reduce that follows them (N1; layers.py:175-179).
+//
+// Design (B200-first, not a cuBLAS clone):
+//  * swap-AB: the *weight* tile is the UMMA A operand (M=128 output features per tile) and
+//    the activations are the B operand (N = 16..256 tokens).  Decode batches (1..256 tokens)
+//    therefore use full-width tensor-core instructions with no padding waste, and the
+//    accumulator sits in TMEM as [feature lane][token column] so bias is a per-thread scalar.
+//  * TMA (cp.async.bulk.tensor, 128B swizzle) feeds a multi-stage mbarrier ring; one elected
+//    thread issues tcgen05.mma; accumulators are double-buffered in TMEM so the epilogue of
+//    one work segment overlaps the main loop of the next.
+//  * stream-K persistent scheduling: the (tile x k-block) iteration space is cut into
+//    gridDim.x equal contiguous ranges, so all 148 SMs stream weights for the same time
+//    whatever the shape (decode GEMMs have far fewer than 148 output tiles).  Tiles touched
+//    by several CTAs are reduced through an L2-resident fp32 workspace by the last arriver
+//    in a fixed order (deterministic).
+//  * fused all-reduce (ar=1): the CTA that owns the finished tile pushes it (16-byte
+//    vectors, tile-blocked layout) into every peer's symmetric buffer, raises a per-tile
+//    flag, waits for the peers' flags of the *same tile only*, sums the t partials in rank
+//    order (bit-identical on all ranks), adds bias/residual and stores.  Transfer of tile i
+//    overlaps the math of tile i+1; there is no grid-wide or host-side barrier.
+//  * epilogues: bias, activation (optionally only for features >= act_start: GPT-J's fused
+//    QKV+fc_in GEMM), SwiGLU gating on interleaved (gate, up) rows, residual add, fp32 out.
+#include "common.cuh"
+#include "symm.cuh"
+
+#include <cuda.h>
+#include <string.h>
+
+namespace {
+
+constexpr int BM = 128;  // output features per tile (UMMA M)
+constexpr int BK = 64;   // k-block: 64 x 16-bit = one 128-byte swizzle row
+constexpr int kNumThreads = 192;  // warp 0 TMA, warp 1 MMA (+TMEM alloc), warps 2..5 epilogue
+constexpr int kEpiThreads = 128;
+
+template <int BN>
+struct Cfg {
+  static constexpr int W_BYTES = BM * BK * 2;
+  static constexpr int X_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = W_BYTES + X_BYTES;
+  static constexpr int STAGES_RAW = (196 * 1024) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 12 ? 12 : STAGES_RAW;
+  static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int CH = (BN < 32) ? BN : 32;  // accumulator columns per epilogue chunk
+  static constexpr int NCH = BN / CH;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
+};
+
+struct GemmArgs {
+  int M, N, K;
+  int tiles_n, tiles_m, kb_total;
+  int dtype;  // LLMSS_F16 / LLMSS_BF16
+  const void* bias;
+  const void* residual;
+  int64_t ldr;
+  void* out;
+  int64_t ldo;
+  int out_f32;
+  int act, act_start, gated;
+  float* sk_ws;           // stream-K partial slots: [2 * grid][BN][128] fp32 (first / last segment of a CTA)
+  uint32_t* sk_counters;  // [tiles], zero between launches
+  int ar;                 // fused all-reduce over ws
+  SymmWs ws;
+};
+
+// ----- stream-K work decomposition (identical on every rank) -----
+struct Segment {
+  int tile, kb0, kb1;  // k-block range [kb0, kb1) of `tile`
+  int first_cta, last_cta;  // CTAs contributing to this tile
+};
+__device__ __forceinline__ int64_t cta_start(int g, int64_t total, int G) { return ((int64_t)g * total) / G; }
+__device__ __forceinline__ int cta_of(int64_t w, int64_t total, int G) { return (int)((((w + 1) * G) - 1) / total); }
+
+struct SegIter {
+  int64_t w, w_end, total;
+  int kb_total, G;
+  __device__ SegIter(int g, int G_, int tiles, int kb_total_) : kb_total(kb_total_), G(G_) {
+    total = (int64_t)tiles * kb_total_;
+    w = cta_start(g, total, G_);
+    w_end = cta_start(g + 1, total, G_);
+  }
+  __device__ bool next(Segment& s) {
+    if (w >= w_end) return false;
+    s.tile = (int)(w / kb_total);
+    s.kb0 = (int)(w % kb_total);
+    const int64_t tile_end = (int64_t)(s.tile + 1) * kb_total;
+    const int64_t e = tile_end < w_end ? tile_end : w_end;
+    s.kb1 = s.kb0 + (int)(e - w);
+    s.first_cta = cta_of((int64_t)s.tile * kb_total, total, G);
+    s.last_cta = cta_of(tile_end - 1, total, G);
+    w = e;
+    return true;
+  }
+};
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ float ld_cg_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint4 ld_cg_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+template <typename T, int BN>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                   const __grid_constant__ GemmArgs a) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + C::STAGES;
+  uint64_t* tfull_bar = bars + 2 * C::STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  volatile int* s_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = gridDim.x, g = blockIdx.x;
+  const int tiles = a.tiles_n * a.tiles_m;
+
+  uint32_t epoch = 0;
+  if (a.ar) epoch = *a.ws.epoch + 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_x);
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      const uint64_t pol_w = l2_policy_evict_first();  // weights are streamed once
+      const uint64_t pol_x = l2_policy_evict_last();   // activations are re-read by every tile
+      int stage = 0;
+      uint32_t phase = 0;
+      SegIter it(g, G, tiles, a.kb_total);
+      Segment sg;
+      while (it.next(sg)) {
+        const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1, 10);
+          uint8_t* sw = smem + stage * C::STAGE_BYTES;
+          mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
+          tma_load_2d(sw + C::W_BYTES, &tmap_x, &full_bar[stage], kb * BK, tm * BN, pol_x);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      SegIter it(g, G, tiles, a.kb_total);
+      Segment sg;
+      while (it.next(sg)) {
+        mbar_wait(&tempty_bar[as], aphase ^ 1, 20);
+        tcgen05_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase, 21);
+          tcgen05_fence_after();
+          const uint32_t sw = smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint32_t sx = sw + C::W_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            umma_f16_ss(d_tmem, umma_desc_k_sw128(sw + k * 32), umma_desc_k_sw128(sx + k * 32), idesc,
+                        (kb > sg.kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
+    const int quarter = warp & 3;            // TMEM lane quarter this warp may access
+    const int f = quarter * 32 + lane;       // feature within the tile
+    const int epi_tid = threadIdx.x - 64;
+    int as = 0;
+    uint32_t aphase = 0;
+    SegIter it(g, G, tiles, a.kb_total);
+    Segment sg;
+    const T* bias = reinterpret_cast<const T*>(a.bias);
+    const T* residual = reinterpret_cast<const T*>(a.residual);
+    constexpr int CH = C::CH, NCH = C::NCH;
+    int seg_idx = -1;
+    constexpr int VPC = CH * (int)sizeof(T) / 16;  // 16-byte vectors per chunk per thread (AR exchange)
+    const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
+
+    while (it.next(sg)) {
+      ++seg_idx;
+      const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
+      const int n = tn * BM + f;
+      const int m0 = tm * BN;
+      const bool full_tile = (sg.kb0 == 0 && sg.kb1 == a.kb_total);
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN);
+
+      mbar_wait(&tfull_bar[as], aphase, 30);
+      tcgen05_fence_after();
+
+      // ---- final-value consumers -------------------------------------------------
+      auto store_chunk = [&](const float (&v)[CH], int c) {
+        // bias / activation / gating / residual, then transposed store out[m][n]
+        const float b = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+#pragma unroll
+        for (int j = 0; j < CH; ++j) {
+          const int m = m0 + c * CH + j;
+          float y = v[j] + b;
+          if (a.gated) {
+            const float other = __shfl_xor_sync(0xffffffffu, y, 1);
+            if ((lane & 1) == 0 && m < a.M && n < a.N) {
+              float r = act_apply(y, a.act) * other;
+              const int64_t o = (int64_t)m * a.ldo + (n >> 1);
+              if (residual != nullptr) r += to_f32(residual[(int64_t)m * a.ldr + (n >> 1)]);
+              if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = r;
+              else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(r);
+            }
+          } else if (m < a.M && n < a.N) {
+            if (a.act != LLMSS_ACT_NONE && n >= a.act_start) y = act_apply(y, a.act);
+            if (residual != nullptr) y += to_f32(residual[(int64_t)m * a.ldr + n]);
+            const int64_t o = (int64_t)m * a.ldo + n;
+            if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = y;
+            else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(y);
+          }
+        }
+      };
+      auto push_chunk = [&](const float (&v)[CH], int c, int par) {
+        // round to T and write the chunk into slot [rank] of every rank's exchange buffer
+        uint4 vec[VPC];
+#pragma unroll
+        for (int q = 0; q < VPC; ++q) {
+          float t8[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) t8[i] = v[q * 8 + i];
+          vec[q] = pack8<T>(t8);
+        }
+        const size_t off = (size_t)a.ws.rank * ar_slot_bytes + ((size_t)sg.tile * NCH + c) * (BM * CH * sizeof(T));
+#pragma unroll 1
+        for (int p = 0; p < a.ws.nranks; ++p) {
+          const int peer = (a.ws.rank + p) % a.ws.nranks;
+          uint4* dst = reinterpret_cast<uint4*>(symm_buf<uint8_t>(a.ws, peer, par) + off);
+#pragma unroll
+          for (int q = 0; q < VPC; ++q) dst[q * BM + f] = vec[q];
+        }
+      };
+
+      bool have_final = full_tile;
+      if (!full_tile) {
+        // ---- stream-K: publish my partial, last arriver reduces ----
+        float* part = a.sk_ws + (size_t)(2 * g + (seg_idx > 0 ? 1 : 0)) * (BM * BN);
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          uint32_t r[CH];
+          if constexpr (CH == 32) tmem_ld_32x32b_x32(t_addr + c * CH, r);
+          else tmem_ld_32x32b_x16(t_addr + c * CH, *reinterpret_cast<uint32_t(*)[16]>(r));
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < CH; ++j) part[(c * CH + j) * BM + f] = __uint_as_float(r[j]);
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[as]);
+        __threadfence();
+        epi_bar();
+        if (epi_tid == 0) {
+          const int contributors = sg.last_cta - sg.first_cta + 1;
+          const uint32_t old = atomicAdd(&a.sk_counters[sg.tile], 1u);
+          const int last = (old == (uint32_t)(contributors - 1));
+          if (last) a.sk_counters[sg.tile] = 0;
+          *s_flag = last;
+        }
+        epi_bar();
+        have_final = (*s_flag != 0);
+        epi_bar();  // s_flag may be rewritten by the next segment
+        if (have_final) __threadfence();
+      }
+
+      if (have_final) {
+        const int par = epoch & 1;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float v[CH];
+          if (full_tile) {
+            uint32_t r[CH];
+            if constexpr (CH == 32) tmem_ld_32x32b_x32(t_addr + c * CH, r);
+            else tmem_ld_32x32b_x16(t_addr + c * CH, *reinterpret_cast<uint32_t(*)[16]>(r));
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < CH; ++j) v[j] = __uint_as_float(r[j]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < CH; ++j) v[j] = 0.f;
+            for (int cta = sg.first_cta; cta <= sg.last_cta; ++cta) {  // fixed order: deterministic
+              // a tile is the *first* segment of every contributor except (possibly) its first one
+              const int slot = 2 * cta + ((cta == sg.first_cta && cta_start(cta, it.total, G) != (int64_t)sg.tile * a.kb_total) ? 1 : 0);
+              const float* p = a.sk_ws + (size_t)slot * (BM * BN);
+#pragma unroll
+              for (int j = 0; j < CH; ++j) v[j] += ld_cg_f32(p + (c * CH + j) * BM + f);
+            }
+          }
+          if (a.ar) push_chunk(v, c, par);
+          else store_chunk(v, c);
+        }
+        if (full_tile) {
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[as]);
+        }
+        if (a.ar) {
+          // ---- per-tile handshake with the peers, then rank-ordered sum ----
+          __threadfence_system();
+          epi_bar();
+          if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
+            st_release_sys(symm_flag(a.ws, epi_tid, 0, sg.tile) + a.ws.rank, epoch);
+          if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
+            wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, sg.tile) + epi_tid, epoch, 31);
+          epi_bar();
+          const uint8_t* mine = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
+#pragma unroll 1
+          for (int c = 0; c < NCH; ++c) {
+            float v[CH];
+#pragma unroll
+            for (int j = 0; j < CH; ++j) v[j] = 0.f;
+            for (int r = 0; r < a.ws.nranks; ++r) {
+              const uint4* src = reinterpret_cast<const uint4*>(
+                  mine + (size_t)r * ar_slot_bytes + ((size_t)sg.tile * NCH + c) * (BM * CH * sizeof(T)));
+#pragma unroll
+              for (int q = 0; q < VPC; ++q) {
+                float t8[8];
+                unpack8<T>(ld_cg_u4(src + q * BM + f), t8);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[q * 8 + i] += t8[i];
+              }
+            }
+            store_chunk(v, c);
+          }
+        }
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  // ---- teardown ----
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+  if (a.ar) symm_finish(a.ws, epoch);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+// 2-D row-major [rows, cols] 16-bit tensor with row stride `ld` elements; box = [box_rows, 64 cols], 128B swizzle.
+int make_tmap(CUtensorMap* map, const void* ptr, int dtype, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  LLMSS_REQUIRE(enc != nullptr, "gemm: cuTensorMapEncodeTiled entry point not available");
+  LLMSS_REQUIRE(((uintptr_t)ptr % 16) == 0 && (ld * 2) % 16 == 0, "gemm: operand base / row stride must be 16-byte aligned");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, dtype == LLMSS_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  LLMSS_REQUIRE(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld)",
+                (int)r, (long long)rows, (long long)cols, (long long)ld);
+  return 0;
+}
+
+int g_num_sms = 0;
+int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+template <typename T, int BN>
+int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  static bool configured = false;
+  auto kern = gemm_swapab_kernel<T, BN>;
+  if (!configured) {
+    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured = true;
+  }
+  kern<<<grid, kNumThreads, C::SMEM_BYTES, stream>>>(tw, tx, a);
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int pick_bn(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256; }
+
+}  // namespace
+
+// Plan of a GEMM launch (so the caller can size the workspaces before capture).
+struct llmss_gemm_plan {
+  int bn, tiles, kb_total, grid;
+  int64_t sk_ws_floats;     // stream-K partial workspace (floats)
+  int64_t sk_counters;      // uint32 counters (must be zero before first use)
+  int64_t ar_bytes;         // symmetric buffer bytes needed per parity when ar=1
+};
+
+LLMSS_API int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p) {
+  const int bn = pick_bn(M);
+  const int tiles_n = (N + BM - 1) / BM, tiles_m = (M + bn - 1) / bn;
+  const int tiles = tiles_n * tiles_m;
+  const int kb_total = (K + BK - 1) / BK;
+  const int64_t work = (int64_t)tiles * kb_total;
+  int sms = max_ctas > 0 ? max_ctas : num_sms();
+  // at least ~4 k-blocks (64 KB of weights) per CTA so the stream-K fix-up stays a small fraction
+  int64_t grid = work / 4;
+  if (grid < tiles && tiles <= sms) grid = tiles;
+  if (grid < 1) grid = 1;
+  if (grid > sms) grid = sms;
+  if (grid > work) grid = work;
+  p->bn = bn;
+  p->tiles = tiles;
+  p->kb_total = kb_total;
+  p->grid = (int)grid;
+  p->sk_ws_floats = (int64_t)2 * grid * BM * bn;
+  p->sk_counters = tiles;
+  p->ar_bytes = (int64_t)nranks * tiles * BM * bn * elem_bytes;
+  return 0;
+}
+
+// out = epilogue(x @ w^T).  x: [M,K] row stride ldx; w: [N,K] row stride ldw; both 16-bit `dtype`.
+// gated: rows of w interleave (gate, up); out has N/2 columns.  ar: fused all-reduce over `ws`
+// (bias/residual are applied once, after the reduction).  sk_ws / sk_counters: see plan query.
+LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
+                         const void* residual, int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype,
+                         int out_f32, int act, int act_start, int gated, float* sk_ws, uint32_t* sk_counters,
+                         SymmWs* ws, int max_ctas, cudaStream_t stream) {
+  LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "gemm: dtype must be f16/bf16");
+  LLMSS_REQUIRE(M > 0 && N > 0 && K > 0 && K % 8 == 0, "gemm: bad shape M=%d N=%d K=%d (K must be a multiple of 8)", M, N, K);
+  LLMSS_REQUIRE(!gated || (N % 2 == 0), "gemm: gated epilogue needs even N");
+  const bool ar = (ws != nullptr && ws->nranks > 1);
+  LLMSS_REQUIRE(!(ar && (gated || act != LLMSS_ACT_NONE || out_f32)), "gemm: fused all-reduce supports bias/residual epilogues only");
+  llmss_gemm_plan p;
+  llmss_gemm_plan_query(M, N, K, ar ? ws->nranks : 1, 2, max_ctas, &p);
+  const bool need_sk = (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
+  LLMSS_REQUIRE(!need_sk || (sk_ws != nullptr && sk_counters != nullptr), "gemm: stream-K workspace required for this shape");
+  if (ar) {
+    LLMSS_REQUIRE(p.tiles <= kSymmMaxSlots, "gemm: %d tiles exceed the %d flag slots of the symmetric workspace", p.tiles, kSymmMaxSlots);
+    LLMSS_REQUIRE((size_t)p.ar_bytes <= ws->buf_bytes, "gemm: fused all-reduce needs %lld bytes of symmetric buffer (have %zu)",
+                  (long long)p.ar_bytes, ws->buf_bytes);
+  }
+  CUtensorMap tw, tx;
+  if (int e = make_tmap(&tw, w, dtype, N, K, ldw, BM)) return e;
+  if (int e = make_tmap(&tx, x, dtype, M, K, ldx, p.bn)) return e;
+  GemmArgs a;
+  memset(&a, 0, sizeof(a));
+  a.M = M; a.N = N; a.K = K;
+  a.tiles_n = (N + BM - 1) / BM;
+  a.tiles_m = (M + p.bn - 1) / p.bn;
+  a.kb_total = p.kb_total;
+  a.dtype = dtype;
+  a.bias = bias; a.residual = residual; a.ldr = ldr;
+  a.out = out; a.ldo = ldo; a.out_f32 = out_f32;
+  a.act = act; a.act_start = act_start; a.gated = gated;
+  a.sk_ws = sk_ws; a.sk_counters = sk_counters;
+  a.ar = ar ? 1 : 0;
+  if (ar) a.ws = *ws;
+#define LLMSS_LAUNCH(T_, BN_) return launch<T_, BN_>(tw, tx, a, p.grid, stream)
+  if (dtype == LLMSS_F16) {
+    switch (p.bn) {
+      case 16: LLMSS_LAUNCH(__half, 16);
+      case 32: LLMSS_LAUNCH(__half, 32);
+      case 64: LLMSS_LAUNCH(__half, 64);
+      case 128: LLMSS_LAUNCH(__half, 128);
+      default: LLMSS_LAUNCH(__half, 256);
+    }
+  } else {
+    switch (p.bn) {
+      case 16: LLMSS_LAUNCH(__nv_bfloat16, 16);
+      case 32: LLMSS_LAUNCH(__nv_bfloat16, 32);
+      case 64: LLMSS_LAUNCH(__nv_bfloat16, 64);
+      case 128: LLMSS_LAUNCH(__nv_bfloat16, 128);
+      default: LLMSS_LAUNCH(__nv_bfloat16, 256);
+    }
+  }
+#undef LLMSS_LAUNCH
+}

@@ -1,0 +1,294 @@
+// K11 (sampling half): fused greedy / top-p / top-k / temperature sampler over fp32 logits.
+//
+// Replaces the reference's rank-0-only sampling (SURVEY.md G15/G16 + N6: argmax or
+// softmax + HF warpers + multinomial on rank 0, then a broadcast of the token,
+// generate.py:109-144) with one launch that every rank runs on identical gathered logits
+// and an identical counter-based RNG, so all ranks agree without a collective.  It
+// implements the *intended* warper semantics (quirk Q1: the reference never applies
+// them): top-p on the raw distribution, then top-k, then temperature, then one draw.
+//
+// One CTA per row.  Passes over the row (L2-resident): max/argmax, sum-exp, a 4-pass
+// 8-bit radix select for the k-th largest logit, candidate gather (<= 1024), in-block
+// bitonic sort (value desc, index asc), prefix-mass scan for top-p, inverse-CDF draw.
+// top_k == 0 is treated as k = 1024 when top_p < 1 (top-p is evaluated over the 1024 most
+// probable tokens); top_k == 0 && top_p >= 1 is a plain multinomial over the whole row.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 1024;
+constexpr int kMaxCand = 1024;
+
+__device__ __forceinline__ uint32_t fkey(float x) {  // order-preserving float -> uint
+  uint32_t u = __float_as_uint(x);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ uint32_t fmix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ float rng_uniform(uint32_t seed, uint32_t step, uint32_t row) {
+  uint32_t x = row * 0x9E3779B1u + step * 0x85EBCA77u + seed * 0xC2B2AE3Du;
+  x = fmix32(fmix32(x));
+  return (float)(x >> 8) * (1.0f / 16777216.0f);
+}
+
+struct MaxIdx { float v; int i; };
+__device__ __forceinline__ MaxIdx better(MaxIdx a, MaxIdx b) {
+  return (b.v > a.v || (b.v == a.v && b.i < a.i)) ? b : a;
+}
+
+__device__ __forceinline__ float block_sum_f(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = (l < kThreads / 32) ? red[l] : 0.f;
+  t = warp_sum(t);
+  return t;
+}
+
+__global__ void __launch_bounds__(kThreads) sample_kernel(
+    const float* __restrict__ logits, int64_t ld, int vocab, const int* __restrict__ greedy,
+    const float* __restrict__ temperature, const int* __restrict__ top_k, const float* __restrict__ top_p,
+    uint32_t* __restrict__ rng_state, int* __restrict__ out_tokens, long long* __restrict__ out_tokens64) {
+  __shared__ float red[32];
+  __shared__ int redi[32];
+  __shared__ int hist[256];
+  __shared__ float cval[kMaxCand];
+  __shared__ int cidx[kMaxCand];
+  __shared__ int s_count;
+  __shared__ uint32_t s_prefix;
+  __shared__ int s_krem;
+  __shared__ int s_pick;
+  __shared__ float s_f;
+
+  const int row = blockIdx.x;
+  const float* x = logits + (int64_t)row * ld;
+  const int tid = threadIdx.x;
+
+  // ---- pass 1: max / argmax (first index on ties)
+  MaxIdx best{-INFINITY, 0x7fffffff};
+  for (int i = tid; i < vocab; i += kThreads) best = better(best, MaxIdx{x[i], i});
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MaxIdx other{__shfl_xor_sync(0xffffffffu, best.v, o), __shfl_xor_sync(0xffffffffu, best.i, o)};
+    best = better(best, other);
+  }
+  if ((tid & 31) == 0) { red[tid >> 5] = best.v; redi[tid >> 5] = best.i; }
+  __syncthreads();
+  if (tid < 32) {
+    MaxIdx b{red[tid], redi[tid]};
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      MaxIdx other{__shfl_xor_sync(0xffffffffu, b.v, o), __shfl_xor_sync(0xffffffffu, b.i, o)};
+      b = better(b, other);
+    }
+    if (tid == 0) { s_f = b.v; s_pick = b.i; }
+  }
+  __syncthreads();
+  const float xmax = s_f;
+  const int amax = s_pick;
+  const uint32_t seed = rng_state[2 * row], step = rng_state[2 * row + 1];
+  if (tid == 0) rng_state[2 * row + 1] = step + 1;
+  if (greedy[row]) {
+    if (tid == 0) {
+      if (out_tokens) out_tokens[row] = amax;
+      if (out_tokens64) out_tokens64[row] = amax;
+    }
+    return;
+  }
+  const float temp = temperature[row];
+  const float inv_t = 1.0f / temp;
+  const float tp = top_p[row];
+  int k = top_k[row];
+  const float u01 = rng_uniform(seed, step, (uint32_t)row);
+
+  if (k <= 0 && tp >= 1.0f) {
+    // ---- plain multinomial over the whole row, inverse CDF in index order
+    float part = 0.f;
+    const int per = (vocab + kThreads - 1) / kThreads;
+    const int i0 = tid * per, i1 = min(vocab, i0 + per);
+    for (int i = i0; i < i1; ++i) part += __expf((x[i] - xmax) * inv_t);
+    // block exclusive scan of `part`
+    float incl = part;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      float n = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((tid & 31) >= o) incl += n;
+    }
+    __syncthreads();
+    if ((tid & 31) == 31) red[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+      float w = red[tid], wi = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        float n = __shfl_up_sync(0xffffffffu, wi, o);
+        if (tid >= o) wi += n;
+      }
+      red[tid] = wi - w;  // exclusive warp offsets
+      if (tid == 31) s_f = wi;
+    }
+    if (tid == 0) s_pick = vocab - 1;
+    __syncthreads();
+    const float total = s_f;
+    const float target = u01 * total;
+    const float before = red[tid >> 5] + incl - part;
+    if (part > 0.f && target >= before && target < before + part) {
+      float c = before;
+      int pick = i1 - 1;
+      for (int i = i0; i < i1; ++i) {
+        c += __expf((x[i] - xmax) * inv_t);
+        if (target < c) { pick = i; break; }
+      }
+      s_pick = pick;  // exactly one thread's interval contains target
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (out_tokens) out_tokens[row] = s_pick;
+      if (out_tokens64) out_tokens64[row] = s_pick;
+    }
+    return;
+  }
+
+  // ---- sum-exp at temperature 1 (top-p is applied to the raw distribution)
+  float part = 0.f;
+  for (int i = tid; i < vocab; i += kThreads) part += __expf(x[i] - xmax);
+  const float Z = block_sum_f(part, red);
+
+  // ---- radix select: key of the k-th largest logit
+  if (k <= 0 || k > kMaxCand) k = kMaxCand;
+  if (k > vocab) k = vocab;
+  if (tid == 0) { s_prefix = 0; s_krem = k; }
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 24 - 8 * pass;
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
+    const uint32_t prefix = s_prefix;
+    const uint32_t pmask = (pass == 0) ? 0u : (0xffffffffu << (shift + 8));
+    for (int i = tid; i < vocab; i += kThreads) {
+      const uint32_t key = fkey(x[i]);
+      if ((key & pmask) == prefix) atomicAdd(&hist[(key >> shift) & 0xff], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int rem = s_krem, bin = 255;
+      for (; bin > 0; --bin) {
+        if (hist[bin] >= rem) break;
+        rem -= hist[bin];
+      }
+      s_krem = rem;
+      s_prefix = prefix | ((uint32_t)bin << shift);
+    }
+    __syncthreads();
+  }
+  const uint32_t thr_key = s_prefix;
+
+  // ---- gather candidates (logit >= k-th largest), then sort (value desc, index asc)
+  if (tid == 0) s_count = 0;
+  __syncthreads();
+  for (int i = tid; i < vocab; i += kThreads) {
+    const float v = x[i];
+    if (fkey(v) >= thr_key) {
+      const int slot = atomicAdd(&s_count, 1);
+      if (slot < kMaxCand) { cval[slot] = v; cidx[slot] = i; }
+    }
+  }
+  __syncthreads();
+  const int count = min(s_count, kMaxCand);
+  int nsort = 1;
+  while (nsort < count) nsort <<= 1;
+  for (int i = tid; i < nsort; i += kThreads)
+    if (i >= count) { cval[i] = -INFINITY; cidx[i] = 0x7fffffff; }
+  __syncthreads();
+  for (int size = 2; size <= nsort; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const int i = tid;
+      if (i < nsort) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool desc_block = ((i & size) == 0);  // this block sorted "better first"
+          const float vi = cval[i], vj = cval[j];
+          const int ii = cidx[i], ij = cidx[j];
+          const bool i_before_j = (vi > vj) || (vi == vj && ii < ij);
+          if (i_before_j != desc_block) { cval[i] = vj; cval[j] = vi; cidx[i] = ij; cidx[j] = ii; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // ---- top-p over the sorted candidates, temperature weights, inverse-CDF draw (thread 0..31)
+  if (tid < 32) {
+    // n_p = number of sorted positions whose preceding mass is < top_p
+    float run = 0.f;  // mass before the current 32-chunk
+    int n_p = 0;
+    float thr_p = -INFINITY;
+    for (int base = 0; base < count; base += 32) {
+      const int i = base + tid;
+      const float p = (i < count) ? __expf(cval[i] - xmax) / Z : 0.f;
+      float incl = p;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        float n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (tid >= o) incl += n;
+      }
+      const bool ok = (i < count) && ((run + incl - p) < tp);
+      const unsigned mask = __ballot_sync(0xffffffffu, ok);
+      n_p += __popc(mask);
+      run += __shfl_sync(0xffffffffu, incl, 31);
+      if (mask != 0xffffffffu) break;
+    }
+    n_p = max(n_p, 1);
+    thr_p = cval[n_p - 1];
+    // keep = prefix with value >= thr_p (ties stay), already limited to >= k-th largest
+    int n_keep = 0;
+    for (int base = 0; base < count; base += 32) {
+      const int i = base + tid;
+      const unsigned mask = __ballot_sync(0xffffffffu, (i < count) && (cval[i] >= thr_p));
+      n_keep += __popc(mask);
+      if (mask != 0xffffffffu) break;
+    }
+    // total weight at temperature
+    float tot = 0.f;
+    for (int i = tid; i < n_keep; i += 32) tot += __expf((cval[i] - xmax) * inv_t);
+    tot = warp_sum(tot);
+    const float target = u01 * tot;
+    float before = 0.f;
+    int pick = n_keep - 1;
+    bool found = false;
+    for (int base = 0; base < n_keep && !found; base += 32) {
+      const int i = base + tid;
+      const float w = (i < n_keep) ? __expf((cval[i] - xmax) * inv_t) : 0.f;
+      float incl = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        float n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (tid >= o) incl += n;
+      }
+      const bool hit = (i < n_keep) && (target < before + incl);
+      const unsigned mask = __ballot_sync(0xffffffffu, hit);
+      if (mask) { pick = base + __ffs(mask) - 1; found = true; }
+      before += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (tid == 0) {
+      const int tok = cidx[pick];
+      if (out_tokens) out_tokens[row] = tok;
+      if (out_tokens64) out_tokens64[row] = tok;
+    }
+  }
+}
+
+}  // namespace
+
+LLMSS_API int llmss_sample(const float* logits, int64_t ld, int B, int vocab, const int* greedy,
+                           const float* temperature, const int* top_k, const float* top_p, uint32_t* rng_state,
+                           int* out_tokens, long long* out_tokens64, cudaStream_t stream) {
+  LLMSS_REQUIRE(vocab > 0 && ld >= vocab, "sample: bad vocab/ld");
+  if (B == 0) return 0;
+  sample_kernel<<<B, kThreads, 0, stream>>>(logits, ld, vocab, greedy, temperature, top_k, top_p, rng_state,
+                                            out_tokens, out_tokens64);
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,87 @@
+/* llmss_b200 -- C ABI of the hand-written sm_100a kernel library (libllmss_b200.so).
+ *
+ * Every entry point returns 0 on success; on failure it returns a non-zero code and
+ * llmss_last_error() describes the problem.  Pointers are device pointers unless noted.
+ * All launches go to the given stream; nothing here synchronises the device except the
+ * symmetric-memory set-up calls.  dtype: 0 = fp16, 1 = bf16, 2 = fp32.
+ *
+ * Each declaration cites the reference (jongwon-jay-lee/llmss) code it replaces; see
+ * SURVEY.md sections 2.5 / 2.6 for the N*/G* numbering.
+ */
+#ifndef LLMSS_B200_H_
+#define LLMSS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* llmss_stream_t;
+typedef struct SymmWs llmss_symm_t;
+
+enum { LLMSS_DT_F16 = 0, LLMSS_DT_BF16 = 1, LLMSS_DT_F32 = 2 };
+
+const char* llmss_last_error(void);
+int llmss_version(void);
+
+/* ---- symmetric memory (replaces c10d/NCCL bring-up for the hot path; dist.py:44-73) ---- */
+int llmss_symm_alloc(size_t bytes, void** ptr);
+int llmss_symm_free(void* ptr);
+int llmss_ipc_get_handle(void* ptr, unsigned char* out64);
+int llmss_ipc_open_handle(const unsigned char* in64, void** ptr);
+int llmss_ipc_close(void* ptr);
+size_t llmss_symm_region_bytes(size_t buf_bytes);
+int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, llmss_symm_t** out);
+int llmss_symm_destroy(llmss_symm_t* ws);
+int llmss_symm_epoch(llmss_symm_t* ws, uint32_t* out_host);
+
+/* ---- K4 collectives over NVLink peer memory (N1/N2: layers.py:178,213; N3: layers.py:133) ---- */
+int llmss_allreduce(llmss_symm_t* ws, const void* in, void* out, int64_t n, int dtype, int algo,
+                    llmss_stream_t stream);
+int llmss_allgather(llmss_symm_t* ws, const void* in, void* out, int64_t bytes, llmss_stream_t stream);
+
+/* ---- K5/K1/K2 tcgen05 GEMM (+ fused all-reduce epilogue) (G3,G4,G9,G10,G12,G14; layers.py:62,175-179) ---- */
+typedef struct llmss_gemm_plan {
+  int bn, tiles, kb_total, grid;
+  int64_t sk_ws_floats;
+  int64_t sk_counters;
+  int64_t ar_bytes;
+} llmss_gemm_plan;
+int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p);
+int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias, const void* residual,
+               int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype, int out_f32, int act,
+               int act_start, int gated, float* sk_ws, uint32_t* sk_counters, llmss_symm_t* ws, int max_ctas,
+               llmss_stream_t stream);
+
+/* ---- K6 fused residual add + LayerNorm / RMSNorm (G2, G13, G18; layers.py:12-36,217-256) ---- */
+int llmss_norm_residual(const void* x, const void* x2, const void* residual_in, void* residual_out,
+                        const void* weight, const void* bias, void* out, int M, int H, int64_t ldx, int64_t ldx2,
+                        int64_t ldr, int64_t ldo, float eps, int kind, int dtype, llmss_stream_t stream);
+
+/* ---- K7 RoPE + paged KV-cache append (G5, G6; gptj_modeling.py:26-47,206-233) ---- */
+int llmss_rope_kv_write(void* qkv, const int* positions, const int* slot_mapping, void* k_cache, void* v_cache,
+                        int T, int64_t ld, int hq, int hkv, int d, int rotary_dim, int style, float base, int q_off,
+                        int k_off, int v_off, int block_size, int dtype, llmss_stream_t stream);
+
+/* ---- K9 paged split-KV decode attention (G7, G8, G17; gptj_modeling.py:128-169) ---- */
+int64_t llmss_attn_decode_scratch_floats(int B, int hq, int d, int num_splits);
+int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                      const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
+                      float* scratch, int B, int hq, int hkv, int d, int block_size, float scale, int num_splits,
+                      int dtype, llmss_stream_t stream);
+
+/* ---- K10 embedding gather (G1; layers.py:182-214) ---- */
+int llmss_embed(const int* tokens, const int* positions, const void* wte, const void* wpe, void* out, int T, int H,
+                int vocab, int max_pos, int pos_offset, int64_t ldo, int dtype, llmss_stream_t stream);
+
+/* ---- K11 fused sampler (G15, G16, N6; generate.py:109-144) ---- */
+int llmss_sample(const float* logits, int64_t ld, int B, int vocab, const int* greedy, const float* temperature,
+                 const int* top_k, const float* top_p, uint32_t* rng_state, int* out_tokens,
+                 long long* out_tokens64, llmss_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLMSS_B200_H_ */

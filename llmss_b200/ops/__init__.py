@@ -1,0 +1,125 @@
+"""Op front door: CPU tensors run the fp32 PyTorch oracles (ops.reference), CUDA tensors run
+the hand-written sm_100a kernels (ops.cuda_impl -> libllmss_b200.so).  There is no silent
+fallback on CUDA: a missing library or an unsupported shape raises.
+
+The only library (non-hand-written) kernel still reachable on the CUDA path is the
+``generic`` attention fallback used for prefill-with-prior-context (chunked prefill /
+HF-compat forward with a multi-token query and a non-empty cache); see attention().
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import reference as ref
+from .reference import (ACT_GELU_ERF, ACT_GELU_TANH, ACT_IDS, ACT_NONE, ACT_RELU, ACT_SILU, NORM_LAYER, NORM_RMS,
+                        ROPE_GPTJ, ROPE_NEOX, ROPE_NONE)
+
+
+def _cuda(t: torch.Tensor) -> bool:
+    return t.is_cuda
+
+
+def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start: int = 0, residual=None,
+           out_dtype=None, comm=None):
+    """y = epilogue(x @ w.T); with ``comm`` the product is summed over the TP group first
+    (row-parallel layer: reference `TensorParallelRowLinear.forward`, layers.py:175-179) and
+    bias/residual are applied once after the reduction."""
+    reduce = comm is not None and not comm.single
+    if _cuda(x):
+        from . import cuda_impl as cu
+
+        if not reduce:
+            return cu.linear(x, w, bias, act, gated, act_start, residual, out_dtype)
+        symm = comm.symm
+        if symm is not None:
+            plan = cu.gemm_plan(x.shape[0], w.shape[0], x.shape[1], symm.nranks)
+            if plan.ar_bytes <= symm.buf_bytes and plan.tiles <= 2048:
+                return cu.linear(x, w, bias, ACT_NONE, False, 0, residual, None, symm=symm)
+        y = cu.linear(x, w, None, ACT_NONE, False, 0, None, None)
+        comm.all_reduce(y)
+        if bias is not None:
+            y = y + bias
+        if residual is not None:
+            y = y + residual
+        return y
+    if not reduce:
+        return ref.linear(x, w, bias, act, gated, act_start, residual, out_dtype)
+    y = ref.linear(x, w, None, ACT_NONE, False, 0, None, torch.float32)
+    comm.all_reduce(y)
+    if bias is not None:
+        y = y + bias.float()
+    if residual is not None:
+        y = y + residual.float()
+    return y.to(out_dtype or x.dtype)
+
+
+def norm_residual(x, residual, weight, bias, eps: float, kind: int, x2=None):
+    """Returns (norm(x [+x2] [+residual]), the pre-norm sum)."""
+    if _cuda(x):
+        from . import cuda_impl as cu
+
+        return cu.norm_residual(x, residual, weight, bias, eps, kind, x2=x2)
+    if x2 is not None:
+        x = (x.float() + x2.float()).to(x.dtype)
+    return ref.norm_residual(x, residual, weight, bias, eps, kind)
+
+
+def rope_kv_write(qkv, positions, slot_mapping, k_cache, v_cache, hq, hkv, d, rotary_dim, style, base,
+                  q_off, k_off, v_off):
+    if _cuda(qkv):
+        from . import cuda_impl as cu
+
+        return cu.rope_kv_write(qkv, positions, slot_mapping, k_cache, v_cache, hq, hkv, d, rotary_dim, style, base,
+                                q_off, k_off, v_off)
+    return ref.rope_kv_write(qkv, positions, slot_mapping, k_cache, v_cache, hq, hkv, d, rotary_dim, style, base,
+                             q_off, k_off, v_off)
+
+
+def attention(qkv, out, batch, k_cache, v_cache, hq, hkv, d, scale, q_off, k_off, v_off, out_off=0):
+    """Causal attention for a packed batch; writes ``out[:, out_off : out_off + hq*d]``.
+
+    decode batches (one query per sequence) -> split-KV paged kernel (K9);
+    fresh prefill (no prior context)        -> varlen causal prefill kernel (K8);
+    anything else                           -> generic gather path (oracle math).
+    """
+    T = qkv.shape[0]
+    q_view = qkv[:, q_off:q_off + hq * d]
+    out_view = out[:, out_off:out_off + hq * d]
+    if _cuda(qkv):
+        from . import cuda_impl as cu
+
+        if batch.is_decode:
+            splits = batch.decode_splits or cu.decode_splits(batch.num_seqs, hkv, 1, batch.max_kv)
+            cu.attn_decode(q_view, k_cache, v_cache, batch.block_tables, batch.seq_lens, out_view, hq, hkv, d, scale,
+                           splits)
+            return out
+        if batch.is_fresh_prefill and cu._lib.has("llmss_attn_prefill") and d in (64, 128, 256):
+            cu.attn_prefill(q_view, qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d], out_view,
+                            batch.cu_q, batch.num_seqs, batch.max_q, hq, hkv, d, scale)
+            return out
+    o = ref.attention_paged(q_view.reshape(T, hq, d), k_cache, v_cache, batch.block_tables, batch.seq_lens,
+                            batch.cu_q, scale)
+    out_view.copy_(o.reshape(T, hq * d))
+    return out
+
+
+def embed(tokens, wte, positions=None, wpe=None, pos_offset: int = 0):
+    if _cuda(wte):
+        from . import cuda_impl as cu
+
+        return cu.embed(tokens, wte, positions, wpe, pos_offset)
+    return ref.embed(tokens, wte, positions, wpe, pos_offset)
+
+
+def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab: Optional[int] = None, out=None):
+    if _cuda(logits):
+        from . import cuda_impl as cu
+
+        return cu.sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab, out)
+    tok = ref.sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab).to(torch.int32)
+    if out is not None:
+        out.copy_(tok)
+        return out
+    return tok

@@ -1,0 +1,187 @@
+"""CUDA execution path: thin wrappers that hand torch tensors to the sm_100a kernels.
+
+All launches use torch's current stream, so they are captured by ``torch.cuda.graph``.
+Outputs are allocated with torch (graph-pool friendly); scratch for stream-K / split-KV is
+a per-device arena allocated once.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .reference import ACT_NONE
+
+_DT = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _count(n: int = 1):
+    _lib.LAUNCHES["count"] += n
+
+
+class _Arena:
+    """Per-device scratch: stream-K partials + tile counters + split-KV partials."""
+
+    SK_FLOATS = 2 * 148 * 128 * 256
+    SK_COUNTERS = 1 << 16
+
+    def __init__(self, device):
+        self.sk_ws = torch.empty(self.SK_FLOATS, dtype=torch.float32, device=device)
+        self.sk_counters = torch.zeros(self.SK_COUNTERS, dtype=torch.int32, device=device)
+        self.attn = None
+
+    def attn_scratch(self, nfloats: int, device):
+        if self.attn is None or self.attn.numel() < nfloats:
+            self.attn = torch.empty(max(nfloats, 1 << 20), dtype=torch.float32, device=device)
+        return self.attn
+
+
+_ARENAS = {}
+
+
+def arena(device) -> _Arena:
+    key = torch.device(device).index or 0
+    a = _ARENAS.get(key)
+    if a is None:
+        a = _ARENAS[key] = _Arena(device)
+    return a
+
+
+def _rows2d(x: torch.Tensor):
+    assert x.dim() == 2 and x.stride(1) == 1, "expected a 2-D tensor with contiguous last dim"
+    return x.shape[0], x.shape[1], x.stride(0)
+
+
+# --------------------------------------------------------------------------- GEMM
+def gemm_plan(M: int, N: int, K: int, nranks: int = 1, max_ctas: int = 0) -> _lib.GemmPlan:
+    p = _lib.GemmPlan()
+    _lib.check(_lib.load().llmss_gemm_plan_query(M, N, K, nranks, 2, max_ctas, C.byref(p)), "gemm_plan_query")
+    return p
+
+
+def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start: int = 0, residual=None,
+           out_dtype=None, symm=None, out=None, max_ctas: int = 0):
+    lib = _lib.load()
+    M, K, ldx = _rows2d(x)
+    N, Kw, ldw = _rows2d(w)
+    assert K == Kw, f"linear: x has K={K}, w has K={Kw}"
+    assert x.dtype == w.dtype and x.dtype in (torch.float16, torch.bfloat16)
+    out_f32 = 1 if out_dtype == torch.float32 else 0
+    n_out = N // 2 if gated else N
+    if out is None:
+        out = torch.empty(M, n_out, dtype=torch.float32 if out_f32 else x.dtype, device=x.device)
+    if M == 0:
+        return out
+    ldr = residual.stride(0) if residual is not None else 0
+    ar = symm is not None and symm.nranks > 1
+    a = arena(x.device)
+    rc = lib.llmss_gemm(_ptr(x), ldx, _ptr(w), ldw, _ptr(bias), _ptr(residual), ldr, _ptr(out), out.stride(0),
+                        M, N, K, _DT[x.dtype], out_f32, act, act_start, 1 if gated else 0,
+                        _ptr(a.sk_ws), _ptr(a.sk_counters), symm.handle if ar else None, max_ctas, _stream())
+    _lib.check(rc, "llmss_gemm")
+    _count()
+    return out
+
+
+# --------------------------------------------------------------------------- norm
+def norm_residual(x, residual, weight, bias, eps: float, kind: int, x2=None, write_residual: bool = True):
+    lib = _lib.load()
+    M, H, ldx = _rows2d(x)
+    out = torch.empty(M, H, dtype=x.dtype, device=x.device)
+    need_res = write_residual and (residual is not None or x2 is not None)
+    new_res = torch.empty(M, H, dtype=x.dtype, device=x.device) if need_res else None
+    # the kernel uses one stride for residual in and out
+    if residual is not None and new_res is not None and residual.stride(0) != new_res.stride(0):
+        residual = residual.contiguous()
+    ldr = new_res.stride(0) if new_res is not None else (residual.stride(0) if residual is not None else H)
+    rc = lib.llmss_norm_residual(_ptr(x), _ptr(x2), _ptr(residual), _ptr(new_res), _ptr(weight), _ptr(bias), _ptr(out),
+                                 M, H, ldx, x2.stride(0) if x2 is not None else H, ldr, out.stride(0), eps, kind,
+                                 _DT[x.dtype], _stream())
+    _lib.check(rc, "llmss_norm_residual")
+    _count()
+    return out, (new_res if new_res is not None else x)
+
+
+# --------------------------------------------------------------------------- rope + kv
+def rope_kv_write(qkv, positions, slot_mapping, k_cache, v_cache, hq, hkv, d, rotary_dim, style, base,
+                  q_off, k_off, v_off):
+    lib = _lib.load()
+    T, _, ld = _rows2d(qkv)
+    bs = k_cache.shape[2]
+    rc = lib.llmss_rope_kv_write(_ptr(qkv), _ptr(positions), _ptr(slot_mapping), _ptr(k_cache), _ptr(v_cache), T, ld,
+                                 hq, hkv, d, rotary_dim, style, float(base), q_off, k_off, v_off, bs, _DT[qkv.dtype],
+                                 _stream())
+    _lib.check(rc, "llmss_rope_kv_write")
+    _count()
+
+
+# --------------------------------------------------------------------------- attention
+def decode_splits(B: int, hkv: int, g_tiles: int, max_kv: int) -> int:
+    """Split-KV factor: enough CTAs for ~2 waves of 148 SMs x 4 resident CTAs, >= 256 tokens per split."""
+    ctas = max(1, B * hkv * g_tiles)
+    want = max(1, (148 * 4) // ctas)
+    by_len = max(1, max_kv // 256)
+    return int(max(1, min(want, by_len, 32)))
+
+
+def attn_decode(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, hq, hkv, d, scale, num_splits):
+    lib = _lib.load()
+    B = q_view.shape[0]
+    bs = k_cache.shape[2]
+    scratch = None
+    if num_splits > 1:
+        n = lib.llmss_attn_decode_scratch_floats(B, hq, d, num_splits)
+        scratch = arena(q_view.device).attn_scratch(n, q_view.device)
+    rc = lib.llmss_attn_decode(_ptr(q_view), q_view.stride(0), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables),
+                               block_tables.shape[1], _ptr(seq_lens), _ptr(out_view), out_view.stride(0),
+                               _ptr(scratch), B, hq, hkv, d, bs, float(scale), num_splits, _DT[q_view.dtype],
+                               _stream())
+    _lib.check(rc, "llmss_attn_decode")
+    _count(2 if num_splits > 1 else 1)
+
+
+def attn_prefill(q, k, v, out, cu_seqlens, num_seqs, max_seqlen, hq, hkv, d, scale):
+    lib = _lib.load()
+    rc = lib.llmss_attn_prefill(_ptr(q), q.stride(0), _ptr(k), k.stride(0), _ptr(v), v.stride(0), _ptr(out),
+                                out.stride(0), _ptr(cu_seqlens), num_seqs, max_seqlen, hq, hkv, d, float(scale),
+                                _DT[q.dtype], _stream())
+    _lib.check(rc, "llmss_attn_prefill")
+    _count()
+
+
+# --------------------------------------------------------------------------- embed / sample
+def embed(tokens, wte, positions=None, wpe=None, pos_offset: int = 0):
+    lib = _lib.load()
+    T = tokens.numel()
+    V, H = wte.shape
+    out = torch.empty(T, H, dtype=wte.dtype, device=wte.device)
+    rc = lib.llmss_embed(_ptr(tokens), _ptr(positions), _ptr(wte), _ptr(wpe), _ptr(out), T, H, V,
+                         wpe.shape[0] if wpe is not None else 0, pos_offset, out.stride(0), _DT[wte.dtype], _stream())
+    _lib.check(rc, "llmss_embed")
+    _count()
+    return out
+
+
+def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab=None, out=None):
+    lib = _lib.load()
+    B, Vp = logits.shape
+    assert logits.dtype == torch.float32 and logits.stride(1) == 1
+    if out is None:
+        out = torch.empty(B, dtype=torch.int32, device=logits.device)
+    o32 = _ptr(out) if out.dtype == torch.int32 else None
+    o64 = _ptr(out) if out.dtype == torch.int64 else None
+    rc = lib.llmss_sample(_ptr(logits), logits.stride(0), B, vocab or Vp, _ptr(greedy), _ptr(temperature), _ptr(top_k),
+                          _ptr(top_p), _ptr(rng_state), o32, o64, _stream())
+    _lib.check(rc, "llmss_sample")
+    _count()
+    return out

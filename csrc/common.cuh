@@ -127,7 +127,7 @@ struct SpinGuard {
     return true;
   }
 };
-__device__ __noinline__ void spin_timeout_trap(const char* what, int a, int b) {
+static __device__ __noinline__ void spin_timeout_trap(const char* what, int a, int b) {
   printf("[llmss_b200] device watchdog: %s timed out (block %d,%d,%d thread %d; %d %d)\n", what,
          blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, a, b);
   __trap();
@@ -244,6 +244,12 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
         "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr)
       : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(

@@ -48,8 +48,6 @@ struct Cfg {
   static constexpr int STAGES_RAW = (196 * 1024) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 12 ? 12 : STAGES_RAW;
   static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-  static constexpr int CH = (BN < 32) ? BN : 32;  // accumulator columns per epilogue chunk
-  static constexpr int NCH = BN / CH;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
 };
 
@@ -104,6 +102,11 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: 
 __device__ __forceinline__ float ld_cg_f32(const float* p) {
   float v;
   asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
 }
 __device__ __forceinline__ uint4 ld_cg_u4(const void* p) {
@@ -210,6 +213,9 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     }
   } else {
     // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
+    // The accumulator is consumed in groups of 8 token columns through *rolled* loops: the
+    // epilogue runs once per segment, so its code must stay small enough not to be
+    // instruction-fetch bound (a fully unrolled 256-column epilogue is ~20k SASS instructions).
     const int quarter = warp & 3;            // TMEM lane quarter this warp may access
     const int f = quarter * 32 + lane;       // feature within the tile
     const int epi_tid = threadIdx.x - 64;
@@ -219,80 +225,36 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     Segment sg;
     const T* bias = reinterpret_cast<const T*>(a.bias);
     const T* residual = reinterpret_cast<const T*>(a.residual);
-    constexpr int CH = C::CH, NCH = C::NCH;
+    constexpr int NG = BN / 8;               // column groups per tile
     int seg_idx = -1;
-    constexpr int VPC = CH * (int)sizeof(T) / 16;  // 16-byte vectors per chunk per thread (AR exchange)
     const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
+    const int par = epoch & 1;
 
     while (it.next(sg)) {
       ++seg_idx;
       const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
       const int n = tn * BM + f;
       const int m0 = tm * BN;
+      const bool n_ok = n < a.N;
       const bool full_tile = (sg.kb0 == 0 && sg.kb1 == a.kb_total);
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN);
+      const float bval = (bias != nullptr && n_ok) ? to_f32(bias[n]) : 0.f;
 
       mbar_wait(&tfull_bar[as], aphase, 30);
       tcgen05_fence_after();
 
-      // ---- final-value consumers -------------------------------------------------
-      auto store_chunk = [&](const float (&v)[CH], int c) {
-        // bias / activation / gating / residual, then transposed store out[m][n]
-        const float b = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-#pragma unroll
-        for (int j = 0; j < CH; ++j) {
-          const int m = m0 + c * CH + j;
-          float y = v[j] + b;
-          if (a.gated) {
-            const float other = __shfl_xor_sync(0xffffffffu, y, 1);
-            if ((lane & 1) == 0 && m < a.M && n < a.N) {
-              float r = act_apply(y, a.act) * other;
-              const int64_t o = (int64_t)m * a.ldo + (n >> 1);
-              if (residual != nullptr) r += to_f32(residual[(int64_t)m * a.ldr + (n >> 1)]);
-              if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = r;
-              else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(r);
-            }
-          } else if (m < a.M && n < a.N) {
-            if (a.act != LLMSS_ACT_NONE && n >= a.act_start) y = act_apply(y, a.act);
-            if (residual != nullptr) y += to_f32(residual[(int64_t)m * a.ldr + n]);
-            const int64_t o = (int64_t)m * a.ldo + n;
-            if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = y;
-            else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(y);
-          }
-        }
-      };
-      auto push_chunk = [&](const float (&v)[CH], int c, int par) {
-        // round to T and write the chunk into slot [rank] of every rank's exchange buffer
-        uint4 vec[VPC];
-#pragma unroll
-        for (int q = 0; q < VPC; ++q) {
-          float t8[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) t8[i] = v[q * 8 + i];
-          vec[q] = pack8<T>(t8);
-        }
-        const size_t off = (size_t)a.ws.rank * ar_slot_bytes + ((size_t)sg.tile * NCH + c) * (BM * CH * sizeof(T));
-#pragma unroll 1
-        for (int p = 0; p < a.ws.nranks; ++p) {
-          const int peer = (a.ws.rank + p) % a.ws.nranks;
-          uint4* dst = reinterpret_cast<uint4*>(symm_buf<uint8_t>(a.ws, peer, par) + off);
-#pragma unroll
-          for (int q = 0; q < VPC; ++q) dst[q * BM + f] = vec[q];
-        }
-      };
-
       bool have_final = full_tile;
       if (!full_tile) {
         // ---- stream-K: publish my partial, last arriver reduces ----
-        float* part = a.sk_ws + (size_t)(2 * g + (seg_idx > 0 ? 1 : 0)) * (BM * BN);
+        // partial layout [BN/4][128 features][4 cols]: one coalesced 16-byte store per 4 columns
+        float4* part = reinterpret_cast<float4*>(a.sk_ws + (size_t)(2 * g + (seg_idx > 0 ? 1 : 0)) * (BM * BN)) + f;
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
-          uint32_t r[CH];
-          if constexpr (CH == 32) tmem_ld_32x32b_x32(t_addr + c * CH, r);
-          else tmem_ld_32x32b_x16(t_addr + c * CH, *reinterpret_cast<uint32_t(*)[16]>(r));
+        for (int cg = 0; cg < NG; ++cg) {
+          uint32_t r[8];
+          tmem_ld_32x32b_x8(t_addr + cg * 8, r);
           tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < CH; ++j) part[(c * CH + j) * BM + f] = __uint_as_float(r[j]);
+          part[(cg * 2 + 0) * BM] = make_float4(__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3]));
+          part[(cg * 2 + 1) * BM] = make_float4(__uint_as_float(r[4]), __uint_as_float(r[5]), __uint_as_float(r[6]), __uint_as_float(r[7]));
         }
         tcgen05_fence_before();
         __syncwarp();
@@ -313,64 +275,123 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       }
 
       if (have_final) {
-        const int par = epoch & 1;
+        // slot of the first contributor: a tile is the *first* segment of every contributor
+        // except (possibly) the first one, whose range may start in an earlier tile
+        const int first_slot = 2 * sg.first_cta +
+            ((cta_start(sg.first_cta, it.total, G) != (int64_t)sg.tile * a.kb_total) ? 1 : 0);
+        // pass 0: produce the rank-local tile (from TMEM or from the stream-K partials) and either
+        //         store it (no AR) or push it to every rank's exchange buffer (AR);
+        // pass 1: (AR only) after the per-tile handshake, sum the ranks' tiles and store.
+        const int n_pass = a.ar ? 2 : 1;
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
-          float v[CH];
-          if (full_tile) {
-            uint32_t r[CH];
-            if constexpr (CH == 32) tmem_ld_32x32b_x32(t_addr + c * CH, r);
-            else tmem_ld_32x32b_x16(t_addr + c * CH, *reinterpret_cast<uint32_t(*)[16]>(r));
-            tmem_ld_wait();
+        for (int pass = 0; pass < n_pass; ++pass) {
+          if (pass == 1) {
+            if (full_tile) {
+              tcgen05_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            }
+            __threadfence_system();
+            epi_bar();
+            if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
+              st_release_sys(symm_flag(a.ws, epi_tid, 0, sg.tile) + a.ws.rank, epoch);
+            if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
+              wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, sg.tile) + epi_tid, epoch, 31);
+            epi_bar();
+          }
+#pragma unroll 1
+          for (int cg = 0; cg < NG; ++cg) {
+            float v[8];
+            const size_t xoff = ((size_t)sg.tile * NG + cg) * (BM * 16) + (size_t)f * 16;  // exchange-buffer offset
+            if (pass == 0) {
+              if (full_tile) {
+                uint32_t r[8];
+                tmem_ld_32x32b_x8(t_addr + cg * 8, r);
+                tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < CH; ++j) v[j] = __uint_as_float(r[j]);
-          } else {
+                for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]);
+              } else {
 #pragma unroll
-            for (int j = 0; j < CH; ++j) v[j] = 0.f;
-            for (int cta = sg.first_cta; cta <= sg.last_cta; ++cta) {  // fixed order: deterministic
-              // a tile is the *first* segment of every contributor except (possibly) its first one
-              const int slot = 2 * cta + ((cta == sg.first_cta && cta_start(cta, it.total, G) != (int64_t)sg.tile * a.kb_total) ? 1 : 0);
-              const float* p = a.sk_ws + (size_t)slot * (BM * BN);
+                for (int j = 0; j < 8; ++j) v[j] = 0.f;
+                // contributors are summed in CTA order (deterministic); four are fetched per
+                // round trip so the L2 latency is paid once per 4 contributors, not once each
+                for (int c0 = sg.first_cta; c0 <= sg.last_cta; c0 += 4) {
+                  float4 t[4][2];
 #pragma unroll
-              for (int j = 0; j < CH; ++j) v[j] += ld_cg_f32(p + (c * CH + j) * BM + f);
+                  for (int u = 0; u < 4; ++u) {
+                    const int cta = c0 + u;
+                    if (cta <= sg.last_cta) {
+                      const int slot = (cta == sg.first_cta) ? first_slot : 2 * cta;
+                      const float4* p = reinterpret_cast<const float4*>(a.sk_ws + (size_t)slot * (BM * BN)) + f;
+                      t[u][0] = ld_cg_f4(p + (cg * 2 + 0) * BM);
+                      t[u][1] = ld_cg_f4(p + (cg * 2 + 1) * BM);
+                    } else {
+                      t[u][0] = t[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                  }
+#pragma unroll
+                  for (int u = 0; u < 4; ++u) {
+                    v[0] += t[u][0].x; v[1] += t[u][0].y; v[2] += t[u][0].z; v[3] += t[u][0].w;
+                    v[4] += t[u][1].x; v[5] += t[u][1].y; v[6] += t[u][1].z; v[7] += t[u][1].w;
+                  }
+                }
+              }
+              if (a.ar) {
+                // round to T, one 16-byte vector per thread per group, tile-blocked + coalesced
+                const uint4 vec = pack8<T>(v);
+#pragma unroll 1
+                for (int p = 0; p < a.ws.nranks; ++p) {
+                  const int peer = (a.ws.rank + p) % a.ws.nranks;
+                  *reinterpret_cast<uint4*>(symm_buf<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                }
+                continue;
+              }
+            } else {
+              const uint8_t* mine = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = 0.f;
+              for (int r = 0; r < a.ws.nranks; ++r) {  // rank order: bit-identical on every rank
+                float t8[8];
+                unpack8<T>(ld_cg_u4(mine + (size_t)r * ar_slot_bytes + xoff), t8);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] += t8[j];
+              }
+            }
+            // ---- bias / activation / gating / residual, transposed store out[m][n] ----
+            const int mb = m0 + cg * 8;
+            if (a.gated) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float y = v[j] + bval;
+                const float other = __shfl_xor_sync(0xffffffffu, y, 1);
+                if ((lane & 1) == 0 && n_ok && mb + j < a.M) {
+                  float r = act_apply(y, a.act) * other;
+                  if (residual != nullptr) r += to_f32(residual[(int64_t)(mb + j) * a.ldr + (n >> 1)]);
+                  const int64_t o = (int64_t)(mb + j) * a.ldo + (n >> 1);
+                  if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = r;
+                  else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(r);
+                }
+              }
+            } else if (n_ok) {
+              const bool do_act = (a.act != LLMSS_ACT_NONE) && n >= a.act_start;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (mb + j < a.M) {
+                  float y = v[j] + bval;
+                  if (do_act) y = act_apply(y, a.act);
+                  if (residual != nullptr) y += to_f32(residual[(int64_t)(mb + j) * a.ldr + n]);
+                  const int64_t o = (int64_t)(mb + j) * a.ldo + n;
+                  if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = y;
+                  else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(y);
+                }
+              }
             }
           }
-          if (a.ar) push_chunk(v, c, par);
-          else store_chunk(v, c);
         }
-        if (full_tile) {
+        if (full_tile && !a.ar) {
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty_bar[as]);
-        }
-        if (a.ar) {
-          // ---- per-tile handshake with the peers, then rank-ordered sum ----
-          __threadfence_system();
-          epi_bar();
-          if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
-            st_release_sys(symm_flag(a.ws, epi_tid, 0, sg.tile) + a.ws.rank, epoch);
-          if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
-            wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, sg.tile) + epi_tid, epoch, 31);
-          epi_bar();
-          const uint8_t* mine = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
-#pragma unroll 1
-          for (int c = 0; c < NCH; ++c) {
-            float v[CH];
-#pragma unroll
-            for (int j = 0; j < CH; ++j) v[j] = 0.f;
-            for (int r = 0; r < a.ws.nranks; ++r) {
-              const uint4* src = reinterpret_cast<const uint4*>(
-                  mine + (size_t)r * ar_slot_bytes + ((size_t)sg.tile * NCH + c) * (BM * CH * sizeof(T)));
-#pragma unroll
-              for (int q = 0; q < VPC; ++q) {
-                float t8[8];
-                unpack8<T>(ld_cg_u4(src + q * BM + f), t8);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[q * 8 + i] += t8[i];
-              }
-            }
-            store_chunk(v, c);
-          }
         }
       }
       if (++as == 2) { as = 0; aphase ^= 1; }

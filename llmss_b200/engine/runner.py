@@ -1,0 +1,318 @@
+"""ModelRunner: executes packed prefill batches and CUDA-graph-captured decode steps.
+
+Design points vs. the reference loop (generate.py:102-145, consumer_server.py:123-166):
+  * the KV cache is pre-allocated and paged; nothing is concatenated or re-allocated per token;
+  * a decode step is ONE CUDA graph replay (all layers, fused collectives, LM head, sampler);
+    the reference launches ~20 kernels + 2 NCCL ops per layer from Python every token;
+  * every rank samples identically on-device (same logits, same counter RNG), so there is no
+    per-token broadcast from rank 0 (reference N6/N10) and no device sync per token (Q13);
+  * the per-step host inputs live in ONE pinned staging buffer -> one H2D copy per step, and the
+    sampled tokens come back with one D2H copy.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import ops
+from ..models.decoder import DecoderLM
+from .batch import BatchInput
+from .kv_cache import BlockAllocator, KVCache
+
+_BUCKETS = (1, 2, 4, 8, 16, 24, 32, 48, 64, 96, 128, 192, 256)
+
+
+@dataclass
+class SamplingParams:
+    """Per-request sampling controls; same fields and defaults as the reference CLI
+    (generate.py:25-31) and HTTP schema (producer_server.py:9-15)."""
+    max_new_tokens: int = 20
+    is_greedy: bool = False
+    temperature: float = 1.0
+    top_p: float = 0.95
+    top_k: int = 50
+    seed: int = 0
+
+    def validate(self):
+        assert self.max_new_tokens > 0, "Value of max_new_tokens should be over than 0."
+        assert 0.0 < self.temperature <= 1.0, "Value of temperature is not valid."
+        assert 0.0 < self.top_p <= 1.0, "Value of top_p is not valid."
+        assert self.top_k >= 0, "Value of top_k is not valid."
+        return self
+
+
+class SeqState:
+    __slots__ = ("seq_id", "prompt", "output", "blocks", "params", "length", "slot", "finished", "eos")
+
+    def __init__(self, seq_id, prompt, params, eos=None):
+        self.seq_id, self.prompt, self.params = seq_id, list(prompt), params
+        self.output: List[int] = []
+        self.blocks: List[int] = []
+        self.length = 0          # tokens whose KV is in the cache
+        self.slot = -1           # row in the decode batch
+        self.finished = False
+        self.eos = eos
+
+
+class ModelRunner:
+    def __init__(self, core: DecoderLM, max_batch: int = 64, max_seq_len: Optional[int] = None, block_size: int = 16,
+                 num_blocks: Optional[int] = None, use_cuda_graph: Optional[bool] = None):
+        self.core, self.spec = core, core.spec
+        self.device, self.dtype = core.device, core.dtype
+        self.max_batch = max_batch
+        self.max_seq_len = min(max_seq_len or self.spec.max_pos, self.spec.max_pos)
+        self.block_size = block_size
+        self.max_blocks_per_seq = -(-self.max_seq_len // block_size)
+        if num_blocks is None:
+            num_blocks = 1 + max_batch * self.max_blocks_per_seq
+        self.kv = KVCache(self.spec.n_layers, num_blocks, block_size, core.hkv, core.d, self.dtype, self.device)
+        self.alloc = BlockAllocator(num_blocks)
+        self.cuda = self.device.type == "cuda"
+        self.use_graph = self.cuda if use_cuda_graph is None else (use_cuda_graph and self.cuda)
+        self.graphs: Dict[int, torch.cuda.CUDAGraph] = {}
+        self.launches_per_graph: Dict[int, int] = {}   # own-kernel launches captured per decode graph
+        self.graph_pool = None
+        self._setup_static(max_batch)
+        self.stats = {"prefill_tokens": 0, "decode_steps": 0, "graph_replays": 0, "h2d_bytes": 0, "d2h_bytes": 0}
+
+    # ------------------------------------------------------------------ static step buffers
+    def _setup_static(self, B: int):
+        mb = self.max_blocks_per_seq
+        # ONE int32 staging buffer per direction: [tokens | positions | slots | seq_lens | block_tables].
+        # The token region doubles as the sampler output, so a step is one H2D and one D2H copy.
+        self.n_meta = 4 * B + B * mb
+        pin = self.cuda
+        self.h_in = torch.zeros(self.n_meta, dtype=torch.int32, pin_memory=pin)
+        self.d_in = torch.zeros(self.n_meta, dtype=torch.int32, device=self.device)
+        self.h_out = torch.zeros(B, dtype=torch.int32, pin_memory=pin)
+        self.np_in = self.h_in.numpy()
+        self.np_out = self.h_out.numpy()
+        self.np_tok, self.np_pos = self.np_in[0:B], self.np_in[B:2 * B]
+        self.np_slot, self.np_slen = self.np_in[2 * B:3 * B], self.np_in[3 * B:4 * B]
+        self.np_bt = self.np_in[4 * B:].reshape(B, mb)
+        self.np_len = np.zeros(B, dtype=np.int64)       # tokens already in the cache, per row
+        self.np_nblk = np.zeros(B, dtype=np.int64)      # blocks owned, per row
+        self.np_active = np.zeros(B, dtype=bool)
+        self.np_slot[:] = -1
+        self.d_in.copy_(self.h_in)
+        # sampler parameters (change only when the batch composition changes)
+        self.h_samp_i = torch.zeros(2 * B, dtype=torch.int32, pin_memory=pin)     # [greedy | top_k]
+        self.h_samp_f = torch.ones(2 * B, dtype=torch.float32, pin_memory=pin)    # [temperature | top_p]
+        self.h_samp_i[:B] = 1
+        self.d_samp_i = self.h_samp_i.to(self.device)
+        self.d_samp_f = self.h_samp_f.to(self.device)
+        self.d_rng = torch.zeros(B, 2, dtype=torch.int32, device=self.device)
+        self.d_last_idx = torch.arange(B, dtype=torch.int64, device=self.device)
+        self.d_cu = torch.arange(B + 1, dtype=torch.int32, device=self.device)
+        self.batch_seqs: List[SeqState] = []
+
+    def _dev_views(self, B: int):
+        buf, MB, mb = self.d_in, self.max_batch, self.max_blocks_per_seq
+        return (buf[0:B], buf[MB:MB + B], buf[2 * MB:2 * MB + B], buf[3 * MB:3 * MB + B],
+                buf[4 * MB:].view(MB, mb)[:B])
+
+    # ------------------------------------------------------------------ sequences
+    def blocks_needed(self, n_tokens: int) -> int:
+        return -(-n_tokens // self.block_size)
+
+    def can_admit(self, prompt_len: int, max_new: int) -> bool:
+        return self.alloc.num_free >= self.blocks_needed(min(prompt_len + max_new, self.max_seq_len))
+
+    def _grow(self, seq: SeqState, total_len: int):
+        need = self.blocks_needed(total_len) - len(seq.blocks)
+        if need > 0:
+            seq.blocks.extend(self.alloc.alloc(need))
+
+    def release(self, seq: SeqState):
+        self.alloc.release(seq.blocks)
+        seq.blocks = []
+
+    # ------------------------------------------------------------------ prefill
+    @torch.no_grad()
+    def prefill(self, seqs: Sequence[SeqState]) -> List[int]:
+        """Run the prompts of ``seqs`` (packed, no padding) and sample their first tokens."""
+        for s in seqs:
+            s.prompt = s.prompt[-(self.max_seq_len - 1):]  # left-truncate like the reference tokenizer call
+            self._grow(s, len(s.prompt))
+        batch = BatchInput.build([s.prompt for s in seqs], [0] * len(seqs), [s.blocks for s in seqs],
+                                 self.block_size, self.device, max_blocks=self.max_blocks_per_seq)
+        logits = self.core.forward(batch, self.kv, last_only=True)
+        B = len(seqs)
+        dev = self.device
+        greedy = torch.tensor([int(s.params.is_greedy) for s in seqs], dtype=torch.int32, device=dev)
+        temp = torch.tensor([s.params.temperature for s in seqs], dtype=torch.float32, device=dev)
+        top_k = torch.tensor([s.params.top_k for s in seqs], dtype=torch.int32, device=dev)
+        top_p = torch.tensor([s.params.top_p for s in seqs], dtype=torch.float32, device=dev)
+        rng = torch.tensor([[s.params.seed & 0x7FFFFFFF, 0] for s in seqs], dtype=torch.int32, device=dev)
+        toks = ops.sample(logits, greedy, temp, top_k, top_p, rng, vocab=self.spec.vocab).tolist()
+        for s, t in zip(seqs, toks):
+            s.length = len(s.prompt)
+            s.output.append(int(t))
+        self.stats["prefill_tokens"] += int(batch.tokens.numel())
+        return [int(t) for t in toks]
+
+    # ------------------------------------------------------------------ decode
+    def _bucket(self, B: int) -> int:
+        for b in _BUCKETS:
+            if b >= B and b <= self.max_batch:
+                return b
+        return self.max_batch
+
+    def set_batch(self, seqs: Sequence[SeqState]):
+        """(Re)bind the decode batch rows to sequences; uploads sampler parameters and block tables."""
+        B, MB = len(seqs), self.max_batch
+        assert B <= MB
+        self.batch_seqs = list(seqs)
+        self.h_samp_i[:MB] = 1
+        rng = torch.zeros(MB, 2, dtype=torch.int32)
+        self.np_in[:] = 0
+        self.np_slot[:] = -1
+        self.np_active[:] = False
+        self.np_len[:] = 0
+        self.np_nblk[:] = 0
+        for i, s in enumerate(seqs):
+            s.slot = i
+            self.h_samp_i[i] = int(s.params.is_greedy)
+            self.h_samp_i[MB + i] = s.params.top_k
+            self.h_samp_f[i] = s.params.temperature
+            self.h_samp_f[MB + i] = s.params.top_p
+            rng[i, 0] = s.params.seed & 0x7FFFFFFF
+            rng[i, 1] = len(s.output)
+            self.np_active[i] = not s.finished
+            self.np_len[i] = s.length
+            self.np_nblk[i] = len(s.blocks)
+            self.np_bt[i, :len(s.blocks)] = s.blocks
+            if s.output:
+                self.np_tok[i] = s.output[-1]
+        self.d_samp_i.copy_(self.h_samp_i, non_blocking=True)
+        self.d_samp_f.copy_(self.h_samp_f, non_blocking=True)
+        self.d_rng.copy_(rng.to(self.device))
+
+    def deactivate(self, seq: SeqState):
+        """Stop generating for a bound row (its slot becomes padding until the next set_batch)."""
+        seq.finished = True
+        if 0 <= seq.slot < self.max_batch and seq.slot < len(self.batch_seqs) and self.batch_seqs[seq.slot] is seq:
+            self.np_active[seq.slot] = False
+
+    def _fill_step_inputs(self):
+        """Vectorised (numpy on the pinned buffer) metadata for this step of the bound batch."""
+        bs = self.block_size
+        act = self.np_active
+        pos = self.np_len
+        # rows that step onto a new cache block get one (every block_size steps per sequence)
+        need = act & (pos // bs >= self.np_nblk)
+        for i in np.nonzero(need)[0]:
+            s = self.batch_seqs[i]
+            self._grow(s, int(pos[i]) + 1)
+            self.np_bt[i, :len(s.blocks)] = s.blocks
+            self.np_nblk[i] = len(s.blocks)
+        rows = np.arange(self.max_batch)
+        blk = self.np_bt[rows, np.minimum(pos // bs, self.max_blocks_per_seq - 1)]
+        self.np_pos[:] = np.where(act, pos, 0)
+        self.np_slot[:] = np.where(act, blk * bs + pos % bs, -1)
+        self.np_slen[:] = np.where(act, pos + 1, 0)
+
+    def _decode_body(self, Bp: int, splits: int):
+        tok, pos, slot, slen, bt = self._dev_views(Bp)
+        MB = self.max_batch
+        batch = BatchInput(tokens=tok, positions=pos, slot_mapping=slot, block_tables=bt, seq_lens=slen,
+                           cu_q=self.d_cu[:Bp + 1], last_idx=self.d_last_idx[:Bp], num_seqs=Bp, max_q=1,
+                           max_kv=self.max_seq_len, is_decode=True, is_fresh_prefill=False, decode_splits=splits)
+        logits = self.core.forward(batch, self.kv, last_only=False)  # every row is a last token
+        # the sampler writes into the token region: it is both this step's result and the next
+        # step's input (device-side feedback loop; no host round trip needed between steps)
+        ops.sample(logits, self.d_samp_i[:Bp], self.d_samp_f[:Bp], self.d_samp_i[MB:MB + Bp],
+                   self.d_samp_f[MB:MB + Bp], self.d_rng[:Bp], vocab=self.spec.vocab, out=tok)
+
+    def _splits_for(self, Bp: int) -> int:
+        if not self.cuda:
+            return 1
+        from ..ops import cuda_impl as cu
+
+        return cu.decode_splits(Bp, self.core.hkv, 1, self.max_seq_len)
+
+    def capture(self, Bp: int):
+        """Warm up and capture the decode graph for a padded batch size, on inert inputs
+        (slot -1, seq_len 0: no cache writes), then restore the live step state."""
+        if not self.use_graph or Bp in self.graphs:
+            return
+        splits = self._splits_for(Bp)
+        saved_in, saved_rng = self.d_in.clone(), self.d_rng.clone()
+        inert = torch.zeros_like(self.h_in)
+        MB = self.max_batch
+        inert[2 * MB:3 * MB] = -1
+        self.d_in.copy_(inert)
+        torch.cuda.synchronize()
+        self.core.comm.barrier()
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self._decode_body(Bp, splits)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.core.comm.barrier()
+        from ..ops import _lib
+
+        g = torch.cuda.CUDAGraph()
+        n0 = _lib.LAUNCHES["count"]
+        with torch.cuda.graph(g, pool=self.graph_pool):
+            self._decode_body(Bp, splits)
+        self.launches_per_graph[Bp] = _lib.LAUNCHES["count"] - n0
+        if self.graph_pool is None:
+            self.graph_pool = g.pool()
+        self.graphs[Bp] = g
+        self.d_in.copy_(saved_in)
+        self.d_rng.copy_(saved_rng)
+        torch.cuda.synchronize()
+
+    def _launch_decode(self, Bp: int):
+        if not self.use_graph:
+            self._decode_body(Bp, self._splits_for(Bp))
+            return
+        self.graphs[Bp].replay()
+        self.stats["graph_replays"] += 1
+
+    @torch.no_grad()
+    def decode_step(self, sync: bool = True, host_tokens: bool = True) -> Optional[List[int]]:
+        """One token for every bound sequence.
+
+        ``sync=True``: full host round trip (H2D of the step inputs from pinned memory, D2H of the
+        sampled tokens) -- the public serving path.  ``sync=False, host_tokens=False``: enqueue
+        only; tokens stay on the device and feed the next step (device-timed throughput)."""
+        B = len(self.batch_seqs)
+        Bp = self._bucket(B)
+        MB = self.max_batch
+        if self.use_graph and Bp not in self.graphs:
+            self.capture(Bp)
+        self._fill_step_inputs()
+        if host_tokens:
+            self.d_in.copy_(self.h_in, non_blocking=True)
+            self.stats["h2d_bytes"] += self.n_meta * 4
+        else:
+            self.d_in[MB:].copy_(self.h_in[MB:], non_blocking=True)
+            self.stats["h2d_bytes"] += (self.n_meta - MB) * 4
+        self._launch_decode(Bp)
+        self.stats["decode_steps"] += 1
+        self.np_len[self.np_active] += 1
+        if not sync:
+            return None
+        self.h_out[:Bp].copy_(self.d_in[:Bp], non_blocking=True)
+        self.stats["d2h_bytes"] += Bp * 4
+        if self.cuda:
+            torch.cuda.current_stream().synchronize()
+        toks = self.np_out[:B].tolist()
+        self.np_tok[:B] = self.np_out[:B]
+        for s, t, a in zip(self.batch_seqs, toks, self.np_active[:B].tolist()):
+            if a:
+                s.length += 1
+                s.output.append(t)
+        return toks
+
+    def sync_lengths(self):
+        """After a run of ``sync=False`` steps: bring the host-side SeqState lengths up to date."""
+        for i, s in enumerate(self.batch_seqs):
+            s.length = int(self.np_len[i])

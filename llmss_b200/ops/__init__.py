@@ -99,10 +99,30 @@ def attention(qkv, out, batch, k_cache, v_cache, hq, hkv, d, scale, q_off, k_off
             cu.attn_prefill(q_view, qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d], out_view,
                             batch.cu_q, batch.num_seqs, batch.max_q, hq, hkv, d, scale)
             return out
+        if batch.is_fresh_prefill:
+            # LIBRARY FALLBACK (torch SDPA), only reached when the own prefill kernel is absent from
+            # the loaded library or the head_dim is unsupported by it.
+            _sdpa_prefill(qkv, out_view, batch, hq, hkv, d, scale, q_off, k_off, v_off)
+            return out
     o = ref.attention_paged(q_view.reshape(T, hq, d), k_cache, v_cache, batch.block_tables, batch.seq_lens,
                             batch.cu_q, scale)
     out_view.copy_(o.reshape(T, hq * d))
     return out
+
+
+def _sdpa_prefill(qkv, out_view, batch, hq, hkv, d, scale, q_off, k_off, v_off):
+    import torch.nn.functional as F
+
+    cu = batch.cu_q.tolist()
+    for i in range(batch.num_seqs):
+        a, b = cu[i], cu[i + 1]
+        if b == a:
+            continue
+        q = qkv[a:b, q_off:q_off + hq * d].reshape(1, b - a, hq, d).transpose(1, 2)
+        k = qkv[a:b, k_off:k_off + hkv * d].reshape(1, b - a, hkv, d).transpose(1, 2)
+        v = qkv[a:b, v_off:v_off + hkv * d].reshape(1, b - a, hkv, d).transpose(1, 2)
+        o = F.scaled_dot_product_attention(q, k, v, is_causal=True, scale=scale, enable_gqa=(hq != hkv))
+        out_view[a:b] = o.transpose(1, 2).reshape(b - a, hq * d)
 
 
 def embed(tokens, wte, positions=None, wpe=None, pos_offset: int = 0):

@@ -65,7 +65,19 @@ def _compile(src: Path, verbose: bool) -> Path:
     return obj
 
 
+def tree_digest() -> str:
+    """Digest of everything that determines the library contents."""
+    return hashlib.sha256("".join(_digest(s) for s in sources()).encode()).hexdigest()[:24]
+
+
+def is_current() -> bool:
+    stamp = LIB_DIR / "build.stamp"
+    return LIB_PATH.exists() and stamp.exists() and stamp.read_text().strip() == tree_digest()
+
+
 def build_library(verbose: bool = False, force: bool = False) -> Path:
+    if not force and is_current():  # e.g. on the GPU box: the .so travelled with the tree
+        return LIB_PATH
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
     LIB_DIR.mkdir(parents=True, exist_ok=True)
     if force:
@@ -75,10 +87,8 @@ def build_library(verbose: bool = False, force: bool = False) -> Path:
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(lambda s: _compile(s, verbose), srcs))
     stamp = LIB_DIR / "build.stamp"
-    want = "\n".join(o.name for o in objs)
-    if LIB_PATH.exists() and stamp.exists() and stamp.read_text() == want and not force:
-        return LIB_PATH
-    cmd = [_nvcc(), "-shared", "-o", str(LIB_PATH), *map(str, objs), "-lcudart"]
+    want = tree_digest()
+    cmd = [_nvcc(), "-shared", "-o", str(LIB_PATH), *map(str, objs)]
     if verbose:
         print("[build]", " ".join(cmd), flush=True)
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -1,0 +1,19 @@
+"""Launch one GEMM shape a few times (for ncu).  usage: prof_gemm.py M N K [iters]"""
+import math
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from llmss_b200.ops import cuda_impl as cu
+
+M, N, K = (int(a) for a in sys.argv[1:4])
+iters = int(sys.argv[4]) if len(sys.argv) > 4 else 6
+ws = [torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / math.sqrt(K) for _ in range(3)]
+x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+for i in range(iters):
+    cu.linear(x, ws[i % 3], out=out)
+torch.cuda.synchronize()
+print("ok", cu.gemm_plan(M, N, K).grid)

@@ -1,0 +1,204 @@
+"""GPU numerics: every sm_100a kernel against the plain-PyTorch fp32 oracle of the same op."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from llmss_b200.ops import reference as R  # noqa: E402
+
+
+def _cu():
+    from llmss_b200.ops import cuda_impl
+
+    return cuda_impl
+
+
+def _close(a, b, atol, rtol, what=""):
+    a, b = a.float(), b.float()
+    err = (a - b).abs()
+    tol = atol + rtol * b.abs()
+    bad = (err > tol).sum().item()
+    assert bad == 0, f"{what}: {bad}/{a.numel()} mismatches, max err {err.max().item():.4g}"
+
+
+DT = [torch.bfloat16, torch.float16]
+
+
+def test_library_is_loaded():
+    from llmss_b200.ops import _lib
+
+    lib = _lib.load()
+    assert lib.llmss_version() >= 100
+    assert "libllmss_b200.so" in _lib.LOADED_FROM
+
+
+# ------------------------------------------------------------------ GEMM
+GEMM_SHAPES = [
+    # (M, N, K)   decode-like, stream-K splits, prefill-like, ragged edges
+    (1, 128, 64), (1, 4096, 4096), (8, 512, 1024), (16, 384, 256), (17, 256, 512), (32, 4096, 1024),
+    (64, 12288, 4096), (64, 4096, 2560), (100, 1000, 328), (128, 2048, 2048), (200, 768, 3072),
+    (256, 1024, 1024), (300, 640, 192), (1024, 4096, 4096), (4096, 512, 256),
+]
+
+
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_plain(M, N, K, dtype):
+    cu = _cu()
+    torch.manual_seed(M * 7 + N * 3 + K)
+    x = torch.randn(M, K, device="cuda", dtype=dtype)
+    w = torch.randn(N, K, device="cuda", dtype=dtype) / math.sqrt(K)
+    y = cu.linear(x, w)
+    torch.cuda.synchronize()
+    ref = R.linear(x, w, out_dtype=torch.float32)
+    _close(y, ref, 3e-2 if dtype == torch.bfloat16 else 6e-3, 2e-2, f"gemm {M}x{N}x{K}")
+
+
+def test_gemm_repeatable_and_counter_reset():
+    """stream-K counters must return to zero: the same launch twice gives identical bits."""
+    cu = _cu()
+    x = torch.randn(48, 4096, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(4096, 4096, device="cuda", dtype=torch.bfloat16) / 64
+    a = cu.linear(x, w).clone()
+    b = cu.linear(x, w).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    assert int(cu.arena(x.device).sk_counters.abs().sum().item()) == 0
+
+
+@pytest.mark.parametrize("act", ["gelu_new", "gelu", "relu", "silu"])
+def test_gemm_bias_act_residual(act):
+    cu = _cu()
+    M, N, K = 40, 1536, 512
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / math.sqrt(K)
+    b = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    res = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+    a = R.ACT_IDS[act]
+    y = cu.linear(x, w, b, act=a, residual=res)
+    _close(y, R.linear(x, w, b, act=a, residual=res, out_dtype=torch.float32), 4e-2, 2e-2, act)
+    y2 = cu.linear(x, w, b, act=a, act_start=512)
+    _close(y2, R.linear(x, w, b, act=a, act_start=512, out_dtype=torch.float32), 4e-2, 2e-2, act + " act_start")
+
+
+def test_gemm_gated_and_f32_out_and_strided_input():
+    cu = _cu()
+    M, N, K = 24, 1024, 768
+    big = torch.randn(M, K + 256, device="cuda", dtype=torch.float16)
+    x = big[:, 256:]  # row stride != K
+    w = torch.randn(N, K, device="cuda", dtype=torch.float16) / math.sqrt(K)
+    y = cu.linear(x, w, act=R.ACT_SILU, gated=True)
+    assert y.shape == (M, N // 2)
+    _close(y, R.linear(x, w, act=R.ACT_SILU, gated=True, out_dtype=torch.float32), 1e-2, 2e-2, "gated")
+    z = cu.linear(x, w, out_dtype=torch.float32)
+    assert z.dtype == torch.float32
+    _close(z, R.linear(x, w, out_dtype=torch.float32), 5e-3, 1e-2, "f32 out")
+
+
+# ------------------------------------------------------------------ norm
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("kind", [R.NORM_LAYER, R.NORM_RMS])
+@pytest.mark.parametrize("H", [768, 4096, 6144])
+def test_norm_residual(H, kind, dtype):
+    cu = _cu()
+    M = 37
+    x = torch.randn(M, H, device="cuda", dtype=dtype)
+    res = torch.randn(M, H, device="cuda", dtype=dtype)
+    x2 = torch.randn(M, H, device="cuda", dtype=dtype)
+    w = torch.randn(H, device="cuda", dtype=dtype)
+    b = torch.randn(H, device="cuda", dtype=dtype) if kind == R.NORM_LAYER else None
+    y, r = cu.norm_residual(x, res, w, b, 1e-5, kind, x2=x2)
+    s = (x.float() + x2.float() + res.float())
+    _close(r, s, 4e-2, 1e-2, "residual")
+    yr, _ = R.norm_residual(r, None, w, b, 1e-5, kind, out_dtype=torch.float32)
+    _close(y, yr, 5e-2, 2e-2, "normed")
+    y0, r0 = cu.norm_residual(x, None, w, b, 1e-5, kind)
+    assert r0 is x
+    _close(y0, R.norm_residual(x, None, w, b, 1e-5, kind, out_dtype=torch.float32)[0], 5e-2, 2e-2, "no residual")
+
+
+# ------------------------------------------------------------------ rope + kv write
+@pytest.mark.parametrize("style,d,rd", [(R.ROPE_GPTJ, 256, 64), (R.ROPE_NEOX, 128, 128), (R.ROPE_NONE, 64, 0),
+                                        (R.ROPE_GPTJ, 64, 64)])
+def test_rope_kv_write(style, d, rd):
+    cu = _cu()
+    T, hq, hkv, bs, nb = 19, 4, 2, 16, 12
+    W = (hq + 2 * hkv) * d + 64
+    qkv = torch.randn(T, W, device="cuda", dtype=torch.bfloat16)
+    pos = torch.randint(0, 3000, (T,), device="cuda", dtype=torch.int32)
+    slots = torch.randperm(nb * bs, device="cuda")[:T].to(torch.int32)
+    slots[3] = -1
+    kc = torch.zeros(nb, hkv, bs, d, device="cuda", dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    q_off, k_off, v_off = 64, 64 + hq * d, 64 + (hq + hkv) * d
+    ref_qkv, rk, rv = qkv.clone(), kc.clone(), vc.clone()
+    R.rope_kv_write(ref_qkv, pos, slots, rk, rv, hq, hkv, d, rd, style, 10000.0, q_off, k_off, v_off)
+    cu.rope_kv_write(qkv, pos, slots, kc, vc, hq, hkv, d, rd, style, 10000.0, q_off, k_off, v_off)
+    _close(qkv, ref_qkv, 3e-2, 2e-2, "qkv")
+    _close(kc, rk, 3e-2, 2e-2, "k cache")
+    _close(vc, rv, 0, 0, "v cache")
+
+
+# ------------------------------------------------------------------ decode attention
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("hq,hkv,d", [(4, 4, 256), (8, 8, 128), (12, 12, 64), (8, 2, 128), (6, 1, 128), (16, 1, 64)])
+@pytest.mark.parametrize("splits", [1, 4])
+def test_attn_decode(hq, hkv, d, splits, dtype):
+    cu = _cu()
+    torch.manual_seed(0)
+    B, bs = 5, 16
+    lens = [1, 17, 300, 64, 1025]
+    maxb = (max(lens) + bs - 1) // bs
+    nb = 1 + B * maxb
+    kc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=dtype)
+    vc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=dtype)
+    perm = (torch.randperm(nb - 1) + 1).tolist()
+    tables = [[perm[i * maxb + j] for j in range(maxb)] for i in range(B)]
+    bt = torch.tensor(tables, dtype=torch.int32, device="cuda")
+    sl = torch.tensor(lens, dtype=torch.int32, device="cuda")
+    W = hq * d + 128
+    qbuf = torch.randn(B, W, device="cuda", dtype=dtype)
+    out = torch.zeros(B, W, device="cuda", dtype=dtype)
+    q_view, o_view = qbuf[:, 128:], out[:, 128:]
+    cu.attn_decode(q_view, kc, vc, bt, sl, o_view, hq, hkv, d, d ** -0.5, splits)
+    cu_q = torch.arange(B + 1, dtype=torch.int32, device="cuda")
+    ref = R.attention_paged(q_view.reshape(B, hq, d), kc, vc, bt, sl, cu_q, d ** -0.5).reshape(B, hq * d)
+    _close(o_view, ref, 2e-2, 2e-2, "attn_decode")
+    assert out[:, :128].abs().sum().item() == 0
+
+
+# ------------------------------------------------------------------ embed / sample
+def test_embed():
+    cu = _cu()
+    V, H, P, T = 1000, 768, 128, 33
+    wte = torch.randn(V, H, device="cuda", dtype=torch.bfloat16)
+    wpe = torch.randn(P, H, device="cuda", dtype=torch.bfloat16)
+    tok = torch.randint(0, V, (T,), device="cuda", dtype=torch.int32)
+    pos = torch.randint(0, P - 2, (T,), device="cuda", dtype=torch.int32)
+    _close(cu.embed(tok, wte), R.embed(tok, wte), 0, 0, "wte")
+    _close(cu.embed(tok, wte, pos, wpe, 2), R.embed(tok, wte, pos, wpe, 2).float(), 2e-2, 1e-2, "wte+wpe")
+
+
+def test_sample_matches_oracle():
+    cu = _cu()
+    torch.manual_seed(3)
+    B, V = 16, 50400
+    logits = (torch.randn(B, V + 32, device="cuda") * 3).float()
+    greedy = torch.tensor([1, 0] * (B // 2), dtype=torch.int32, device="cuda")
+    temp = torch.tensor([1.0, 0.7, 1.0, 0.5] * (B // 4), device="cuda")
+    top_k = torch.tensor([50, 50, 0, 5, 0, 1000, 1, 0] * (B // 8), dtype=torch.int32, device="cuda")
+    top_p = torch.tensor([0.95, 0.95, 1.0, 0.5, 0.9, 1.0, 1.0, 1.0] * (B // 8), device="cuda")
+    for step in range(4):
+        rng = torch.tensor([[1234, step]] * B, dtype=torch.int32, device="cuda")
+        rng_ref = rng.clone()
+        got = cu.sample(logits, greedy, temp, top_k, top_p, rng, vocab=V)
+        want = R.sample(logits, greedy, temp, top_k, top_p, rng_ref, vocab=V)
+        torch.cuda.synchronize()
+        assert torch.equal(rng, rng_ref.to(rng.dtype))
+        agree = (got.long() == want.long()).float().mean().item()
+        assert agree >= 0.85, f"step {step}: only {agree:.2f} of rows agree\n{got}\n{want}"
+        g = greedy.bool()
+        assert torch.equal(got.long()[g], logits[g, :V].argmax(-1))
+        assert int(got.max()) < V

@@ -21,6 +21,17 @@ def _cuda(t: torch.Tensor) -> bool:
     return t.is_cuda
 
 
+_WARNED = set()
+
+
+def _warn_once(msg: str):
+    if msg not in _WARNED:
+        _WARNED.add(msg)
+        from ..utils.logging import logger
+
+        logger.warning(msg)
+
+
 def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start: int = 0, residual=None,
            out_dtype=None, comm=None):
     """y = epilogue(x @ w.T); with ``comm`` the product is summed over the TP group first
@@ -90,16 +101,18 @@ def attention(qkv, out, batch, k_cache, v_cache, hq, hkv, d, scale, q_off, k_off
     if _cuda(qkv):
         from . import cuda_impl as cu
 
-        if batch.is_decode:
+        if d not in (64, 128, 256):
+            _warn_once(f"head_dim={d} has no sm_100a attention kernel (64/128/256 do); using the generic PyTorch path")
+        elif batch.is_decode:
             splits = batch.decode_splits or cu.decode_splits(batch.num_seqs, hkv, 1, batch.max_kv)
             cu.attn_decode(q_view, k_cache, v_cache, batch.block_tables, batch.seq_lens, out_view, hq, hkv, d, scale,
                            splits)
             return out
-        if batch.is_fresh_prefill and cu._lib.has("llmss_attn_prefill") and d in (64, 128, 256):
+        elif batch.is_fresh_prefill and cu._lib.has("llmss_attn_prefill"):
             cu.attn_prefill(q_view, qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d], out_view,
                             batch.cu_q, batch.num_seqs, batch.max_q, hq, hkv, d, scale)
             return out
-        if batch.is_fresh_prefill:
+        elif batch.is_fresh_prefill:
             # LIBRARY FALLBACK (torch SDPA), only reached when the own prefill kernel is absent from
             # the loaded library or the head_dim is unsupported by it.
             _sdpa_prefill(qkv, out_view, batch, hq, hkv, d, scale, q_off, k_off, v_off)

@@ -25,7 +25,7 @@ def test_engine_gpu_matches_cpu_oracle(tmp_path, preset, fuse):
     assert gpu.runner.stats["graph_replays"] > 0
 
 
-@pytest.mark.parametrize("family", ["llama", "gpt_bigcode", "gpt2", "opt"])
+@pytest.mark.parametrize("family", ["llama", "gpt_bigcode", "gpt2", "opt", "gptj"])
 def test_families_gpu_logits_close_to_cpu(tmp_path, family):
     """Prefill + one decode step logits on GPU (own kernels) vs the CPU oracle for every family."""
     import sys
@@ -40,7 +40,7 @@ def test_families_gpu_logits_close_to_cpu(tmp_path, family):
     from llmss_b200.utils.weights import Weights
     from transformers import AutoConfig
 
-    cfg, _ = make_tiny(family, tmp_path)
+    cfg, _ = make_tiny(family, tmp_path, hidden=256)  # head_dim 64 -> own attention kernels
     conf = AutoConfig.from_pretrained(str(tmp_path))
 
     def load(device, dtype):

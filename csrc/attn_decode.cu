@@ -294,3 +294,78 @@ LLMSS_API int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache,
   }
 #undef LLMSS_D
 }
+
+// ---------------------------------------------------------------------------------------
+// llmss_attn_decode_static: the same split-KV decode attention, for callers that have no way
+// to give us scratch memory and must not trigger an allocation.
+//
+// Who that is: (a) a server that has already committed all of HBM to weights and KV-cache
+// pages, where one more cudaMalloc can fail or fragment the pool; (b) a latency-critical decode
+// loop, because cudaMalloc / cudaFree synchronise the whole device and would stall every stream;
+// (c) a plain C / C++ host (no torch allocator behind it) that only owns its input and output
+// buffers.  For them the split-KV partials live in a fixed array that is part of the library
+// image itself: every GPU that loads libllmss_b200.so carries these 8 MiB until the process
+// exits, whether or not this entry point is ever called.
+//
+// Rules of use:
+//   * Limit: B * hq * num_splits * (d + 2) floats must fit in kStaticScratchFloats (8 MiB);
+//     larger requests are refused with an error, nothing is launched.  num_splits == 1 needs no
+//     scratch and is always accepted.
+//   * The first call on each device looks up the array's device address (one
+//     cudaGetSymbolAddress, which may also make the driver load the module).  Make that first
+//     call during start-up, before any stream capture begins on that device.
+//   * All calls on a device share the one array and it keeps whatever the previous call left
+//     there.  Nothing in it has to start at zero: every slot the combine pass reads is written by
+//     the first pass of the same call (empty splits write m = -inf, l = 0), so no clearing is
+//     done.  Two calls whose kernels overlap on the GPU (different streams, or two host threads)
+//     race on the array and corrupt each other; serialise them on one stream.
+//   * No cudaMalloc, cudaFree, or allocating library routine is called on any path.
+// ---------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kStaticScratchFloats = (size_t)2 * 1024 * 1024;  // 8 MiB per GPU
+static __device__ __align__(256) float g_static_scratch[kStaticScratchFloats];
+
+constexpr int kMaxDevices = 64;
+float* g_static_scratch_addr[kMaxDevices] = {};  // host-side cache of the per-device address
+
+// The name `g_static_scratch` in host code is only a handle for the runtime, not a device
+// pointer; the usable address has to come from cudaGetSymbolAddress with the device current.
+int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  LLMSS_CHECK_CUDA(cudaGetDevice(&dev));
+  LLMSS_REQUIRE(dev >= 0 && dev < kMaxDevices, "attn_decode_static: device ordinal %d out of range", dev);
+  float* p = __atomic_load_n(&g_static_scratch_addr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    LLMSS_CHECK_CUDA(cudaGetSymbolAddress(&sym, g_static_scratch));
+    LLMSS_REQUIRE(sym != nullptr, "attn_decode_static: cudaGetSymbolAddress returned a null address");
+    p = static_cast<float*>(sym);
+    __atomic_store_n(&g_static_scratch_addr[dev], p, __ATOMIC_RELEASE);  // same value from any thread
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace
+
+LLMSS_API int64_t llmss_attn_decode_static_max_floats() { return (int64_t)kStaticScratchFloats; }
+
+LLMSS_API int llmss_attn_decode_static(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                                       const int* block_tables, int max_blocks, const int* seq_lens, void* out,
+                                       int64_t ldo, int B, int hq, int hkv, int d, int block_size, float scale,
+                                       int num_splits, int dtype, cudaStream_t stream) {
+  LLMSS_REQUIRE(B >= 0 && hq > 0 && d > 0 && num_splits >= 1, "attn_decode_static: bad sizes B=%d hq=%d d=%d splits=%d",
+                B, hq, d, num_splits);
+  const int64_t need = llmss_attn_decode_scratch_floats(B, hq, d, num_splits);
+  LLMSS_REQUIRE(need <= (int64_t)kStaticScratchFloats,
+                "attn_decode_static: B=%d x hq=%d x splits=%d x (d=%d + 2) = %lld floats of scratch exceed the built-in "
+                "%lld (8 MiB); lower num_splits or use llmss_attn_decode with caller-provided scratch",
+                B, hq, num_splits, d, (long long)need, (long long)kStaticScratchFloats);
+  float* scratch = nullptr;
+  if (num_splits > 1) {
+    if (int e = static_scratch_for_current_device(&scratch)) return e;
+  }
+  return llmss_attn_decode(q, ldq, k_cache, v_cache, block_tables, max_blocks, seq_lens, out, ldo, scratch, B, hq, hkv,
+                           d, block_size, scale, num_splits, dtype, stream);
+}

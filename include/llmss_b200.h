@@ -72,6 +72,20 @@ int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache, const voi
                       float* scratch, int B, int hq, int hkv, int d, int block_size, float scale, int num_splits,
                       int dtype, llmss_stream_t stream);
 
+/* No counterpart in the reference (it has no native code and allocates freely through torch).
+ * Same operation as llmss_attn_decode for hosts that cannot allocate: servers whose HBM is fully
+ * committed to weights + KV pages, decode loops that cannot afford the device-wide sync of
+ * cudaMalloc/cudaFree, and plain C hosts with no allocator to lend us scratch.  The split-KV
+ * partials live in an 8 MiB array built into the library (held by every GPU that loads it).
+ * Refuses B*hq*num_splits*(d+2) floats > llmss_attn_decode_static_max_floats().  The first call
+ * on a device resolves the array's address: make it at start-up, before any stream capture.
+ * Calls share the array; kernels of two calls that overlap on the GPU race. */
+int64_t llmss_attn_decode_static_max_floats(void);
+int llmss_attn_decode_static(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                             const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
+                             int B, int hq, int hkv, int d, int block_size, float scale, int num_splits, int dtype,
+                             llmss_stream_t stream);
+
 /* ---- K10 embedding gather (G1; layers.py:182-214) ---- */
 int llmss_embed(const int* tokens, const int* positions, const void* wte, const void* wpe, void* out, int T, int H,
                 int vocab, int max_pos, int pos_offset, int64_t ldo, int dtype, llmss_stream_t stream);

@@ -79,22 +79,31 @@ __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
   const int64_t head_stride = (int64_t)block_size * D;
   constexpr int TOK_PER_ITER = TPW * U;
 
-  for (int t0 = t_begin + warp * TOK_PER_ITER; t0 < t_end; t0 += kWarps * TOK_PER_ITER) {
-    uint4 kraw[U], vraw[U];
-    bool valid[U];
+  // Register double buffering: the loads of iteration i+1 are in flight while iteration i is
+  // reduced, so every lane keeps 2*U 16-byte requests outstanding for the whole stream.
+  auto issue = [&](int t0, uint4 (&kr)[U], uint4 (&vr)[U]) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int t = t0 + u * TPW + grp;
-      valid[u] = t < t_end;
-      kraw[u] = make_uint4(0, 0, 0, 0);
-      vraw[u] = make_uint4(0, 0, 0, 0);
-      if (valid[u]) {
+      kr[u] = make_uint4(0, 0, 0, 0);
+      vr[u] = make_uint4(0, 0, 0, 0);
+      if (t < t_end) {
         const int blk = __ldg(bt + t / block_size);
         const int64_t off = ((int64_t)blk * hkv + hk) * head_stride + (int64_t)(t % block_size) * D + lig * 8;
-        kraw[u] = ldg_stream(k_cache + off);
-        vraw[u] = ldg_stream(v_cache + off);
+        kr[u] = ldg_stream(k_cache + off);
+        vr[u] = ldg_stream(v_cache + off);
       }
     }
+  };
+  uint4 kraw[U], vraw[U], knext[U], vnext[U];
+  const int t_first = t_begin + warp * TOK_PER_ITER;
+  if (t_first < t_end) issue(t_first, kraw, vraw);
+  for (int t0 = t_first; t0 < t_end; t0 += kWarps * TOK_PER_ITER) {
+    const int t_nxt = t0 + kWarps * TOK_PER_ITER;
+    if (t_nxt < t_end) issue(t_nxt, knext, vnext);
+    bool valid[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) valid[u] = (t0 + u * TPW + grp) < t_end;
     float s[U][GT];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -144,6 +153,11 @@ __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
       for (int g = 0; g < GT; ++g)
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(s[u][g], vf[i], acc[g][i]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      kraw[u] = knext[u];
+      vraw[u] = vnext[u];
     }
   }
 
@@ -261,6 +275,42 @@ int dispatch_gt(int G, const void* q, int64_t ldq, const void* kc, const void* v
 }
 
 }  // namespace
+
+// Split-KV factor that fills whole waves: CTAs = B * hkv * g_tiles * splits should be close to (from
+// below) a multiple of the resident-CTA capacity, with >= 64 tokens per split.
+LLMSS_API int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int max_kv, int dtype) {
+  const int G = hq / (hkv > 0 ? hkv : 1);
+  const int GT = (G == 1) ? 1 : (G == 2) ? 2 : (d <= 128 ? 4 : 2);
+  const int items = B * hkv * ((G + GT - 1) / GT);
+  if (items <= 0) return 1;
+  int occ = 4, sms = 148, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+#define LLMSS_OCC(T_, D_, GT_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, attn_decode_kernel<T_, D_, GT_, 4>, kThreads, 0)
+  if (dtype == LLMSS_F16) {
+    if (d == 64) { if (GT == 1) LLMSS_OCC(__half, 64, 1); else if (GT == 2) LLMSS_OCC(__half, 64, 2); else LLMSS_OCC(__half, 64, 4); }
+    else if (d == 128) { if (GT == 1) LLMSS_OCC(__half, 128, 1); else if (GT == 2) LLMSS_OCC(__half, 128, 2); else LLMSS_OCC(__half, 128, 4); }
+    else { if (GT == 1) LLMSS_OCC(__half, 256, 1); else LLMSS_OCC(__half, 256, 2); }
+  } else {
+    if (d == 64) { if (GT == 1) LLMSS_OCC(__nv_bfloat16, 64, 1); else if (GT == 2) LLMSS_OCC(__nv_bfloat16, 64, 2); else LLMSS_OCC(__nv_bfloat16, 64, 4); }
+    else if (d == 128) { if (GT == 1) LLMSS_OCC(__nv_bfloat16, 128, 1); else if (GT == 2) LLMSS_OCC(__nv_bfloat16, 128, 2); else LLMSS_OCC(__nv_bfloat16, 128, 4); }
+    else { if (GT == 1) LLMSS_OCC(__nv_bfloat16, 256, 1); else LLMSS_OCC(__nv_bfloat16, 256, 2); }
+  }
+#undef LLMSS_OCC
+  if (occ < 1) occ = 1;
+  const double cap = (double)sms * occ;
+  const int max_s = max_kv / 64 > 1 ? (max_kv / 64 < 32 ? max_kv / 64 : 32) : 1;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int sp = 1; sp <= max_s; ++sp) {
+    const double waves = items * (double)sp / cap;
+    const double full = waves < 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
+    // small penalty per split for the partial write + combine pass
+    const double eff = waves / full - 0.004 * (sp - 1);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best = sp; }
+  }
+  return best;
+}
 
 // Scratch (floats) needed when num_splits > 1.
 LLMSS_API int64_t llmss_attn_decode_scratch_floats(int B, int hq, int d, int num_splits) {

@@ -16,6 +16,7 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
     T* __restrict__ qkv, const int* __restrict__ positions, const int* __restrict__ slot_mapping,
     T* __restrict__ k_cache, T* __restrict__ v_cache, int64_t ld, int hq, int hkv, int d, int rotary_dim,
     int style, float log2_base, int q_off, int k_off, int v_off, int block_size) {
+  __shared__ float s_cos[128], s_sin[128];  // rotary_dim / 2 <= 128 frequencies
   const int t = blockIdx.x;
   const float pos = (float)positions[t];
   const int slot = slot_mapping[t];
@@ -25,6 +26,14 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
   const int half = rotary_dim >> 1;
   const float inv_rd = 1.0f / (float)(rotary_dim > 0 ? rotary_dim : 1);
 
+  // cos/sin depend on (token, frequency) only: evaluate them once and share them across heads
+  if (style != LLMSS_ROPE_NONE) {
+    for (int i = threadIdx.x; i < half; i += blockDim.x) {
+      const float inv_freq = exp2f(-2.0f * (float)i * inv_rd * log2_base);
+      sincosf(pos * inv_freq, &s_sin[i], &s_cos[i]);
+    }
+    __syncthreads();
+  }
   int64_t cache_base = 0;
   if (slot >= 0) cache_base = ((int64_t)(slot / block_size) * hkv) * block_size * d + (int64_t)(slot % block_size) * d;
 
@@ -42,9 +51,7 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int pair = (c >> 1) + i;  // frequency index
-        float inv_freq = exp2f(-2.0f * (float)pair * inv_rd * log2_base);
-        float sn, cs;
-        sincosf(pos * inv_freq, &sn, &cs);
+        const float sn = s_sin[pair], cs = s_cos[pair];
         float x1 = f[2 * i], x2 = f[2 * i + 1];
         f[2 * i] = x1 * cs - x2 * sn;
         f[2 * i + 1] = x2 * cs + x1 * sn;
@@ -57,9 +64,7 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
         unpack8<T>(*reinterpret_cast<const uint4*>(p + half), g);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float inv_freq = exp2f(-2.0f * (float)(c + i) * inv_rd * log2_base);
-          float sn, cs;
-          sincosf(pos * inv_freq, &sn, &cs);
+          const float sn = s_sin[c + i], cs = s_cos[c + i];
           float x1 = f[i], x2 = g[i];
           f[i] = x1 * cs - x2 * sn;
           g[i] = x2 * cs + x1 * sn;
@@ -103,7 +108,7 @@ LLMSS_API int llmss_rope_kv_write(void* qkv, const int* positions, const int* sl
                                   cudaStream_t stream) {
   LLMSS_REQUIRE(d % 8 == 0 && ld % 8 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0,
                 "rope_kv_write: head_dim/offsets/stride must be multiples of 8");
-  LLMSS_REQUIRE(style == LLMSS_ROPE_NONE || (rotary_dim > 0 && rotary_dim <= d && rotary_dim % 16 == 0),
+  LLMSS_REQUIRE(style == LLMSS_ROPE_NONE || (rotary_dim > 0 && rotary_dim <= d && rotary_dim <= 256 && rotary_dim % 16 == 0),
                 "rope_kv_write: rotary_dim=%d must be a multiple of 16 and <= head_dim", rotary_dim);
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "rope_kv_write: dtype must be f16/bf16");
   if (T == 0) return 0;

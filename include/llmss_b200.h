@@ -67,6 +67,7 @@ int llmss_rope_kv_write(void* qkv, const int* positions, const int* slot_mapping
 
 /* ---- K9 paged split-KV decode attention (G7, G8, G17; gptj_modeling.py:128-169) ---- */
 int64_t llmss_attn_decode_scratch_floats(int B, int hq, int d, int num_splits);
+int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int max_kv, int dtype); /* wave-filling split factor */
 int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
                       const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
                       float* scratch, int B, int hq, int hkv, int d, int block_size, float scale, int num_splits,

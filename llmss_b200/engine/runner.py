@@ -232,7 +232,7 @@ class ModelRunner:
             return 1
         from ..ops import cuda_impl as cu
 
-        return cu.decode_splits(Bp, self.core.hkv, 1, self.max_seq_len)
+        return cu.decode_splits(Bp, self.core.hq, self.core.hkv, self.core.d, self.max_seq_len, self.dtype)
 
     def capture(self, Bp: int):
         """Warm up and capture the decode graph for a padded batch size, on inert inputs

@@ -39,10 +39,13 @@ class _Arena:
         self.sk_ws = torch.empty(self.SK_FLOATS, dtype=torch.float32, device=device)
         self.sk_counters = torch.zeros(self.SK_COUNTERS, dtype=torch.int32, device=device)
         self.attn = None
+        self._retired = []  # outgrown buffers stay alive: captured CUDA graphs may still point at them
 
     def attn_scratch(self, nfloats: int, device):
         if self.attn is None or self.attn.numel() < nfloats:
-            self.attn = torch.empty(max(nfloats, 1 << 20), dtype=torch.float32, device=device)
+            if self.attn is not None:
+                self._retired.append(self.attn)
+            self.attn = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=device)
         return self.attn
 
 
@@ -126,12 +129,11 @@ def rope_kv_write(qkv, positions, slot_mapping, k_cache, v_cache, hq, hkv, d, ro
 
 
 # --------------------------------------------------------------------------- attention
-def decode_splits(B: int, hkv: int, g_tiles: int, max_kv: int) -> int:
-    """Split-KV factor: enough CTAs for ~2 waves of 148 SMs x 4 resident CTAs, >= 256 tokens per split."""
-    ctas = max(1, B * hkv * g_tiles)
-    want = max(1, (148 * 4) // ctas)
-    by_len = max(1, max_kv // 256)
-    return int(max(1, min(want, by_len, 32)))
+def decode_splits(B: int, hq: int, hkv: int, d: int, max_kv: int, dtype=torch.bfloat16) -> int:
+    """Split-KV factor chosen by the library so the grid fills whole waves of resident CTAs."""
+    if d not in (64, 128, 256):
+        return 1
+    return int(_lib.load().llmss_attn_decode_pick_splits(B, hq, hkv, d, max_kv, _DT[dtype]))
 
 
 def attn_decode(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, hq, hkv, d, scale, num_splits):

@@ -1,0 +1,109 @@
+"""HTTP producer: `POST /generate` -> broker -> (consumer) -> broker -> response.
+
+Parity: reference `poc-server/producer-consumer/producer_server.py:9-55` (same route, same JSON
+schema, same flags in servers/producer_server.py).  Fixes of quirk Q14: every request carries a
+request id and waits on its *own* reply list with a blocking pop in a worker thread, so concurrent
+clients get their own answers and the event loop is never blocked by a busy-wait.
+Extra routes: `GET /health`, `GET /metrics` (Prometheus text), `POST /generate_stream` (SSE).
+"""
+from __future__ import annotations
+
+import asyncio
+import json
+from typing import Callable, Optional
+
+from fastapi import FastAPI, HTTPException
+from fastapi.responses import PlainTextResponse, StreamingResponse
+from pydantic import BaseModel
+
+from ..utils.metrics import METRICS
+from .broker import PRODUCER_QUEUE
+from .protocol import GenerateRequest, GenerateResponse
+
+
+class Request(BaseModel):
+    prompt: str
+    max_new_tokens: int = 20
+    is_greedy: bool = False
+    temperature: float = 1.0
+    top_p: float = 0.95
+    top_k: int = 50
+    seed: int = 0
+
+
+class Response(BaseModel):
+    prompt: str
+    continuation: str
+
+
+def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0) -> FastAPI:
+    """`broker_factory()` returns a client with lpush/brpop (one per worker thread)."""
+    app = FastAPI(title="llmss_b200 producer")
+
+    def _submit_and_wait(req: GenerateRequest) -> GenerateResponse:
+        client = broker_factory()
+        try:
+            req.with_routing()
+            client.lpush(PRODUCER_QUEUE, req.to_json())
+            got = client.brpop(req.reply_to, timeout=timeout_s)
+            if got is None:
+                raise TimeoutError("no response from the model server")
+            return GenerateResponse.from_json(got[1])
+        finally:
+            close = getattr(client, "close", None)
+            if close:
+                close()
+
+    @app.post("/generate")
+    async def generate(request: Request) -> Response:
+        METRICS.inc("http_requests_total")
+        req = GenerateRequest(**request.model_dump())
+        try:
+            req.sampling()
+        except AssertionError as e:
+            raise HTTPException(status_code=422, detail=str(e))
+        try:
+            resp = await asyncio.get_running_loop().run_in_executor(None, _submit_and_wait, req)
+        except TimeoutError as e:
+            raise HTTPException(status_code=504, detail=str(e))
+        if resp.error:
+            raise HTTPException(status_code=500, detail=resp.error)
+        return Response(prompt=resp.prompt, continuation=resp.continuation)
+
+    @app.post("/generate_stream")
+    async def generate_stream(request: Request):
+        req = GenerateRequest(**request.model_dump(), stream=True).with_routing()
+        loop = asyncio.get_running_loop()
+        client = broker_factory()
+        client.lpush(PRODUCER_QUEUE, req.to_json())
+
+        async def events():
+            try:
+                while True:
+                    got = await loop.run_in_executor(None, lambda: client.brpop(req.reply_to, timeout=timeout_s))
+                    if got is None:
+                        yield "event: error\ndata: timeout\n\n"
+                        return
+                    yield f"data: {got[1]}\n\n"
+                    if json.loads(got[1]).get("done", True):
+                        return
+            finally:
+                close = getattr(client, "close", None)
+                if close:
+                    close()
+
+        return StreamingResponse(events(), media_type="text/event-stream")
+
+    @app.get("/health")
+    async def health():
+        try:
+            ok = bool(broker_factory().ping())
+        except Exception:
+            ok = False
+        return {"status": "ok" if ok else "broker-unreachable"}
+
+    @app.get("/metrics", response_class=PlainTextResponse)
+    async def metrics():
+        return METRICS.render_prometheus()
+
+    return app

@@ -71,12 +71,24 @@ def import_reference():
     return MODEL_REGISTRY, initialize_torch_distributed, weight_files, Weights
 
 
+_PG = None
+
+
+def init_reference_dist():
+    """The reference's own process-group bring-up (dist.py:40-77); idempotent."""
+    global _PG
+    if _PG is None:
+        _, initialize_torch_distributed, _, _ = import_reference()
+        _PG = initialize_torch_distributed()
+    return _PG
+
+
 def build_reference_model(path: str, local_rank: int, dtype=torch.float16, device=None):
     """Same bring-up sequence as the reference's generate.py:42-68."""
     from transformers import AutoConfig
 
-    MODEL_REGISTRY, initialize_torch_distributed, weight_files, Weights = import_reference()
-    process_group, rank, world_size = initialize_torch_distributed()
+    MODEL_REGISTRY, _, weight_files, Weights = import_reference()
+    process_group, rank, world_size = init_reference_dist()
     if device is None:
         device = torch.device(f"cuda:{local_rank}") if torch.cuda.is_available() else torch.device("cpu")
     config = AutoConfig.from_pretrained(path)

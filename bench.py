@@ -234,7 +234,9 @@ def run_reference(args, rank, world, local):
     """The unmodified reference package (baseline/_ref/llmss) driven by a loop equivalent to its
     generate.py:102-145 (model -> logits -> rank-0 argmax -> broadcast), same checkpoint / shapes."""
     try:
-        from baseline.ref_runner import build_reference_model
+        from baseline.ref_runner import build_reference_model, init_reference_dist
+
+        init_reference_dist()  # the reference's own NCCL bring-up (dist.py:40-77)
     except Exception as e:  # noqa: BLE001
         if rank == 0:
             print(json.dumps({"impl": "reference", "unavailable": f"reference import failed: {e}"[:300]}), flush=True)

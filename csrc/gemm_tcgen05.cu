@@ -31,6 +31,7 @@
 #include "symm.cuh"
 
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace {
@@ -62,11 +63,17 @@ struct GemmArgs {
   int64_t ldo;
   int out_f32;
   int act, act_start, gated;
+  int epi;                // EPI_* flavour, derived from the flags above on the host
   float* sk_ws;           // stream-K partial slots: [2 * grid][BN][128] fp32 (first / last segment of a CTA)
   uint32_t* sk_counters;  // [tiles], zero between launches
   int ar;                 // fused all-reduce over ws
+  unsigned long long* dbg;  // optional per-CTA phase timestamps [grid][8] (globaltimer ns), see llmss_gemm_set_debug
   SymmWs ws;
 };
+#define LLMSS_STAMP(slot_)                                                                   \
+  do {                                                                                       \
+    if (a.dbg != nullptr) a.dbg[(size_t)blockIdx.x * 8 + (slot_)] = globaltimer_ns();        \
+  } while (0)
 
 // ----- stream-K work decomposition (identical on every rank) -----
 struct Segment {
@@ -115,6 +122,125 @@ __device__ __forceinline__ uint4 ld_cg_u4(const void* p) {
   return r;
 }
 
+
+// ---- bias / activation / gating / residual + transposed store of 8 token columns of one feature ----
+// The epilogue flavour is decided once on the host (GemmArgs::epi) and dispatched once per group, so
+// the per-element code is a handful of instructions (an earlier fully generic per-element version
+// was ~140 instructions per output and made the tail of the kernel instruction-bound).
+enum { EPI_PLAIN = 0, EPI_ACT = 1, EPI_GATED = 2, EPI_F32 = 3 };
+
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float act_fast(float x, int act) {
+  if (act == LLMSS_ACT_GELU_TANH) return 0.5f * x * (1.0f + tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+  if (act == LLMSS_ACT_RELU) return fmaxf(x, 0.0f);
+  if (act == LLMSS_ACT_SILU) return __fdividef(x, 1.0f + __expf(-x));
+  if (act == LLMSS_ACT_GELU_ERF) return 0.5f * x * (1.0f + erff(x * 0.7071067811865475f));
+  return x;
+}
+
+template <typename T>
+__device__ __forceinline__ void epilogue_store8(const GemmArgs& a, const float (&v)[8], int n, int mb, int lane,
+                                                float bval) {
+  const int rows = a.M - mb;  // valid token rows in this group (may be <= 0 or >= 8)
+  const bool n_ok = n < a.N;
+  switch (a.epi) {
+    case EPI_PLAIN: {
+      if (!n_ok) return;
+      T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + n;
+      if (a.residual != nullptr) {
+        const T* r = reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + n;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j < rows) o[(int64_t)j * a.ldo] = from_f32<T>(v[j] + bval + to_f32(r[(int64_t)j * a.ldr]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j < rows) o[(int64_t)j * a.ldo] = from_f32<T>(v[j] + bval);
+      }
+      return;
+    }
+    case EPI_ACT: {
+      if (!n_ok) return;
+      T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + n;
+      const int act = (n >= a.act_start) ? a.act : LLMSS_ACT_NONE;
+      const T* r = a.residual != nullptr ? reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + n : nullptr;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (j < rows) {
+          float y = act_fast(v[j] + bval, act);
+          if (r != nullptr) y += to_f32(r[(int64_t)j * a.ldr]);
+          o[(int64_t)j * a.ldo] = from_f32<T>(y);
+        }
+      }
+      return;
+    }
+    case EPI_GATED: {
+      // rows of w interleave (gate, up): even lane holds gate_j, odd lane up_j of output feature n/2
+      T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + (n >> 1);
+      const T* r = a.residual != nullptr ? reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + (n >> 1) : nullptr;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float y = v[j] + bval;
+        const float other = __shfl_xor_sync(0xffffffffu, y, 1);
+        if ((lane & 1) == 0 && n_ok && j < rows) {
+          float g = act_fast(y, a.act) * other;
+          if (r != nullptr) g += to_f32(r[(int64_t)j * a.ldr]);
+          o[(int64_t)j * a.ldo] = from_f32<T>(g);
+        }
+      }
+      return;
+    }
+    default: {  // EPI_F32: fp32 output (LM head logits), optional bias / activation / residual
+      if (!n_ok) return;
+      float* o = reinterpret_cast<float*>(a.out) + (int64_t)mb * a.ldo + n;
+      const int act = (n >= a.act_start) ? a.act : LLMSS_ACT_NONE;
+      const T* r = a.residual != nullptr ? reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + n : nullptr;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (j < rows) {
+          float y = act_fast(v[j] + bval, act);
+          if (r != nullptr) y += to_f32(r[(int64_t)j * a.ldr]);
+          o[(int64_t)j * a.ldo] = y;
+        }
+      }
+      return;
+    }
+  }
+}
+
+// ---- thread-block-cluster helpers (split-K kernel) ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local_smem_addr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t cluster_addr) {
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(cluster_addr)
+               : "memory");
+  return v;
+}
+
 template <typename T, int BN>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
@@ -133,6 +259,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = gridDim.x, g = blockIdx.x;
   const int tiles = a.tiles_n * a.tiles_m;
+  if (threadIdx.x == 0) LLMSS_STAMP(0);
 
   uint32_t epoch = 0;
   if (a.ar) epoch = *a.ws.epoch + 1;
@@ -158,6 +285,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -196,6 +324,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase, 21);
+          if (a.dbg != nullptr && a.dbg[(size_t)blockIdx.x * 8 + 3] == 0) LLMSS_STAMP(3);
           tcgen05_fence_after();
           const uint32_t sw = smem_u32(smem + stage * C::STAGE_BYTES);
           const uint32_t sx = sw + C::W_BYTES;
@@ -210,6 +339,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+      LLMSS_STAMP(4);
     }
   } else {
     // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
@@ -224,7 +354,6 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     SegIter it(g, G, tiles, a.kb_total);
     Segment sg;
     const T* bias = reinterpret_cast<const T*>(a.bias);
-    const T* residual = reinterpret_cast<const T*>(a.residual);
     constexpr int NG = BN / 8;               // column groups per tile
     int seg_idx = -1;
     const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
@@ -242,6 +371,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
 
       mbar_wait(&tfull_bar[as], aphase, 30);
       tcgen05_fence_after();
+      if (epi_tid == 0) LLMSS_STAMP(5);
 
       bool have_final = full_tile;
       if (!full_tile) {
@@ -272,6 +402,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         have_final = (*s_flag != 0);
         epi_bar();  // s_flag may be rewritten by the next segment
         if (have_final) __threadfence();
+        if (epi_tid == 0) LLMSS_STAMP(2);
       }
 
       if (have_final) {
@@ -357,35 +488,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 for (int j = 0; j < 8; ++j) v[j] += t8[j];
               }
             }
-            // ---- bias / activation / gating / residual, transposed store out[m][n] ----
-            const int mb = m0 + cg * 8;
-            if (a.gated) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float y = v[j] + bval;
-                const float other = __shfl_xor_sync(0xffffffffu, y, 1);
-                if ((lane & 1) == 0 && n_ok && mb + j < a.M) {
-                  float r = act_apply(y, a.act) * other;
-                  if (residual != nullptr) r += to_f32(residual[(int64_t)(mb + j) * a.ldr + (n >> 1)]);
-                  const int64_t o = (int64_t)(mb + j) * a.ldo + (n >> 1);
-                  if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = r;
-                  else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(r);
-                }
-              }
-            } else if (n_ok) {
-              const bool do_act = (a.act != LLMSS_ACT_NONE) && n >= a.act_start;
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                if (mb + j < a.M) {
-                  float y = v[j] + bval;
-                  if (do_act) y = act_apply(y, a.act);
-                  if (residual != nullptr) y += to_f32(residual[(int64_t)(mb + j) * a.ldr + n]);
-                  const int64_t o = (int64_t)(mb + j) * a.ldo + n;
-                  if (a.out_f32) reinterpret_cast<float*>(a.out)[o] = y;
-                  else reinterpret_cast<T*>(a.out)[o] = from_f32<T>(y);
-                }
-              }
-            }
+            epilogue_store8<T>(a, v, n, m0 + cg * 8, lane, bval);
           }
         }
         if (full_tile && !a.ar) {
@@ -396,6 +499,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    if (epi_tid == 0) LLMSS_STAMP(6);
   }
 
   // ---- teardown ----
@@ -406,6 +510,194 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     tmem_dealloc(tmem_base, C::TMEM_COLS);
   }
   if (a.ar) symm_finish(a.ws, epoch);
+  if (threadIdx.x == 0) LLMSS_STAMP(7);
+}
+
+
+// ======================================================================================
+// Cluster split-K variant for shapes with few output tiles (decode GEMMs at TP >= 2, every
+// row-parallel GEMM: N = hidden -> 32 tiles).  A thread-block cluster of S CTAs shares one
+// tile: CTA r streams k-blocks [r*kb/S, (r+1)*kb/S), parks its fp32 accumulator in its own
+// shared memory (the drained TMA ring), and after one cluster barrier each CTA reduces 1/S of
+// the tile straight out of its peers' shared memory (DSMEM, fixed CTA order -> deterministic)
+// and runs the epilogue / fused all-reduce for that slice.  No global workspace, no atomics,
+// no fences: the fix-up costs ~1 us instead of several L2 round trips.
+// ======================================================================================
+template <typename T, int BN>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                    const __grid_constant__ GemmArgs a) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + C::STAGES;
+  uint64_t* tfull_bar = bars + 2 * C::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull_bar + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int S = (int)cluster_nctarank(), r = (int)cluster_ctarank();
+  const int tile = blockIdx.x / S;
+  const int tn = tile % a.tiles_n, tm = tile / a.tiles_n;
+  const int kb0 = (int)(((int64_t)r * a.kb_total) / S), kb1 = (int)(((int64_t)(r + 1) * a.kb_total) / S);
+  constexpr int NG = BN / 8;
+  constexpr int TCOLS = BN < 32 ? 32 : BN;
+  if (threadIdx.x == 0) LLMSS_STAMP(0);
+
+  uint32_t epoch = 0;
+  if (a.ar) epoch = *a.ws.epoch + 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_x);
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tfull_bar[0], 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TCOLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  float4* staging = reinterpret_cast<float4*>(smem);  // [NG*2][128] float4, reuses the drained TMA ring
+  if (threadIdx.x == 0) LLMSS_STAMP(1);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint64_t pol_w = l2_policy_evict_first();
+      const uint64_t pol_x = l2_policy_evict_last();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1, 40);
+        uint8_t* sw = smem + stage * C::STAGE_BYTES;
+        mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+        tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
+        tma_load_2d(sw + C::W_BYTES, &tmap_x, &full_bar[stage], kb * BK, tm * BN, pol_x);
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase, 41);
+        if (kb == kb0) LLMSS_STAMP(3);
+        tcgen05_fence_after();
+        const uint32_t sw = smem_u32(smem + stage * C::STAGE_BYTES);
+        const uint32_t sx = sw + C::W_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)
+          umma_f16_ss(tmem_base, umma_desc_k_sw128(sw + k * 32), umma_desc_k_sw128(sx + k * 32), idesc,
+                      (kb > kb0 || k > 0) ? 1u : 0u);
+        umma_commit(&empty_bar[stage]);
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(&tfull_bar[0]);
+      LLMSS_STAMP(4);
+    }
+  } else {
+    // park the accumulator in shared memory: [(cg*2 + half)][feature] float4, conflict-free
+    const int quarter = warp & 3;
+    const int f = quarter * 32 + lane;
+    const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    mbar_wait(&tfull_bar[0], 0, 42);  // all MMAs retired => every TMA stage has landed and been consumed
+    tcgen05_fence_after();
+    if (threadIdx.x == 64) LLMSS_STAMP(5);
+#pragma unroll 1
+    for (int cg = 0; cg < NG; ++cg) {
+      uint32_t q[8];
+      tmem_ld_32x32b_x8(t_addr + cg * 8, q);
+      tmem_ld_wait();
+      staging[(cg * 2 + 0) * BM + f] = make_float4(__uint_as_float(q[0]), __uint_as_float(q[1]), __uint_as_float(q[2]), __uint_as_float(q[3]));
+      staging[(cg * 2 + 1) * BM + f] = make_float4(__uint_as_float(q[4]), __uint_as_float(q[5]), __uint_as_float(q[6]), __uint_as_float(q[7]));
+    }
+  }
+  __syncwarp();
+  cluster_sync_all();  // every CTA's partial tile is now visible cluster-wide
+
+  if (warp >= 2) {
+    const int epi_tid = threadIdx.x - 64;
+    const int per = NG * BM / S;                 // (column group, feature) items owned by this CTA
+    const T* bias = reinterpret_cast<const T*>(a.bias);
+    const int tiles = a.tiles_n * a.tiles_m;
+    const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
+    const int par = epoch & 1;
+    const uint32_t stage_u32 = smem_u32(staging);
+    const int n_pass = a.ar ? 2 : 1;
+#pragma unroll 1
+    for (int pass = 0; pass < n_pass; ++pass) {
+      if (pass == 1) {
+        __threadfence_system();
+        epi_bar();
+        const int slot = tile * S + r;  // one flag slot per (tile, slice): the same CTA owns it on every rank
+        if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
+          st_release_sys(symm_flag(a.ws, epi_tid, 0, slot) + a.ws.rank, epoch);
+        if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
+          wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, slot) + epi_tid, epoch, 43);
+        epi_bar();
+      }
+#pragma unroll 1
+      for (int it = epi_tid; it < per; it += 128) {
+        const int item = r * per + it;
+        const int cg = item / BM, f = item % BM;
+        const int n = tn * BM + f;
+        const size_t xoff = ((size_t)tile * NG + cg) * (BM * 16) + (size_t)f * 16;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = 0.f;
+        if (pass == 0) {
+          const uint32_t off = (uint32_t)(((cg * 2) * BM + f) * 16);
+          for (int q = 0; q < S; ++q) {  // CTA order: deterministic
+            const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
+            const float4 lo = ld_dsmem_f4(base), hi = ld_dsmem_f4(base + BM * 16);
+            v[0] += lo.x; v[1] += lo.y; v[2] += lo.z; v[3] += lo.w;
+            v[4] += hi.x; v[5] += hi.y; v[6] += hi.z; v[7] += hi.w;
+          }
+          if (a.ar) {
+            const uint4 vec = pack8<T>(v);
+#pragma unroll 1
+            for (int p = 0; p < a.ws.nranks; ++p) {
+              const int peer = (a.ws.rank + p) % a.ws.nranks;
+              *reinterpret_cast<uint4*>(symm_buf<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+            }
+            continue;
+          }
+        } else {
+          const uint8_t* mine = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
+          for (int q = 0; q < a.ws.nranks; ++q) {  // rank order: bit-identical on every rank
+            float t8[8];
+            unpack8<T>(ld_cg_u4(mine + (size_t)q * ar_slot_bytes + xoff), t8);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += t8[j];
+          }
+        }
+        const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+        epilogue_store8<T>(a, v, n, tm * BN + cg * 8, lane, bval);
+      }
+    }
+  }
+  if (threadIdx.x == 64) LLMSS_STAMP(6);
+  __syncwarp();
+  cluster_sync_all();  // nobody may exit while a peer is still reading its shared memory
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, TCOLS);
+  }
+  if (a.ar) symm_finish(a.ws, epoch);
+  if (threadIdx.x == 0) LLMSS_STAMP(7);
 }
 
 // ------------------------------------------------------------------ host side
@@ -441,6 +733,7 @@ int make_tmap(CUtensorMap* map, const void* ptr, int dtype, int64_t rows, int64_
   return 0;
 }
 
+unsigned long long* g_dbg = nullptr;
 int g_num_sms = 0;
 int num_sms() {
   if (g_num_sms == 0) {
@@ -466,13 +759,71 @@ int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int 
   return 0;
 }
 
+template <typename T, int BN>
+int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int tiles, int split,
+                   cudaStream_t stream) {
+  using C = Cfg<BN>;
+  static bool configured = false;
+  auto kern = gemm_cluster_kernel<T, BN>;
+  if (!configured) {
+    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(tiles * split);
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = split;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  LLMSS_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, a));
+  return 0;
+}
+
+// 0 = stream-K persistent kernel; 2/4/8 = cluster split-K factor.  LLMSS_GEMM_MODE=streamk|cluster forces one.
+int pick_cluster_split(int tiles, int kb_total, int bn, int sms) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("LLMSS_GEMM_MODE");
+    forced = (e == nullptr) ? 0 : (strcmp(e, "streamk") == 0 ? 1 : (strcmp(e, "cluster") == 0 ? 2 : 0));
+  }
+  if (forced == 1) return 0;
+  const int staging_bytes = BM * bn * 4;
+  if (staging_bytes > Cfg<16>::STAGES * 0 + 190 * 1024) return 0;  // accumulator must fit in the drained ring
+  int best = 0;
+  for (int s = 2; s <= 8; s *= 2) {
+    if (tiles * s > sms && forced != 2) break;
+    if (kb_total / s < 2) break;
+    best = s;
+  }
+  if (forced == 2 && best == 0 && kb_total >= 2) best = 2;
+  // stream-K fills all SMs; prefer the cluster only when it occupies at least ~70% of them
+  if (forced != 2 && best > 0 && tiles * best * 10 < sms * 7) return 0;
+  return best;
+}
+
 int pick_bn(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256; }
 
 }  // namespace
 
+// Profiling aid: when non-null, every CTA of the following llmss_gemm launches writes 8 globaltimer
+// stamps (entry, prologue done, last TMA issued, first stage landed, last MMA issued, first
+// accumulator ready, epilogue done, exit) to buf[cta*8 .. cta*8+7].  buf must be zeroed by the caller.
+LLMSS_API int llmss_gemm_set_debug(unsigned long long* buf) {
+  g_dbg = buf;
+  return 0;
+}
+
 // Plan of a GEMM launch (so the caller can size the workspaces before capture).
 struct llmss_gemm_plan {
-  int bn, tiles, kb_total, grid;
+  int bn, tiles, kb_total, grid;  // grid: CTAs launched (stream-K) or tiles * split (cluster)
+  int split;                // 0 = stream-K kernel, else cluster split-K factor
   int64_t sk_ws_floats;     // stream-K partial workspace (floats)
   int64_t sk_counters;      // uint32 counters (must be zero before first use)
   int64_t ar_bytes;         // symmetric buffer bytes needed per parity when ar=1
@@ -494,8 +845,10 @@ LLMSS_API int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_by
   p->bn = bn;
   p->tiles = tiles;
   p->kb_total = kb_total;
+  p->split = pick_cluster_split(tiles, kb_total, bn, sms);
+  if (p->split > 0) grid = (int64_t)tiles * p->split;
   p->grid = (int)grid;
-  p->sk_ws_floats = (int64_t)2 * grid * BM * bn;
+  p->sk_ws_floats = p->split > 0 ? 0 : (int64_t)2 * grid * BM * bn;
   p->sk_counters = tiles;
   p->ar_bytes = (int64_t)nranks * tiles * BM * bn * elem_bytes;
   return 0;
@@ -511,14 +864,16 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "gemm: dtype must be f16/bf16");
   LLMSS_REQUIRE(M > 0 && N > 0 && K > 0 && K % 8 == 0, "gemm: bad shape M=%d N=%d K=%d (K must be a multiple of 8)", M, N, K);
   LLMSS_REQUIRE(!gated || (N % 2 == 0), "gemm: gated epilogue needs even N");
+  LLMSS_REQUIRE(!(gated && out_f32), "gemm: gated epilogue with fp32 output is not supported");
   const bool ar = (ws != nullptr && ws->nranks > 1);
   LLMSS_REQUIRE(!(ar && (gated || act != LLMSS_ACT_NONE || out_f32)), "gemm: fused all-reduce supports bias/residual epilogues only");
   llmss_gemm_plan p;
   llmss_gemm_plan_query(M, N, K, ar ? ws->nranks : 1, 2, max_ctas, &p);
-  const bool need_sk = (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
+  const bool need_sk = p.split == 0 && (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
   LLMSS_REQUIRE(!need_sk || (sk_ws != nullptr && sk_counters != nullptr), "gemm: stream-K workspace required for this shape");
   if (ar) {
-    LLMSS_REQUIRE(p.tiles <= kSymmMaxSlots, "gemm: %d tiles exceed the %d flag slots of the symmetric workspace", p.tiles, kSymmMaxSlots);
+    LLMSS_REQUIRE(p.tiles * (p.split > 0 ? p.split : 1) <= kSymmMaxSlots,
+                  "gemm: %d tiles exceed the %d flag slots of the symmetric workspace", p.tiles, kSymmMaxSlots);
     LLMSS_REQUIRE((size_t)p.ar_bytes <= ws->buf_bytes, "gemm: fused all-reduce needs %lld bytes of symmetric buffer (have %zu)",
                   (long long)p.ar_bytes, ws->buf_bytes);
   }
@@ -535,10 +890,13 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
   a.bias = bias; a.residual = residual; a.ldr = ldr;
   a.out = out; a.ldo = ldo; a.out_f32 = out_f32;
   a.act = act; a.act_start = act_start; a.gated = gated;
+  a.epi = gated ? EPI_GATED : (out_f32 ? EPI_F32 : (act != LLMSS_ACT_NONE ? EPI_ACT : EPI_PLAIN));
   a.sk_ws = sk_ws; a.sk_counters = sk_counters;
   a.ar = ar ? 1 : 0;
+  a.dbg = g_dbg;
   if (ar) a.ws = *ws;
-#define LLMSS_LAUNCH(T_, BN_) return launch<T_, BN_>(tw, tx, a, p.grid, stream)
+#define LLMSS_LAUNCH(T_, BN_) \
+  return p.split > 0 ? launch_cluster<T_, BN_>(tw, tx, a, p.tiles, p.split, stream) : launch<T_, BN_>(tw, tx, a, p.grid, stream)
   if (dtype == LLMSS_F16) {
     switch (p.bn) {
       case 16: LLMSS_LAUNCH(__half, 16);

@@ -45,10 +45,12 @@ int llmss_allgather(llmss_symm_t* ws, const void* in, void* out, int64_t bytes, 
 /* ---- K5/K1/K2 tcgen05 GEMM (+ fused all-reduce epilogue) (G3,G4,G9,G10,G12,G14; layers.py:62,175-179) ---- */
 typedef struct llmss_gemm_plan {
   int bn, tiles, kb_total, grid;
+  int split; /* 0 = stream-K persistent kernel, 2/4/8 = thread-block-cluster split-K */
   int64_t sk_ws_floats;
   int64_t sk_counters;
   int64_t ar_bytes;
 } llmss_gemm_plan;
+int llmss_gemm_set_debug(unsigned long long* per_cta_stamps); /* profiling aid: 8 globaltimer stamps per CTA */
 int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p);
 int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias, const void* residual,
                int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype, int out_f32, int act,

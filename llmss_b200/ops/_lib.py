@@ -17,7 +17,7 @@ c_void_p, c_int, c_int64, c_float, c_size_t = C.c_void_p, C.c_int, C.c_int64, C.
 
 
 class GemmPlan(C.Structure):
-    _fields_ = [("bn", c_int), ("tiles", c_int), ("kb_total", c_int), ("grid", c_int),
+    _fields_ = [("bn", c_int), ("tiles", c_int), ("kb_total", c_int), ("grid", c_int), ("split", c_int),
                 ("sk_ws_floats", c_int64), ("sk_counters", c_int64), ("ar_bytes", c_int64)]
 
 
@@ -35,6 +35,7 @@ _SIGS = {
     "llmss_symm_epoch": (c_int, [c_void_p, C.POINTER(C.c_uint32)]),
     "llmss_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "llmss_allgather": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "llmss_gemm_set_debug": (c_int, [c_void_p]),
     "llmss_gemm_plan_query": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, C.POINTER(GemmPlan)]),
     "llmss_gemm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
                            c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

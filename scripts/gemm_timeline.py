@@ -1,0 +1,48 @@
+"""Per-CTA phase timeline of the GEMM kernels (globaltimer stamps, see llmss_gemm_set_debug)."""
+import ctypes as C
+import math
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from llmss_b200.ops import _lib
+from llmss_b200.ops import cuda_impl as cu
+
+NAMES = ["entry", "prologue", "fixupDecided", "firstFull", "lastMMA", "accReady(last seg)", "epiDone", "exit"]
+
+
+def run(M, N, K):
+    lib = _lib.load()
+    w = [torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / math.sqrt(K) for _ in range(3)]
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    p = cu.gemm_plan(M, N, K)
+    for i in range(3):
+        cu.linear(x, w[i], out=out)
+    dbg = torch.zeros(p.grid * 8, dtype=torch.int64, device="cuda")
+    lib.llmss_gemm_set_debug(C.c_void_p(dbg.data_ptr()))
+    cu.linear(x, w[0], out=out)
+    torch.cuda.synchronize()
+    lib.llmss_gemm_set_debug(None)
+    t = dbg.view(p.grid, 8).cpu().double()
+    t0 = t[:, 0].min()
+    rel = (t - t0) / 1e3
+    print(f"M={M} N={N} K={K} bn={p.bn} split={p.split} grid={p.grid}: kernel span {rel[:, 7].max():.1f} us")
+    for i, n in enumerate(NAMES):
+        col = rel[:, i][t[:, i] > 0]
+        if len(col):
+            print(f"   {n:18s} min {col.min():7.2f}  median {col.median():7.2f}  max {col.max():7.2f} us")
+
+
+    if p.split == 0:
+        d1 = (t[:, 2] - t[:, 5])[t[:, 2] > 0] / 1e3
+        d2 = (t[:, 6] - t[:, 2])[t[:, 2] > 0] / 1e3
+        d3 = (t[:, 6] - t[:, 5]) / 1e3
+        print(f"   last segment: dump+fence+ticket median {d1.median():.2f} max {d1.max():.2f} us | after decision -> done "
+              f"median {d2.median():.2f} max {d2.max():.2f} us | total median {d3.median():.2f} max {d3.max():.2f}")
+
+
+for shape in [(64, 4096, 2560), (16, 4096, 2560), (64, 28672, 4096), (64, 4096, 20480)]:
+    run(*shape)

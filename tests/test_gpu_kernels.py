@@ -202,3 +202,38 @@ def test_sample_matches_oracle():
         g = greedy.bool()
         assert torch.equal(got.long()[g], logits[g, :V].argmax(-1))
         assert int(got.max()) < V
+
+
+@pytest.mark.parametrize("mode", ["streamk", "cluster"])
+def test_gemm_modes_agree(mode):
+    """Both schedulers (persistent stream-K, thread-block-cluster split-K) in a fresh process."""
+    import os
+    import subprocess
+    import sys
+
+    code = r"""
+import math, torch
+from llmss_b200.ops import cuda_impl as cu, reference as R
+torch.manual_seed(0)
+bad = 0
+for (M, N, K) in [(1, 128, 128), (8, 4096, 2560), (16, 3584, 4096), (64, 4096, 2560), (64, 4096, 20480), (33, 1000, 328),
+                  (128, 2048, 1024), (256, 4096, 4096), (64, 512, 8192)]:
+    for dt in (torch.bfloat16, torch.float16):
+        x = torch.randn(M, K, device='cuda', dtype=dt); w = torch.randn(N, K, device='cuda', dtype=dt) / math.sqrt(K)
+        b = torch.randn(N, device='cuda', dtype=dt); r = torch.randn(M, N, device='cuda', dtype=dt)
+        p = cu.gemm_plan(M, N, K)
+        y = cu.linear(x, w, b, act=R.ACT_GELU_TANH, residual=r)
+        y2 = cu.linear(x, w, b, act=R.ACT_GELU_TANH, residual=r)
+        ref = R.linear(x, w, b, act=R.ACT_GELU_TANH, residual=r, out_dtype=torch.float32)
+        err = (y.float() - ref).abs()
+        nbad = int((err > 4e-2 + 2e-2 * ref.abs()).sum())
+        same = torch.equal(y, y2)
+        print(M, N, K, dt, 'split', p.split, 'grid', p.grid, 'max err', err.max().item(), 'bad', nbad, 'repeatable', same)
+        bad += nbad + (0 if same else 1)
+    g = cu.linear(x[:, :], torch.randn(N + (N % 2), K, device='cuda', dtype=dt) / math.sqrt(K), act=R.ACT_SILU, gated=True)
+torch.cuda.synchronize()
+print('MODES_OK' if bad == 0 else 'MODES_FAILED')
+"""
+    env = dict(os.environ, LLMSS_GEMM_MODE=mode, PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert "MODES_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]

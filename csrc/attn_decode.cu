@@ -17,6 +17,8 @@ namespace {
 
 constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
+constexpr int kStages = 4;  // cp.async ring depth per warp
+constexpr int kRingBytes(int U) { return kWarps * kStages * U * 2 * 32 * 16; }
 
 __device__ __forceinline__ uint4 ldg_stream(const void* p) {
   uint4 r;
@@ -79,31 +81,52 @@ __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
   const int64_t head_stride = (int64_t)block_size * D;
   constexpr int TOK_PER_ITER = TPW * U;
 
-  // Register double buffering: the loads of iteration i+1 are in flight while iteration i is
-  // reduced, so every lane keeps 2*U 16-byte requests outstanding for the whole stream.
-  auto issue = [&](int t0, uint4 (&kr)[U], uint4 (&vr)[U]) {
+  // cp.async ring: every lane stages its own 16-byte K and V slices for the next kStages-1
+  // iterations in shared memory (no registers held by loads in flight, no cross-lane sharing, so a
+  // per-thread cp.async.wait_group is the only synchronisation).  ~12 KB of requests stay in
+  // flight per warp for the whole stream.
+  extern __shared__ uint4 ring_raw[];
+  uint4* ring = ring_raw + (size_t)warp * (kStages * U * 2 * 32) + lane;  // [stage][u][k|v][lane]
+  auto issue = [&](int t0, int stage) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int t = t0 + u * TPW + grp;
-      kr[u] = make_uint4(0, 0, 0, 0);
-      vr[u] = make_uint4(0, 0, 0, 0);
-      if (t < t_end) {
-        const int blk = __ldg(bt + t / block_size);
-        const int64_t off = ((int64_t)blk * hkv + hk) * head_stride + (int64_t)(t % block_size) * D + lig * 8;
-        kr[u] = ldg_stream(k_cache + off);
-        vr[u] = ldg_stream(v_cache + off);
-      }
+      const bool ok = t < t_end;
+      const int tt = ok ? t : t_begin;  // any valid token: with src-size 0 nothing is read, zeros are written
+      const int blk = __ldg(bt + tt / block_size);
+      const int64_t off = ((int64_t)blk * hkv + hk) * head_stride + (int64_t)(tt % block_size) * D + lig * 8;
+      const uint32_t dst = smem_u32(ring + (size_t)((stage * U + u) * 2) * 32);
+      const int nbytes = ok ? 16 : 0;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(k_cache + off), "r"(nbytes) : "memory");
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 512), "l"(v_cache + off), "r"(nbytes) : "memory");
     }
   };
-  uint4 kraw[U], vraw[U], knext[U], vnext[U];
   const int t_first = t_begin + warp * TOK_PER_ITER;
-  if (t_first < t_end) issue(t_first, kraw, vraw);
-  for (int t0 = t_first; t0 < t_end; t0 += kWarps * TOK_PER_ITER) {
-    const int t_nxt = t0 + kWarps * TOK_PER_ITER;
-    if (t_nxt < t_end) issue(t_nxt, knext, vnext);
+  const int t_stride = kWarps * TOK_PER_ITER;
+#pragma unroll
+  for (int st = 0; st < kStages - 1; ++st) {
+    if (t_first + st * t_stride < t_end) issue(t_first + st * t_stride, st);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  int stage = 0;
+  for (int t0 = t_first; t0 < t_end; t0 += t_stride) {
+    {
+      const int t_pre = t0 + (kStages - 1) * t_stride;
+      int st_pre = stage + kStages - 1;
+      if (st_pre >= kStages) st_pre -= kStages;
+      if (t_pre < t_end) issue(t_pre, st_pre);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group %0;" ::"n"(kStages - 1) : "memory");
+    }
+    uint4 kraw[U], vraw[U];
     bool valid[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) valid[u] = (t0 + u * TPW + grp) < t_end;
+    for (int u = 0; u < U; ++u) {
+      valid[u] = (t0 + u * TPW + grp) < t_end;
+      kraw[u] = ring[(size_t)((stage * U + u) * 2) * 32];
+      vraw[u] = ring[(size_t)((stage * U + u) * 2 + 1) * 32];
+    }
+    if (++stage == kStages) stage = 0;
     float s[U][GT];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -153,11 +176,6 @@ __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
       for (int g = 0; g < GT; ++g)
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(s[u][g], vf[i], acc[g][i]);
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      kraw[u] = knext[u];
-      vraw[u] = vnext[u];
     }
   }
 
@@ -248,7 +266,13 @@ int launch_decode(const void* q, int64_t ldq, const void* kc, const void* vc, co
   const int g_tiles = (G + GT - 1) / GT;
   dim3 grid(num_splits, hkv * g_tiles, B);
   const float scale_log2 = scale * 1.4426950408889634f;
-  attn_decode_kernel<T, D, GT, U><<<grid, kThreads, 0, stream>>>(
+  static bool configured = false;
+  if (!configured) {
+    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(attn_decode_kernel<T, D, GT, U>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          kRingBytes(U)));
+    configured = true;
+  }
+  attn_decode_kernel<T, D, GT, U><<<grid, kThreads, kRingBytes(U), stream>>>(
       (const T*)q, ldq, (const T*)kc, (const T*)vc, bt, max_blocks, seq_lens, (T*)out, ldo, part_o, part_ml, hq, hkv,
       block_size, scale_log2, num_splits);
   LLMSS_CHECK_CUDA(cudaGetLastError());
@@ -286,7 +310,11 @@ LLMSS_API int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int m
   int occ = 4, sms = 148, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-#define LLMSS_OCC(T_, D_, GT_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, attn_decode_kernel<T_, D_, GT_, 4>, kThreads, 0)
+#define LLMSS_OCC(T_, D_, GT_)                                                                                      \
+  do {                                                                                                            \
+    cudaFuncSetAttribute(attn_decode_kernel<T_, D_, GT_, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRingBytes(4)); \
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, attn_decode_kernel<T_, D_, GT_, 4>, kThreads, kRingBytes(4));     \
+  } while (0)
   if (dtype == LLMSS_F16) {
     if (d == 64) { if (GT == 1) LLMSS_OCC(__half, 64, 1); else if (GT == 2) LLMSS_OCC(__half, 64, 2); else LLMSS_OCC(__half, 64, 4); }
     else if (d == 128) { if (GT == 1) LLMSS_OCC(__half, 128, 1); else if (GT == 2) LLMSS_OCC(__half, 128, 2); else LLMSS_OCC(__half, 128, 4); }

@@ -24,6 +24,9 @@ PRESETS: Dict[str, dict] = {
     "gptj-tiny": dict(model_type="gptj", architectures=["GPTJForCausalLM"], vocab_size=512, n_positions=256,
                       n_embd=256, n_layer=2, n_head=4, rotary_dim=32, n_inner=None, activation_function="gelu_new",
                       layer_norm_epsilon=1e-5, tie_word_embeddings=False, bos_token_id=0, eos_token_id=0),
+    "gptj-tiny8": dict(model_type="gptj", architectures=["GPTJForCausalLM"], vocab_size=512, n_positions=256,
+                       n_embd=512, n_layer=2, n_head=8, rotary_dim=32, n_inner=None, activation_function="gelu_new",
+                       layer_norm_epsilon=1e-5, tie_word_embeddings=False, bos_token_id=0, eos_token_id=0),
     # StarCoder shape (MQA) -- the reference's second family
     "starcoder": dict(model_type="gpt_bigcode", architectures=["GPTBigCodeForCausalLM"], vocab_size=49152,
                       n_positions=8192, n_embd=6144, n_layer=40, n_head=48, n_inner=24576, multi_query=True,

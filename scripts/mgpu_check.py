@@ -171,9 +171,9 @@ def main():
     from llmss_b200.utils.checkpoint import write_random_checkpoint
     from llmss_b200.utils.dist import FakeGroup
 
-    path = "/tmp/llmss_mgpu_ckpt"
+    path = "/tmp/llmss_mgpu_ckpt8"
     if rank == 0:
-        write_random_checkpoint(path, "gptj-tiny", dtype=torch.float16, device="cuda", std=0.08)
+        write_random_checkpoint(path, "gptj-tiny8", dtype=torch.float16, device="cuda", std=0.05)
     dist.barrier()
     prompts = [[3, 14, 15, 92, 65], [35, 89, 79], [32, 38, 46, 26, 43, 38, 32], [7] * 20]
     sp = SamplingParams(max_new_tokens=10, is_greedy=True)

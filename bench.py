@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--dtype", default=None, help="bf16 | fp16 (default: bf16 ours, fp16 reference)")
     ap.add_argument("--ckpt-dir", default=os.environ.get("LLMSS_BENCH_CKPT", "/tmp/llmss_b200_bench"))
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--profile-ops", action="store_true", help="eager decode with per-op CUDA-event timing (diagnostic)")
     return ap.parse_args()
 
 
@@ -209,6 +210,21 @@ def run_ours(args, rank, world, local):
 
     value = B * K / (dev_ms / 1e3)
     e2e_value = B * K / e2e_s
+    if args.profile_ops:
+        from llmss_b200.utils import tracing
+
+        tracing.enable(profile=True)
+        tracing.reset()
+        runner.use_graph = False
+        for _ in range(4):
+            runner.decode_step(sync=False, host_tokens=False)
+        rep = tracing.report()
+        if rank == 0:
+            print("[bench] per-op device time over 4 eager decode steps:", file=sys.stderr)
+            for k, v in rep.items():
+                print(f"[bench]   {k:28s} calls={v['calls']:5d} avg={v['avg_us']:9.2f} us total={v['total_us'] / 4:10.1f} us/step",
+                      file=sys.stderr)
+        runner.sync_lengths()
     out = {
         "metric": "decode_tokens_per_s", "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": K,
         "warmup": Wm, "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "strong",

@@ -32,6 +32,7 @@ from .. import ops
 from ..engine.batch import BatchInput
 from ..ops import (ACT_IDS, ACT_NONE, NORM_LAYER, NORM_RMS, ROPE_GPTJ, ROPE_NEOX, ROPE_NONE)
 from ..parallel.comm import comm_for
+from ..utils.tracing import trace
 
 
 @dataclass
@@ -166,14 +167,19 @@ class DecoderLM(nn.Module):
 
     def _layer_fused_parallel(self, L: LayerWeights, x, resid, batch: BatchInput, kc, vc):
         s = self.spec
-        hn, resid = ops.norm_residual(x, resid, L.ln1_w, L.ln1_b, s.eps, s.norm)
+        with trace("norm_residual"):
+            hn, resid = ops.norm_residual(x, resid, L.ln1_w, L.ln1_b, s.eps, s.norm)
         qkv_dim = self.q_dim + 2 * self.kv_dim
-        y = ops.linear(hn, L.w1, L.b1, act=s.act, act_start=qkv_dim)        # [k | v | q | act(up)]
+        with trace("gemm_qkv_up"):
+            y = ops.linear(hn, L.w1, L.b1, act=s.act, act_start=qkv_dim)    # [k | v | q | act(up)]
         k_off, v_off, q_off = 0, self.kv_dim, 2 * self.kv_dim
-        ops.rope_kv_write(y, batch.positions, batch.slot_mapping, kc, vc, self.hq, self.hkv, self.d, s.rotary_dim,
-                          s.rope, s.rope_base, q_off, k_off, v_off)
-        ops.attention(y, y, batch, kc, vc, self.hq, self.hkv, self.d, s.scale, q_off, k_off, v_off, out_off=q_off)
-        out = ops.linear(y[:, q_off:], L.w2, L.b2, comm=self.comm)           # one GEMM + one all-reduce
+        with trace("rope_kv_write"):
+            ops.rope_kv_write(y, batch.positions, batch.slot_mapping, kc, vc, self.hq, self.hkv, self.d, s.rotary_dim,
+                              s.rope, s.rope_base, q_off, k_off, v_off)
+        with trace("attention"):
+            ops.attention(y, y, batch, kc, vc, self.hq, self.hkv, self.d, s.scale, q_off, k_off, v_off, out_off=q_off)
+        with trace("gemm_out_down_allreduce"):
+            out = ops.linear(y[:, q_off:], L.w2, L.b2, comm=self.comm)       # one GEMM + one all-reduce
         return out, resid
 
     def forward_hidden(self, batch: BatchInput, kv) -> torch.Tensor:
@@ -196,10 +202,12 @@ class DecoderLM(nn.Module):
 
         Vocab-parallel head GEMM on the selected rows only (the reference runs it on all S
         positions, quirk Q11) followed by one all-gather (reference N3, layers.py:131-135)."""
-        local = ops.linear(hidden_rows, self.w_head, self.b_head, out_dtype=torch.float32)
+        with trace("lm_head"):
+            local = ops.linear(hidden_rows, self.w_head, self.b_head, out_dtype=torch.float32)
         if self.tp == 1:
             return local
-        return self.comm.all_gather_cat(local, dim=-1)
+        with trace("logits_all_gather"):
+            return self.comm.all_gather_cat(local, dim=-1)
 
     def forward(self, batch: BatchInput, kv, last_only: bool = True) -> torch.Tensor:
         h = self.forward_hidden(batch, kv)

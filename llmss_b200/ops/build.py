@@ -21,13 +21,15 @@ OBJ_DIR = ROOT / "build" / "obj"
 LIB_DIR = ROOT / "llmss_b200" / "_C"
 LIB_PATH = LIB_DIR / "libllmss_b200.so"
 
-NVCC_FLAGS = [
+BASE_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
     "--expt-relaxed-constexpr",
-    "-I", str(ROOT / "include"), "-I", str(CSRC),
 ]
+# include paths are location dependent and must not enter the staleness digest: the tree (with its
+# prebuilt .so) is copied to other machines under a different root.
+NVCC_FLAGS = BASE_FLAGS + ["-I", str(ROOT / "include"), "-I", str(CSRC)]
 
 
 def _nvcc() -> str:
@@ -43,7 +45,7 @@ def sources():
 
 def _digest(src: Path) -> str:
     h = hashlib.sha256()
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(BASE_FLAGS).encode())
     h.update(src.read_bytes())
     for inc in sorted(list(CSRC.glob("*.cuh")) + list((ROOT / "include").glob("*.h"))):
         h.update(inc.read_bytes())
@@ -78,8 +80,22 @@ def is_current() -> bool:
 def build_library(verbose: bool = False, force: bool = False) -> Path:
     if not force and is_current():  # e.g. on the GPU box: the .so travelled with the tree
         return LIB_PATH
-    OBJ_DIR.mkdir(parents=True, exist_ok=True)
     LIB_DIR.mkdir(parents=True, exist_ok=True)
+    # one builder at a time (torchrun starts N ranks at once); the others wait, then see a current library
+    import fcntl
+
+    with open(LIB_DIR / ".build.lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():
+                return LIB_PATH
+            return _build_locked(verbose, force)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool, force: bool) -> Path:
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
     if force:
         for o in OBJ_DIR.glob("*.o"):
             o.unlink()
@@ -88,12 +104,14 @@ def build_library(verbose: bool = False, force: bool = False) -> Path:
         objs = list(ex.map(lambda s: _compile(s, verbose), srcs))
     stamp = LIB_DIR / "build.stamp"
     want = tree_digest()
-    cmd = [_nvcc(), "-shared", "-o", str(LIB_PATH), *map(str, objs)]
+    tmp = LIB_PATH.with_suffix(f".so.tmp{os.getpid()}")
+    cmd = [_nvcc(), "-shared", "-o", str(tmp), *map(str, objs)]
     if verbose:
         print("[build]", " ".join(cmd), flush=True)
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp, LIB_PATH)  # atomic: a concurrent dlopen never sees a half-written file
     stamp.write_text(want)
     return LIB_PATH
 

@@ -36,9 +36,22 @@ LLMSS_API const char* llmss_last_error() { return g_err; }
 LLMSS_API int llmss_version() { return 100; }
 
 // ---------------------------------------------------------------- symmetric memory plumbing
-LLMSS_API int llmss_symm_alloc(size_t bytes, void** ptr) {
+namespace {
+__global__ void fill_u32_kernel(uint32_t* p, size_t n, uint32_t v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+}  // namespace
+
+// One region per rank: flags (zeroed) + Lamport area (filled with the sentinel) + bulk area.
+LLMSS_API int llmss_symm_alloc(size_t buf_bytes, size_t lam_bytes, void** ptr) {
+  const size_t bytes = kSymmDataOffset + 2 * lam_bytes + 2 * buf_bytes;
+  LLMSS_REQUIRE(lam_bytes % 16 == 0 && buf_bytes % 16 == 0, "symm_alloc: sizes must be multiples of 16");
   LLMSS_CHECK_CUDA(cudaMalloc(ptr, bytes));
   LLMSS_CHECK_CUDA(cudaMemset(*ptr, 0, bytes));
+  if (lam_bytes > 0) {
+    fill_u32_kernel<<<256, 256>>>(reinterpret_cast<uint32_t*>((char*)*ptr + kSymmDataOffset), 2 * lam_bytes / 4, kLamSentinel);
+    LLMSS_CHECK_CUDA(cudaGetLastError());
+  }
   LLMSS_CHECK_CUDA(cudaDeviceSynchronize());
   return 0;
 }
@@ -63,11 +76,14 @@ LLMSS_API int llmss_ipc_close(void* ptr) {
   LLMSS_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
   return 0;
 }
-LLMSS_API size_t llmss_symm_region_bytes(size_t buf_bytes) { return kSymmDataOffset + 2 * buf_bytes; }
+LLMSS_API size_t llmss_symm_region_bytes(size_t buf_bytes, size_t lam_bytes) {
+  return kSymmDataOffset + 2 * lam_bytes + 2 * buf_bytes;
+}
 
 // Build the by-value descriptor the kernels take.  `peer_bases[r]` is the mapping of rank
 // r's region in this process (peer_bases[rank] = the local allocation).
-LLMSS_API int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, SymmWs** out) {
+LLMSS_API int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, size_t lam_bytes,
+                                 SymmWs** out) {
   LLMSS_REQUIRE(nranks >= 1 && nranks <= kSymmMaxRanks, "symm_create: nranks=%d unsupported (max %d)", nranks,
                 kSymmMaxRanks);
   SymmWs* ws = new SymmWs();
@@ -76,6 +92,7 @@ LLMSS_API int llmss_symm_create(int rank, int nranks, void* const* peer_bases, s
   ws->rank = rank;
   ws->nranks = nranks;
   ws->buf_bytes = buf_bytes;
+  ws->lam_bytes = lam_bytes;
   uint32_t* ctl = nullptr;
   LLMSS_CHECK_CUDA(cudaMalloc(&ctl, 256));
   LLMSS_CHECK_CUDA(cudaMemset(ctl, 0, 256));
@@ -123,10 +140,12 @@ __device__ __forceinline__ void accum8<float>(float (&acc)[8], const uint4& raw)
 }
 
 // ---- one-shot all-reduce: every rank pushes its whole input to every peer, then sums locally.
-// Latency-optimal for decode-size messages (one NVLink round trip).  `nvec` = 16-byte vectors.
+// Latency-optimal for decode-size messages: self-validating vectors (symm.cuh), so the whole
+// collective is one NVLink one-way trip -- no flags, no fences, no block barriers.
 template <typename T>
 __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(SymmWs ws, const uint4* __restrict__ in,
                                                                      uint4* __restrict__ out, int64_t nvec) {
+  constexpr int EB = std::is_same<T, float>::value ? 4 : 2;
   const uint32_t e = *ws.epoch + 1;
   const int par = e & 1;
   const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
@@ -134,27 +153,18 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(SymmWs ws, 
 
   // push my chunk into slot [rank] of every peer's buffer
   for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
-    const uint4 val = in[v];
+    const uint4 val = lam_sanitize<EB>(in[v]);
 #pragma unroll 1
     for (int p = 1; p < ws.nranks; ++p) {
       const int peer = (ws.rank + p) % ws.nranks;
-      symm_buf<uint4>(ws, peer, par)[(int64_t)ws.rank * nvec + v] = val;
+      symm_lam<uint4>(ws, peer, par)[(int64_t)ws.rank * nvec + v] = val;
     }
   }
-  __syncthreads();
-  if (threadIdx.x == 0) __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x < ws.nranks && threadIdx.x != ws.rank)
-    st_release_sys(symm_flag(ws, threadIdx.x, 0, blockIdx.x) + ws.rank, e);
-  if (threadIdx.x < ws.nranks && threadIdx.x != ws.rank)
-    wait_flag_ge(symm_flag(ws, ws.rank, 0, blockIdx.x) + threadIdx.x, e, 1);
-  __syncthreads();
-
-  const uint4* mine = symm_buf<uint4>(ws, ws.rank, par);
+  uint4* mine = symm_lam<uint4>(ws, ws.rank, par);
   for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int r = 0; r < ws.nranks; ++r) {  // fixed order -> bit-identical on all ranks
-      const uint4 raw = (r == ws.rank) ? in[v] : ld_cg_v4(mine + (int64_t)r * nvec + v);
+      const uint4 raw = (r == ws.rank) ? lam_sanitize<EB>(in[v]) : lam_take(mine + (int64_t)r * nvec + v, 1);
       accum8<T>(acc, raw);
     }
     uint4 o;
@@ -291,11 +301,14 @@ LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, 
     if (in != out) LLMSS_CHECK_CUDA(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice, stream));
     return 0;
   }
-  if (algo == 0) algo = (bytes <= (int64_t)(1 << 20) || nvec % ws->nranks != 0) ? 1 : 2;
+  if (algo == 0)
+    algo = ((bytes <= (int64_t)(1 << 20) && (size_t)(bytes * ws->nranks) <= ws->lam_bytes) || nvec % ws->nranks != 0) ? 1 : 2;
   if (algo == 2 && nvec % ws->nranks != 0) algo = 1;
+  if (algo == 0) {}
   const int64_t need = (algo == 1) ? bytes * ws->nranks : bytes * 2;
-  LLMSS_REQUIRE((size_t)need <= ws->buf_bytes, "allreduce: message of %lld bytes needs %lld bytes of workspace (have %zu)",
-                (long long)bytes, (long long)need, ws->buf_bytes);
+  const size_t have = (algo == 1) ? ws->lam_bytes : ws->buf_bytes;
+  LLMSS_REQUIRE((size_t)need <= have, "allreduce: message of %lld bytes needs %lld bytes of workspace (have %zu)",
+                (long long)bytes, (long long)need, have);
   SymmWs w = *ws;
   if (algo == 1) {
     const int grid = pick_grid(nvec, 128);

@@ -416,19 +416,10 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         const int n_pass = a.ar ? 2 : 1;
 #pragma unroll 1
         for (int pass = 0; pass < n_pass; ++pass) {
-          if (pass == 1) {
-            if (full_tile) {
-              tcgen05_fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(&tempty_bar[as]);
-            }
-            __threadfence_system();
-            epi_bar();
-            if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
-              st_release_sys(symm_flag(a.ws, epi_tid, 0, sg.tile) + a.ws.rank, epoch);
-            if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
-              wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, sg.tile) + epi_tid, epoch, 31);
-            epi_bar();
+          if (pass == 1 && full_tile) {
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[as]);
           }
 #pragma unroll 1
           for (int cg = 0; cg < NG; ++cg) {
@@ -469,21 +460,22 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
               }
               if (a.ar) {
                 // round to T, one 16-byte vector per thread per group, tile-blocked + coalesced
-                const uint4 vec = pack8<T>(v);
+                const uint4 vec = lam_sanitize<2>(pack8<T>(v));
 #pragma unroll 1
                 for (int p = 0; p < a.ws.nranks; ++p) {
                   const int peer = (a.ws.rank + p) % a.ws.nranks;
-                  *reinterpret_cast<uint4*>(symm_buf<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                  *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
                 }
                 continue;
               }
             } else {
-              const uint8_t* mine = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
+              uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
 #pragma unroll
               for (int j = 0; j < 8; ++j) v[j] = 0.f;
               for (int r = 0; r < a.ws.nranks; ++r) {  // rank order: bit-identical on every rank
                 float t8[8];
-                unpack8<T>(ld_cg_u4(mine + (size_t)r * ar_slot_bytes + xoff), t8);
+                // self-validating vector: wait for it, re-arm the slot (no flags, no fences)
+                unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)r * ar_slot_bytes + xoff), 31), t8);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[j] += t8[j];
               }
@@ -636,16 +628,6 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     const int n_pass = a.ar ? 2 : 1;
 #pragma unroll 1
     for (int pass = 0; pass < n_pass; ++pass) {
-      if (pass == 1) {
-        __threadfence_system();
-        epi_bar();
-        const int slot = tile * S + r;  // one flag slot per (tile, slice): the same CTA owns it on every rank
-        if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
-          st_release_sys(symm_flag(a.ws, epi_tid, 0, slot) + a.ws.rank, epoch);
-        if (epi_tid < a.ws.nranks && epi_tid != a.ws.rank)
-          wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, slot) + epi_tid, epoch, 43);
-        epi_bar();
-      }
 #pragma unroll 1
       for (int it = epi_tid; it < per; it += 128) {
         const int item = r * per + it;
@@ -664,19 +646,19 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
             v[4] += hi.x; v[5] += hi.y; v[6] += hi.z; v[7] += hi.w;
           }
           if (a.ar) {
-            const uint4 vec = pack8<T>(v);
+            const uint4 vec = lam_sanitize<2>(pack8<T>(v));
 #pragma unroll 1
             for (int p = 0; p < a.ws.nranks; ++p) {
               const int peer = (a.ws.rank + p) % a.ws.nranks;
-              *reinterpret_cast<uint4*>(symm_buf<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+              *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
             }
             continue;
           }
         } else {
-          const uint8_t* mine = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
+          uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
           for (int q = 0; q < a.ws.nranks; ++q) {  // rank order: bit-identical on every rank
             float t8[8];
-            unpack8<T>(ld_cg_u4(mine + (size_t)q * ar_slot_bytes + xoff), t8);
+            unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)q * ar_slot_bytes + xoff), 43), t8);
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] += t8[j];
           }
@@ -874,8 +856,8 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
   if (ar) {
     LLMSS_REQUIRE(p.tiles * (p.split > 0 ? p.split : 1) <= kSymmMaxSlots,
                   "gemm: %d tiles exceed the %d flag slots of the symmetric workspace", p.tiles, kSymmMaxSlots);
-    LLMSS_REQUIRE((size_t)p.ar_bytes <= ws->buf_bytes, "gemm: fused all-reduce needs %lld bytes of symmetric buffer (have %zu)",
-                  (long long)p.ar_bytes, ws->buf_bytes);
+    LLMSS_REQUIRE((size_t)p.ar_bytes <= ws->lam_bytes, "gemm: fused all-reduce needs %lld bytes of Lamport buffer (have %zu)",
+                  (long long)p.ar_bytes, ws->lam_bytes);
   }
   CUtensorMap tw, tx;
   if (int e = make_tmap(&tw, w, dtype, N, K, ldw, BM)) return e;

@@ -13,14 +13,65 @@ struct SymmWs {
   char* peer_base[kSymmMaxRanks];  // this process' mapping of every rank's region
   uint32_t* epoch;                 // device-local: epoch of the last completed call
   uint32_t* ticket;                // device-local: CTAs finished in the current call
-  size_t buf_bytes;                // bytes per parity buffer
+  size_t buf_bytes;                // bytes per parity buffer of the flag-synchronised (bulk) area
+  size_t lam_bytes;                // bytes per parity buffer of the self-validating (Lamport) area
   int rank, nranks;
 };
 
-// region layout:  [flag set 0][flag set 1][data parity 0 : buf_bytes][data parity 1 : buf_bytes]
+// region layout:  [flag set 0][flag set 1][lamport parity 0][lamport parity 1][bulk parity 0][bulk parity 1]
 template <typename V>
 __device__ __forceinline__ V* symm_buf(const SymmWs& ws, int rank, int parity) {
-  return reinterpret_cast<V*>(ws.peer_base[rank] + kSymmDataOffset + (size_t)parity * ws.buf_bytes);
+  return reinterpret_cast<V*>(ws.peer_base[rank] + kSymmDataOffset + 2 * ws.lam_bytes + (size_t)parity * ws.buf_bytes);
+}
+template <typename V>
+__device__ __forceinline__ V* symm_lam(const SymmWs& ws, int rank, int parity) {
+  return reinterpret_cast<V*>(ws.peer_base[rank] + kSymmDataOffset + (size_t)parity * ws.lam_bytes);
+}
+
+// ---- self-validating ("Lamport") exchange for latency-critical messages ----------------------
+// The Lamport area is kept filled with a sentinel word that a sender never emits (16-bit payloads:
+// -0.0 halves are rewritten to +0.0; fp32 payloads: that exact denormal is rewritten to 0).  A
+// receiver spins on the 16-byte vector itself until none of its words is the sentinel, consumes it
+// and puts the sentinel back.  No flags, no fences, one NVLink one-way latency.  Every pushed vector
+// is read (and re-armed) by exactly one thread; parity double-buffering keeps call n+1's pushes away
+// from call n's vectors (a peer can be at most one call ahead, see comm.cu).
+constexpr uint32_t kLamSentinel = 0x80008000u;
+template <int ELEM_BYTES>
+__device__ __forceinline__ uint32_t lam_sanitize_word(uint32_t w) {
+  if constexpr (ELEM_BYTES == 2) {
+    if ((w & 0x0000FFFFu) == 0x00008000u) w &= 0xFFFF0000u;
+    if ((w & 0xFFFF0000u) == 0x80000000u) w &= 0x0000FFFFu;
+    return w;
+  } else {
+    return w == kLamSentinel ? 0u : w;
+  }
+}
+template <int ELEM_BYTES>
+__device__ __forceinline__ uint4 lam_sanitize(uint4 v) {
+  v.x = lam_sanitize_word<ELEM_BYTES>(v.x);
+  v.y = lam_sanitize_word<ELEM_BYTES>(v.y);
+  v.z = lam_sanitize_word<ELEM_BYTES>(v.z);
+  v.w = lam_sanitize_word<ELEM_BYTES>(v.w);
+  return v;
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+// Wait for a vector pushed by a peer, re-arm the slot, return the payload.
+__device__ __forceinline__ uint4 lam_take(uint4* slot, int tag) {
+  SpinGuard g;
+  uint4 v = ld_relaxed_sys_v4(slot);
+  while (v.x == kLamSentinel || v.y == kLamSentinel || v.z == kLamSentinel || v.w == kLamSentinel) {
+    if (!g.ok()) spin_timeout_trap("lamport vector wait", tag, 0);
+    v = ld_relaxed_sys_v4(slot);
+  }
+  *slot = make_uint4(kLamSentinel, kLamSentinel, kLamSentinel, kLamSentinel);
+  return v;
 }
 // &flag[set][slot][0] inside rank `rank`'s region; index by source rank.
 __device__ __forceinline__ uint32_t* symm_flag(const SymmWs& ws, int rank, int set, int slot) {

@@ -27,13 +27,14 @@ const char* llmss_last_error(void);
 int llmss_version(void);
 
 /* ---- symmetric memory (replaces c10d/NCCL bring-up for the hot path; dist.py:44-73) ---- */
-int llmss_symm_alloc(size_t bytes, void** ptr);
+int llmss_symm_alloc(size_t buf_bytes, size_t lam_bytes, void** ptr); /* flags + Lamport area + bulk area */
 int llmss_symm_free(void* ptr);
 int llmss_ipc_get_handle(void* ptr, unsigned char* out64);
 int llmss_ipc_open_handle(const unsigned char* in64, void** ptr);
 int llmss_ipc_close(void* ptr);
-size_t llmss_symm_region_bytes(size_t buf_bytes);
-int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, llmss_symm_t** out);
+size_t llmss_symm_region_bytes(size_t buf_bytes, size_t lam_bytes);
+int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, size_t lam_bytes,
+                      llmss_symm_t** out);
 int llmss_symm_destroy(llmss_symm_t* ws);
 int llmss_symm_epoch(llmss_symm_t* ws, uint32_t* out_host);
 

@@ -46,7 +46,7 @@ def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start:
         symm = comm.symm
         if symm is not None:
             plan = cu.gemm_plan(x.shape[0], w.shape[0], x.shape[1], symm.nranks)
-            if plan.ar_bytes <= symm.buf_bytes and plan.tiles <= 2048:
+            if plan.ar_bytes <= symm.lam_bytes and plan.tiles <= 2048:
                 return cu.linear(x, w, bias, ACT_NONE, False, 0, residual, None, symm=symm)
         y = cu.linear(x, w, None, ACT_NONE, False, 0, None, None)
         comm.all_reduce(y)

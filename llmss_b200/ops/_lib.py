@@ -24,13 +24,13 @@ class GemmPlan(C.Structure):
 _SIGS = {
     "llmss_last_error": (C.c_char_p, []),
     "llmss_version": (c_int, []),
-    "llmss_symm_alloc": (c_int, [c_size_t, C.POINTER(c_void_p)]),
+    "llmss_symm_alloc": (c_int, [c_size_t, c_size_t, C.POINTER(c_void_p)]),
     "llmss_symm_free": (c_int, [c_void_p]),
     "llmss_ipc_get_handle": (c_int, [c_void_p, C.c_char_p]),
     "llmss_ipc_open_handle": (c_int, [C.c_char_p, C.POINTER(c_void_p)]),
     "llmss_ipc_close": (c_int, [c_void_p]),
-    "llmss_symm_region_bytes": (c_size_t, [c_size_t]),
-    "llmss_symm_create": (c_int, [c_int, c_int, C.POINTER(c_void_p), c_size_t, C.POINTER(c_void_p)]),
+    "llmss_symm_region_bytes": (c_size_t, [c_size_t, c_size_t]),
+    "llmss_symm_create": (c_int, [c_int, c_int, C.POINTER(c_void_p), c_size_t, c_size_t, C.POINTER(c_void_p)]),
     "llmss_symm_destroy": (c_int, [c_void_p]),
     "llmss_symm_epoch": (c_int, [c_void_p, C.POINTER(C.c_uint32)]),
     "llmss_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),

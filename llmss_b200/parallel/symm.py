@@ -19,17 +19,17 @@ _DT = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
 
 
 class SymmetricWorkspace:
-    def __init__(self, group, device: torch.device, max_bytes: int = 32 << 20):
+    def __init__(self, group, device: torch.device, max_bytes: int = 32 << 20, lamport_bytes: int = 16 << 20):
         lib = _lib.load()
         self.group = group
         self.rank = group.rank()
         self.nranks = group.size()
         self.device = device
-        self.buf_bytes = int(max_bytes)
-        region = lib.llmss_symm_region_bytes(self.buf_bytes)
+        self.buf_bytes = int(max_bytes)          # flag-synchronised bulk area (two-shot all-reduce, all-gather)
+        self.lam_bytes = int(lamport_bytes)      # self-validating low-latency area (one-shot AR, fused GEMM+AR)
         with torch.cuda.device(device):
             base = C.c_void_p()
-            _lib.check(lib.llmss_symm_alloc(region, C.byref(base)), "symm_alloc")
+            _lib.check(lib.llmss_symm_alloc(self.buf_bytes, self.lam_bytes, C.byref(base)), "symm_alloc")
             self._local = base
             hbuf = C.create_string_buffer(64)
             _lib.check(lib.llmss_ipc_get_handle(base, hbuf), "ipc_get_handle")
@@ -46,7 +46,8 @@ class SymmetricWorkspace:
                     bases[r] = p.value
                     self._opened.append(p)
             h = C.c_void_p()
-            _lib.check(lib.llmss_symm_create(self.rank, self.nranks, bases, self.buf_bytes, C.byref(h)), "symm_create")
+            _lib.check(lib.llmss_symm_create(self.rank, self.nranks, bases, self.buf_bytes, self.lam_bytes, C.byref(h)),
+                       "symm_create")
             self.handle = h
         # everyone has mapped everyone before the first kernel touches a peer
         dist.barrier(group=group, device_ids=[device.index])
@@ -56,9 +57,11 @@ class SymmetricWorkspace:
         nbytes = x.numel() * x.element_size()
         if x.dtype not in _DT or not x.is_contiguous() or nbytes % 16 or x.data_ptr() % 16:
             return False
-        one_shot = nbytes <= (1 << 20) or (nbytes // 16) % self.nranks != 0
-        need = nbytes * self.nranks if one_shot else nbytes * 2
-        return need <= self.buf_bytes
+        if nbytes <= (1 << 20) and nbytes * self.nranks <= self.lam_bytes:
+            return True  # one-shot (Lamport area)
+        if (nbytes // 16) % self.nranks != 0:
+            return nbytes * self.nranks <= self.lam_bytes
+        return nbytes * 2 <= self.buf_bytes  # two-shot (bulk area)
 
     def can_all_gather(self, x: torch.Tensor) -> bool:
         nbytes = x.numel() * x.element_size()

@@ -43,7 +43,7 @@ def main():
                 nbytes = n * torch.empty((), dtype=dtype).element_size()
                 if algo == 2 and (nbytes // 16) % world != 0:
                     continue
-                if (algo == 1 and nbytes * world > symm.buf_bytes) or (algo == 2 and nbytes * 2 > symm.buf_bytes):
+                if (algo == 1 and nbytes * world > symm.lam_bytes) or (algo == 2 and nbytes * 2 > symm.buf_bytes):
                     continue
                 torch.manual_seed(1000 + rank)
                 x = torch.randn(n, device=dev, dtype=dtype)
@@ -90,7 +90,7 @@ def main():
             dist.all_reduce(want)
             want = want + bias.float() + res.float()
             plan = cu.gemm_plan(M, N, K, world)
-            if plan.ar_bytes > symm.buf_bytes:
+            if plan.ar_bytes > symm.lam_bytes:
                 continue
             for rep in range(3):
                 y = cu.linear(xr, wr, bias, residual=res, symm=symm)

@@ -240,6 +240,7 @@ def run_ours(args, rank, world, local):
         "latency": {"ttft_p50_ms": round(1e3 * statistics.median(ttfts), 2), "prefill_total_ms": round(1e3 * prefill_s, 2),
                     "tpot_p50_ms": round(1e3 * statistics.median(step_times), 4)},
         "load_s": round(load_s, 1),
+        "attn_split_tuning": runner.tuning_log.get(runner._bucket(B)),
     }
     if rank == 0:
         print(json.dumps(out), flush=True)

@@ -326,6 +326,9 @@ LLMSS_API int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int m
   }
 #undef LLMSS_OCC
   if (occ < 1) occ = 1;
+  // Heuristic: the split that fills whole waves of resident CTAs (>= 64 tokens per split), with a small
+  // penalty per extra split for the partial write + combine pass.  The engine refines this by timing the
+  // candidates on the real shape when it captures a decode graph (ModelRunner.autotune_decode_splits).
   const double cap = (double)sms * occ;
   const int max_s = max_kv / 64 > 1 ? (max_kv / 64 < 32 ? max_kv / 64 : 32) : 1;
   int best = 1;
@@ -333,7 +336,6 @@ LLMSS_API int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int m
   for (int sp = 1; sp <= max_s; ++sp) {
     const double waves = items * (double)sp / cap;
     const double full = waves < 1.0 ? 1.0 : (double)(long long)(waves + 0.999999);
-    // small penalty per split for the partial write + combine pass
     const double eff = waves / full - 0.004 * (sp - 1);
     if (eff > best_eff + 1e-9) { best_eff = eff; best = sp; }
   }

@@ -1,0 +1,425 @@
+// K8 attn_prefill: causal varlen flash-attention forward on the 5th-generation tensor cores.
+//
+// Replaces the reference's prefill attention (cuBLAS QK^T into a materialised
+// [B,h,S,T] fp32 score tensor, where-mask from a [max_pos,max_pos] bool buffer, softmax, cuBLAS PV;
+// gptj_modeling.py:128-169, gpt_bigcode_modeling.py:170-246) with one kernel that never
+// materialises S^2 data:
+//
+//   one CTA = 128 queries of one (sequence, q head); it walks the causal range of KV tiles.
+//   warp 0      TMA producer: Q once, then K_j / V_j tiles (2-stage ring), 128B-swizzled
+//   warp 1      one thread issues tcgen05.mma:  S = Q K_j^T   (A,B K-major)      -> TMEM [128 x BN] fp32
+//                                               O += P_j V_j  (B = V, MN-major)  -> TMEM [128 x D]  fp32
+//   warps 2-5   one thread per query row: tcgen05.ld its S row, scale + causal mask, online softmax in
+//               fp32 (no shuffles: the row is thread-private), rescale O in TMEM only when the running
+//               max moved, write P_j (bf16/fp16) into shared memory in the UMMA K-major swizzled layout.
+//   q, k, v are column ranges of the packed QKV activation (row stride ld*), so the kernel reads
+//   the GEMM output in place; `out` may alias q (the fused GPT-J block writes the context over q).
+//   GQA/MQA: kv head = q head / (hq / hkv).
+#include "common.cuh"
+
+#include <cuda.h>
+#include <string.h>
+
+namespace {
+
+constexpr int BM = 128;  // queries per CTA
+constexpr int kThreads = 192;
+
+template <int D>
+struct PCfg {
+  static constexpr int BN = (D >= 256) ? 64 : 128;          // keys per tile
+  static constexpr int KV_STAGES = 2;
+  static constexpr int Q_BYTES = BM * D * 2;
+  static constexpr int K_BYTES = BN * D * 2;
+  static constexpr int V_BYTES = BN * D * 2;
+  static constexpr int P_BYTES = BM * BN * 2;
+  static constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * (K_BYTES + V_BYTES) + P_BYTES + 1024 + 256;
+  static constexpr int TMEM_COLS = (BN + D <= 256) ? 256 : 512;  // S at column 0, O at column BN
+};
+
+struct PArgs {
+  const int* cu_seqlens;
+  void* out;
+  int64_t ldo;
+  int hq, hkv;
+  int q_col, k_col, v_col;  // first column of q / k / v inside the packed row (elements)
+  float scale_log2;
+  int dtype;
+};
+
+// MN-major (N contiguous) 128B-swizzled operand: rows are K (keys), 64 elements of N per 128-byte row;
+// LBO = distance between 64-element N chunks, SBO = distance between 8-row K groups.
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t idesc_f16(int fmt, int M, int N, int b_mn_major) {
+  return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  if constexpr (std::is_same<T, __half>::value) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  } else {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(kThreads, 1)
+attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PArgs a) {
+  using C = PCfg<D>;
+  constexpr int BN = C::BN;
+  constexpr int DSUB = D / 64;   // 64-column (128-byte) sub-tiles along head_dim
+  constexpr int NSUB = BN / 64;  // 64-key sub-tiles of P along the key dimension
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + C::Q_BYTES;
+  uint8_t* sV = sK + C::KV_STAGES * C::K_BYTES;
+  uint8_t* sP = sV + C::KV_STAGES * C::V_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BYTES);
+  uint64_t* bar_q = bars;
+  uint64_t* bar_kfull = bars + 1;       // [KV_STAGES]
+  uint64_t* bar_vfull = bars + 3;
+  uint64_t* bar_kempty = bars + 5;
+  uint64_t* bar_vempty = bars + 7;
+  uint64_t* bar_s = bars + 9;           // S_j ready (tcgen05.commit)
+  uint64_t* bar_p = bars + 10;          // P_j written (4 warp arrivals)
+  uint64_t* bar_o = bars + 11;          // PV_j retired (tcgen05.commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int seq = blockIdx.z, head = blockIdx.y;
+  const int seq_start = a.cu_seqlens[seq];
+  const int len = a.cu_seqlens[seq + 1] - seq_start;
+  const int q0 = blockIdx.x * BM;  // first query (position within the sequence) of this CTA
+  if (q0 >= len) return;           // uniform for the whole CTA
+  const int kvh = head / (a.hq / a.hkv);
+  const int kv_end = min(len, q0 + BM);        // causal: keys [0, kv_end)
+  const int n_tiles = (kv_end + BN - 1) / BN;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < C::KV_STAGES; ++s) {
+      mbar_init(&bar_kfull[s], 1);
+      mbar_init(&bar_vfull[s], 1);
+      mbar_init(&bar_kempty[s], 1);
+      mbar_init(&bar_vempty[s], 1);
+    }
+    mbar_init(bar_s, 1);
+    mbar_init(bar_p, 4);
+    mbar_init(bar_o, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tO = tmem_base + BN;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      const uint64_t pol = l2_policy_evict_last();
+      mbar_arrive_expect_tx(bar_q, C::Q_BYTES);
+      // the tensor-map box is [BN rows x 64 cols]; a 128-row Q sub-tile is BM / BN stacked boxes
+      // (the 128B-swizzle pattern repeats every 8 rows, so stacked boxes form one contiguous tile)
+#pragma unroll
+      for (int c = 0; c < DSUB; ++c)
+#pragma unroll
+        for (int h = 0; h < BM / BN; ++h)
+          tma_load_2d(sQ + c * (BM * 128) + h * (BN * 128), &tmap, bar_q, a.q_col + head * D + c * 64,
+                      seq_start + q0 + h * BN, pol);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int j = 0; j < n_tiles; ++j) {
+        const int row = seq_start + j * BN;
+        mbar_wait(&bar_kempty[stage], phase ^ 1, 50);
+        mbar_arrive_expect_tx(&bar_kfull[stage], C::K_BYTES);
+#pragma unroll
+        for (int c = 0; c < DSUB; ++c)
+          tma_load_2d(sK + stage * C::K_BYTES + c * (BN * 128), &tmap, &bar_kfull[stage], a.k_col + kvh * D + c * 64, row, pol);
+        mbar_wait(&bar_vempty[stage], phase ^ 1, 51);
+        mbar_arrive_expect_tx(&bar_vfull[stage], C::V_BYTES);
+#pragma unroll
+        for (int c = 0; c < DSUB; ++c)
+          tma_load_2d(sV + stage * C::V_BYTES + c * (BN * 128), &tmap, &bar_vfull[stage], a.v_col + kvh * D + c * 64, row, pol);
+        if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
+      const uint32_t idesc_s = idesc_f16(fmt, BM, BN, 0);  // S = Q K^T : both operands K-major
+      const uint32_t idesc_o = idesc_f16(fmt, BM, D, 1);   // O += P V  : B (= V) is MN-major
+      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
+      mbar_wait(bar_q, 0, 60);
+      int stage = 0;
+      uint32_t phase = 0;
+      auto issue_qk = [&](int st) {
+        const uint32_t k_addr = smem_u32(sK + st * C::K_BYTES);
+#pragma unroll
+        for (int c = 0; c < DSUB; ++c)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ss(tS, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
+                        umma_desc_k_sw128(k_addr + c * (BN * 128) + k * 32), idesc_s, (c | k) ? 1u : 0u);
+        umma_commit(bar_s);
+        umma_commit(&bar_kempty[st]);
+      };
+      // prologue: S_0
+      mbar_wait(&bar_kfull[0], 0, 61);
+      tcgen05_fence_after();
+      issue_qk(0);
+      for (int j = 0; j < n_tiles; ++j) {
+        // P_j is in shared memory and S_j has been consumed: issue PV_j, then S_{j+1} behind it
+        mbar_wait(bar_p, j & 1, 62);
+        mbar_wait(&bar_vfull[stage], phase, 63);
+        tcgen05_fence_after();
+        const uint32_t v_addr = smem_u32(sV + stage * C::V_BYTES);
+#pragma unroll
+        for (int c = 0; c < NSUB; ++c)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ss(tO, umma_desc_k_sw128(p_addr + c * (BM * 128) + k * 32),
+                        umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
+                        (j > 0 || c > 0 || k > 0) ? 1u : 0u);
+        umma_commit(bar_o);
+        umma_commit(&bar_vempty[stage]);
+        if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
+        if (j + 1 < n_tiles) {
+          mbar_wait(&bar_kfull[stage], phase, 64);
+          tcgen05_fence_after();
+          issue_qk(stage);
+        }
+      }
+    }
+  } else {
+    // ===================== softmax / correction / epilogue: one thread per query row =====================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;         // query row within the tile == TMEM lane
+    const int qpos = q0 + row;                   // position within the sequence
+    const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+    float m_run = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < n_tiles; ++j) {
+      mbar_wait(bar_s, j & 1, 70);
+      tcgen05_fence_after();
+      const int kbase = j * BN;
+      const bool diag = (kbase + BN - 1) > q0;   // some key of this tile may lie above the diagonal
+      // pass 1: row max
+      float m_tile = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tS + lane_off + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(r[i]) * a.scale_log2;
+          if (diag && (kbase + c * 32 + i) > qpos) s = -INFINITY;
+          m_tile = fmaxf(m_tile, s);
+        }
+      }
+      const float m_new = fmaxf(m_run, m_tile);
+      const float alpha = (m_run == -INFINITY) ? 0.f : exp2f(m_run - m_new);
+      // PV_{j-1} must have retired before O is rescaled and before P is overwritten
+      if (j > 0) {
+        mbar_wait(bar_o, (j - 1) & 1, 71);
+        tcgen05_fence_after();
+        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+#pragma unroll 1
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st_32x32b_x32(tO + lane_off + c * 32, r);
+          }
+          tmem_st_wait();
+        }
+      }
+      l_run *= alpha;
+      m_run = m_new;
+      // pass 2: p = exp2(s - m), row sum, P -> shared memory (K-major, 128B swizzle: chunk ^= row & 7)
+      float l_tile = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tS + lane_off + c * 32, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float s0 = __uint_as_float(r[i]) * a.scale_log2, s1 = __uint_as_float(r[i + 1]) * a.scale_log2;
+          if (diag && (kbase + c * 32 + i) > qpos) s0 = -INFINITY;
+          if (diag && (kbase + c * 32 + i + 1) > qpos) s1 = -INFINITY;
+          const float p0 = (m_new == -INFINITY) ? 0.f : exp2f(s0 - m_new);
+          const float p1 = (m_new == -INFINITY) ? 0.f : exp2f(s1 - m_new);
+          l_tile += p0 + p1;
+          pk[i >> 1] = pack2<T>(p0, p1);
+        }
+        // this 32-key chunk = 64 bytes = 4 x 16-byte chunks of the row inside sub-tile (c / 2)
+        uint8_t* sub = sP + (c >> 1) * (BM * 128) + row * 128;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int chunk = ((c & 1) * 4 + q) ^ (row & 7);
+          *reinterpret_cast<uint4*>(sub + chunk * 16) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        }
+      }
+      l_run += l_tile;
+      tcgen05_fence_before();
+      fence_proxy_async_smem();  // generic-proxy writes of P must be visible to the tensor-core (async) proxy
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p);
+    }
+    // epilogue: O / l -> out
+    mbar_wait(bar_o, (n_tiles - 1) & 1, 72);
+    tcgen05_fence_after();
+    const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
+    T* orow = reinterpret_cast<T*>(a.out) + (int64_t)(seq_start + qpos) * a.ldo + (int64_t)head * D;
+#pragma unroll 1
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
+      tmem_ld_wait();
+      if (qpos < len) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float f8[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f8[i] = __uint_as_float(r[q * 8 + i]) * inv_l;
+          *reinterpret_cast<uint4*>(orow + c * 32 + q * 8) = pack8<T>(f8);
+        }
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+template <typename T, int D>
+int launch_prefill(const CUtensorMap& tm, const PArgs& a, int num_seqs, int max_seqlen, cudaStream_t stream) {
+  using C = PCfg<D>;
+  static bool configured = false;
+  auto kern = attn_prefill_kernel<T, D>;
+  if (!configured) {
+    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured = true;
+  }
+  dim3 grid((max_seqlen + BM - 1) / BM, a.hq, num_seqs);
+  kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(tm, a);
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+// q / k / v: pointers to the first q / k / v element of row 0 inside ONE packed activation
+// (same base allocation, same row stride ld); out may alias q.  cu_seqlens: [num_seqs + 1] int32.
+LLMSS_API int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                 void* out, int64_t ldo, const int* cu_seqlens, int num_seqs, int max_seqlen,
+                                 int total_tokens, int hq, int hkv, int d, float scale, int dtype,
+                                 cudaStream_t stream) {
+  LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "attn_prefill: dtype must be f16/bf16");
+  LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_prefill: head_dim=%d unsupported (64/128/256)", d);
+  LLMSS_REQUIRE(hq % hkv == 0, "attn_prefill: hq=%d not a multiple of hkv=%d", hq, hkv);
+  LLMSS_REQUIRE(ldq == ldk && ldk == ldv, "attn_prefill: q, k, v must share one row stride (packed QKV activation)");
+  LLMSS_REQUIRE(ldo % 8 == 0 && ((uintptr_t)out % 16) == 0, "attn_prefill: output must be 16-byte aligned");
+  if (num_seqs == 0 || total_tokens == 0) return 0;
+  // one tensor map over the packed rows, based at the lowest of the three pointers
+  const char* base = (const char*)q;
+  if ((const char*)k < base) base = (const char*)k;
+  if ((const char*)v < base) base = (const char*)v;
+  const int64_t q_col = ((const char*)q - base) / 2, k_col = ((const char*)k - base) / 2, v_col = ((const char*)v - base) / 2;
+  int64_t width = q_col + (int64_t)hq * d;
+  if (k_col + (int64_t)hkv * d > width) width = k_col + (int64_t)hkv * d;
+  if (v_col + (int64_t)hkv * d > width) width = v_col + (int64_t)hkv * d;
+  LLMSS_REQUIRE(width <= ldq, "attn_prefill: q/k/v column ranges exceed the row stride");
+  LLMSS_REQUIRE(((uintptr_t)base % 16) == 0 && (ldq * 2) % 16 == 0 && q_col % 8 == 0 && k_col % 8 == 0 && v_col % 8 == 0,
+                "attn_prefill: packed activation must be 16-byte aligned");
+  PFN_encodeTiled enc = get_encode();
+  LLMSS_REQUIRE(enc != nullptr, "attn_prefill: cuTensorMapEncodeTiled entry point not available");
+  CUtensorMap tm;
+  cuuint64_t dims[2] = {(cuuint64_t)width, (cuuint64_t)total_tokens};
+  cuuint64_t strides[1] = {(cuuint64_t)ldq * 2};
+  const int bn = d >= 256 ? 64 : 128;
+  // one box shape serves Q (128 rows) and K/V (BN rows) only if they agree; use two loads of BN rows for Q when BN < 128
+  cuuint32_t box[2] = {64, (cuuint32_t)bn};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(&tm, dtype == LLMSS_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                   (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  LLMSS_REQUIRE(r == CUDA_SUCCESS, "attn_prefill: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  PArgs a;
+  memset(&a, 0, sizeof(a));
+  a.cu_seqlens = cu_seqlens;
+  a.out = out;
+  a.ldo = ldo;
+  a.hq = hq;
+  a.hkv = hkv;
+  a.q_col = (int)q_col;
+  a.k_col = (int)k_col;
+  a.v_col = (int)v_col;
+  a.scale_log2 = scale * 1.4426950408889634f;
+  a.dtype = dtype;
+#define LLMSS_PF(T_, D_) return launch_prefill<T_, D_>(tm, a, num_seqs, max_seqlen, stream)
+  if (dtype == LLMSS_F16) {
+    if (d == 64) LLMSS_PF(__half, 64);
+    if (d == 128) LLMSS_PF(__half, 128);
+    LLMSS_PF(__half, 256);
+  } else {
+    if (d == 64) LLMSS_PF(__nv_bfloat16, 64);
+    if (d == 128) LLMSS_PF(__nv_bfloat16, 128);
+    LLMSS_PF(__nv_bfloat16, 256);
+  }
+#undef LLMSS_PF
+}

@@ -64,6 +64,7 @@ struct GemmArgs {
   int out_f32;
   int act, act_start, gated;
   int epi;                // EPI_* flavour, derived from the flags above on the host
+  int aligned;            // stream-K kernel: cut CTA ranges at tile boundaries (no partial tiles)
   float* sk_ws;           // stream-K partial slots: [2 * grid][BN][128] fp32 (first / last segment of a CTA)
   uint32_t* sk_counters;  // [tiles], zero between launches
   int ar;                 // fused all-reduce over ws
@@ -86,10 +87,17 @@ __device__ __forceinline__ int cta_of(int64_t w, int64_t total, int G) { return 
 struct SegIter {
   int64_t w, w_end, total;
   int kb_total, G;
-  __device__ SegIter(int g, int G_, int tiles, int kb_total_) : kb_total(kb_total_), G(G_) {
+  // aligned: CTA ranges are cut at tile boundaries (pure data-parallel, no partial tiles) -- used when
+  // there are many tiles per CTA, where the one-tile imbalance is cheaper than the stream-K fix-up.
+  __device__ SegIter(int g, int G_, int tiles, int kb_total_, bool aligned = false) : kb_total(kb_total_), G(G_) {
     total = (int64_t)tiles * kb_total_;
-    w = cta_start(g, total, G_);
-    w_end = cta_start(g + 1, total, G_);
+    if (aligned) {
+      w = (((int64_t)g * tiles) / G_) * kb_total_;
+      w_end = (((int64_t)(g + 1) * tiles) / G_) * kb_total_;
+    } else {
+      w = cta_start(g, total, G_);
+      w_end = cta_start(g + 1, total, G_);
+    }
   }
   __device__ bool next(Segment& s) {
     if (w >= w_end) return false;
@@ -294,7 +302,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       const uint64_t pol_x = l2_policy_evict_last();   // activations are re-read by every tile
       int stage = 0;
       uint32_t phase = 0;
-      SegIter it(g, G, tiles, a.kb_total);
+      SegIter it(g, G, tiles, a.kb_total, a.aligned != 0);
       Segment sg;
       while (it.next(sg)) {
         const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
@@ -316,7 +324,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      SegIter it(g, G, tiles, a.kb_total);
+      SegIter it(g, G, tiles, a.kb_total, a.aligned != 0);
       Segment sg;
       while (it.next(sg)) {
         mbar_wait(&tempty_bar[as], aphase ^ 1, 20);
@@ -351,7 +359,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     const int epi_tid = threadIdx.x - 64;
     int as = 0;
     uint32_t aphase = 0;
-    SegIter it(g, G, tiles, a.kb_total);
+    SegIter it(g, G, tiles, a.kb_total, a.aligned != 0);
     Segment sg;
     const T* bias = reinterpret_cast<const T*>(a.bias);
     constexpr int NG = BN / 8;               // column groups per tile
@@ -619,7 +627,10 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
 
   if (warp >= 2) {
     const int epi_tid = threadIdx.x - 64;
-    const int per = NG * BM / S;                 // (column group, feature) items owned by this CTA
+    // (column group, feature) items owned by this CTA: warp-granular, the last CTA may own fewer
+    const int total_items = NG * BM;
+    const int per = ((total_items + S - 1) / S + 31) / 32 * 32;
+    const int my_items = max(0, min(per, total_items - r * per));
     const T* bias = reinterpret_cast<const T*>(a.bias);
     const int tiles = a.tiles_n * a.tiles_m;
     const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
@@ -629,7 +640,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
 #pragma unroll 1
     for (int pass = 0; pass < n_pass; ++pass) {
 #pragma unroll 1
-      for (int it = epi_tid; it < per; it += 128) {
+      for (int it = epi_tid; it < my_items; it += 128) {
         const int item = r * per + it;
         const int cg = item / BM, f = item % BM;
         const int n = tn * BM + f;
@@ -768,26 +779,65 @@ int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs&
   return 0;
 }
 
-// 0 = stream-K persistent kernel; 2/4/8 = cluster split-K factor.  LLMSS_GEMM_MODE=streamk|cluster forces one.
-int pick_cluster_split(int tiles, int kb_total, int bn, int sms) {
+// Largest cluster size (2..8) for which all `tiles` clusters are co-resident (one wave) and every CTA still
+// streams >= 2 k-blocks; 0 = use the stream-K persistent kernel.  LLMSS_GEMM_MODE=streamk|cluster forces one.
+template <typename T, int BN>
+int max_active_clusters(int split) {
+  static int cache[9] = {-1, -1, -1, -1, -1, -1, -1, -1, -1};
+  if (cache[split] >= 0) return cache[split];
+  using C = Cfg<BN>;
+  auto kern = gemm_cluster_kernel<T, BN>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(split * 64);
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = split;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  cache[split] = n;
+  return n;
+}
+
+int clusters_for(int dtype, int bn, int split) {
+#define LLMSS_MAC(T_)                                          \
+  switch (bn) {                                                \
+    case 16: return max_active_clusters<T_, 16>(split);        \
+    case 32: return max_active_clusters<T_, 32>(split);        \
+    case 64: return max_active_clusters<T_, 64>(split);        \
+    case 128: return max_active_clusters<T_, 128>(split);      \
+    default: return max_active_clusters<T_, 256>(split);       \
+  }
+  if (dtype == LLMSS_F16) { LLMSS_MAC(__half) }
+  LLMSS_MAC(__nv_bfloat16)
+#undef LLMSS_MAC
+}
+
+int pick_cluster_split(int tiles, int kb_total, int bn, int sms, int dtype) {
   static int forced = -1;
   if (forced < 0) {
     const char* e = getenv("LLMSS_GEMM_MODE");
     forced = (e == nullptr) ? 0 : (strcmp(e, "streamk") == 0 ? 1 : (strcmp(e, "cluster") == 0 ? 2 : 0));
   }
   if (forced == 1) return 0;
-  const int staging_bytes = BM * bn * 4;
-  if (staging_bytes > Cfg<16>::STAGES * 0 + 190 * 1024) return 0;  // accumulator must fit in the drained ring
-  int best = 0;
-  for (int s = 2; s <= 8; s *= 2) {
-    if (tiles * s > sms && forced != 2) break;
-    if (kb_total / s < 2) break;
-    best = s;
+  for (int s = 8; s >= 2; --s) {
+    if (kb_total / s < 2) continue;
+    if (forced != 2 && (tiles * s > sms || tiles > clusters_for(dtype, bn, s))) continue;
+    // stream-K uses every SM; take the cluster kernel only if it occupies at least ~70% of them
+    if (forced != 2 && tiles * s * 10 < sms * 7) return 0;
+    return s;
   }
-  if (forced == 2 && best == 0 && kb_total >= 2) best = 2;
-  // stream-K fills all SMs; prefer the cluster only when it occupies at least ~70% of them
-  if (forced != 2 && best > 0 && tiles * best * 10 < sms * 7) return 0;
-  return best;
+  return 0;
 }
 
 int pick_bn(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256; }
@@ -811,7 +861,13 @@ struct llmss_gemm_plan {
   int64_t ar_bytes;         // symmetric buffer bytes needed per parity when ar=1
 };
 
+LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype,
+                                     llmss_gemm_plan* p);
 LLMSS_API int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p) {
+  return llmss_gemm_plan_query2(M, N, K, nranks, elem_bytes, max_ctas, LLMSS_BF16, p);
+}
+LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype,
+                                     llmss_gemm_plan* p) {
   const int bn = pick_bn(M);
   const int tiles_n = (N + BM - 1) / BM, tiles_m = (M + bn - 1) / bn;
   const int tiles = tiles_n * tiles_m;
@@ -827,7 +883,7 @@ LLMSS_API int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_by
   p->bn = bn;
   p->tiles = tiles;
   p->kb_total = kb_total;
-  p->split = pick_cluster_split(tiles, kb_total, bn, sms);
+  p->split = pick_cluster_split(tiles, kb_total, bn, sms, dtype);
   if (p->split > 0) grid = (int64_t)tiles * p->split;
   p->grid = (int)grid;
   p->sk_ws_floats = p->split > 0 ? 0 : (int64_t)2 * grid * BM * bn;
@@ -850,8 +906,9 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
   const bool ar = (ws != nullptr && ws->nranks > 1);
   LLMSS_REQUIRE(!(ar && (gated || act != LLMSS_ACT_NONE || out_f32)), "gemm: fused all-reduce supports bias/residual epilogues only");
   llmss_gemm_plan p;
-  llmss_gemm_plan_query(M, N, K, ar ? ws->nranks : 1, 2, max_ctas, &p);
-  const bool need_sk = p.split == 0 && (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
+  llmss_gemm_plan_query2(M, N, K, ar ? ws->nranks : 1, 2, max_ctas, dtype, &p);
+  const bool aligned = p.split == 0 && p.tiles >= 4 * p.grid;    // many tiles per CTA: plain data-parallel
+  const bool need_sk = p.split == 0 && !aligned && (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
   LLMSS_REQUIRE(!need_sk || (sk_ws != nullptr && sk_counters != nullptr), "gemm: stream-K workspace required for this shape");
   if (ar) {
     LLMSS_REQUIRE(p.tiles * (p.split > 0 ? p.split : 1) <= kSymmMaxSlots,
@@ -872,6 +929,7 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
   a.bias = bias; a.residual = residual; a.ldr = ldr;
   a.out = out; a.ldo = ldo; a.out_f32 = out_f32;
   a.act = act; a.act_start = act_start; a.gated = gated;
+  a.aligned = aligned ? 1 : 0;
   a.epi = gated ? EPI_GATED : (out_f32 ? EPI_F32 : (act != LLMSS_ACT_NONE ? EPI_ACT : EPI_PLAIN));
   a.sk_ws = sk_ws; a.sk_counters = sk_counters;
   a.ar = ar ? 1 : 0;

@@ -46,13 +46,14 @@ int llmss_allgather(llmss_symm_t* ws, const void* in, void* out, int64_t bytes, 
 /* ---- K5/K1/K2 tcgen05 GEMM (+ fused all-reduce epilogue) (G3,G4,G9,G10,G12,G14; layers.py:62,175-179) ---- */
 typedef struct llmss_gemm_plan {
   int bn, tiles, kb_total, grid;
-  int split; /* 0 = stream-K persistent kernel, 2/4/8 = thread-block-cluster split-K */
+  int split; /* 0 = stream-K persistent kernel, 2..8 = thread-block-cluster split-K factor */
   int64_t sk_ws_floats;
   int64_t sk_counters;
   int64_t ar_bytes;
 } llmss_gemm_plan;
 int llmss_gemm_set_debug(unsigned long long* per_cta_stamps); /* profiling aid: 8 globaltimer stamps per CTA */
 int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p);
+int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype, llmss_gemm_plan* p);
 int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias, const void* residual,
                int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype, int out_f32, int act,
                int act_start, int gated, float* sk_ws, uint32_t* sk_counters, llmss_symm_t* ws, int max_ctas,
@@ -75,6 +76,11 @@ int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache, const voi
                       const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
                       float* scratch, int B, int hq, int hkv, int d, int block_size, float scale, int num_splits,
                       int dtype, llmss_stream_t stream);
+
+/* ---- K8 causal varlen prefill attention on tcgen05 (G7, G8, G17; gpt_bigcode_modeling.py:170-246) ---- */
+int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, void* out,
+                       int64_t ldo, const int* cu_seqlens, int num_seqs, int max_seqlen, int total_tokens, int hq,
+                       int hkv, int d, float scale, int dtype, llmss_stream_t stream);
 
 /* No counterpart in the reference (it has no native code and allocates freely through torch).
  * Same operation as llmss_attn_decode for hosts that cannot allocate: servers whose HBM is fully

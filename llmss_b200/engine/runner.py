@@ -74,6 +74,8 @@ class ModelRunner:
         self.use_graph = self.cuda if use_cuda_graph is None else (use_cuda_graph and self.cuda)
         self.graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self.launches_per_graph: Dict[int, int] = {}   # own-kernel launches captured per decode graph
+        self._tuned_splits: Dict[int, int] = {}
+        self.tuning_log: Dict[int, dict] = {}
         self.graph_pool = None
         self._setup_static(max_batch)
         self.stats = {"prefill_tokens": 0, "decode_steps": 0, "graph_replays": 0, "h2d_bytes": 0, "d2h_bytes": 0}
@@ -230,16 +232,57 @@ class ModelRunner:
     def _splits_for(self, Bp: int) -> int:
         if not self.cuda:
             return 1
+        if Bp in self._tuned_splits:
+            return self._tuned_splits[Bp]
         from ..ops import cuda_impl as cu
 
         return cu.decode_splits(Bp, self.core.hq, self.core.hkv, self.core.d, self.max_seq_len, self.dtype)
+
+    def autotune_decode_splits(self, Bp: int) -> int:
+        """Time the split-KV candidates of the decode-attention kernel on this runner's real shape
+        (batch bucket, heads per rank, current context length) and keep the fastest.  Read-only on the
+        KV cache; ~1 ms once per captured graph."""
+        c = self.core
+        if not self.cuda or c.d not in (64, 128, 256):
+            return 1
+        from ..ops import cuda_impl as cu
+
+        L = int(self.np_len.max()) + 32 if self.np_active.any() else self.max_seq_len // 2
+        L = max(64, min(L, self.max_seq_len))
+        nblk = -(-L // self.block_size)
+        dev = self.device
+        bt = (torch.arange(Bp * nblk, device=dev, dtype=torch.int32) % max(1, self.kv.num_blocks - 1) + 1).view(Bp, nblk)
+        sl = torch.full((Bp,), L, dtype=torch.int32, device=dev)
+        q = torch.randn(Bp, c.q_dim, device=dev, dtype=self.dtype)
+        out = torch.empty_like(q)
+        kc, vc = self.kv.k(0), self.kv.v(0)
+        base = cu.decode_splits(Bp, c.hq, c.hkv, c.d, L, self.dtype)
+        cands = sorted({s for s in (1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 24, base) if s <= max(1, L // 64)})
+        best, best_t = base, float("inf")
+        table = {}
+        for s_ in cands:
+            for _ in range(2):
+                cu.attn_decode(q, kc, vc, bt, sl, out, c.hq, c.hkv, c.d, c.spec.scale, s_)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(8):
+                cu.attn_decode(q, kc, vc, bt, sl, out, c.hq, c.hkv, c.d, c.spec.scale, s_)
+            b.record()
+            torch.cuda.synchronize()
+            t = a.elapsed_time(b)
+            table[s_] = round(t * 1e3 / 8, 1)
+            if t < best_t:
+                best, best_t = s_, t
+        self._tuned_splits[Bp] = best
+        self.tuning_log[Bp] = {"ctx": L, "us_per_call": table, "picked": best, "heuristic": base}
+        return best
 
     def capture(self, Bp: int):
         """Warm up and capture the decode graph for a padded batch size, on inert inputs
         (slot -1, seq_len 0: no cache writes), then restore the live step state."""
         if not self.use_graph or Bp in self.graphs:
             return
-        splits = self._splits_for(Bp)
+        splits = self.autotune_decode_splits(Bp)
         saved_in, saved_rng = self.d_in.clone(), self.d_rng.clone()
         inert = torch.zeros_like(self.h_in)
         MB = self.max_batch

@@ -46,7 +46,10 @@ def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start:
         symm = comm.symm
         if symm is not None:
             plan = cu.gemm_plan(x.shape[0], w.shape[0], x.shape[1], symm.nranks)
-            if plan.ar_bytes <= symm.lam_bytes and plan.tiles <= 2048:
+            # fused one-shot epilogue while the per-rank push stays small; beyond that the bandwidth-optimal
+            # two-shot all-reduce after a plain GEMM wins (measured crossover ~1 MB per rank at 8 GPUs)
+            push_bytes = x.shape[0] * w.shape[0] * x.element_size() * (symm.nranks - 1)
+            if plan.ar_bytes <= symm.lam_bytes and plan.tiles <= 2048 and push_bytes <= (6 << 20):
                 return cu.linear(x, w, bias, ACT_NONE, False, 0, residual, None, symm=symm)
         y = cu.linear(x, w, None, ACT_NONE, False, 0, None, None)
         comm.all_reduce(y)

@@ -56,7 +56,7 @@ _SIGS = {
 }
 _OPTIONAL = {
     "llmss_attn_prefill": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
-                                   c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p]),
+                                   c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p]),
 }
 
 

@@ -155,8 +155,8 @@ def attn_decode(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, hq, 
 def attn_prefill(q, k, v, out, cu_seqlens, num_seqs, max_seqlen, hq, hkv, d, scale):
     lib = _lib.load()
     rc = lib.llmss_attn_prefill(_ptr(q), q.stride(0), _ptr(k), k.stride(0), _ptr(v), v.stride(0), _ptr(out),
-                                out.stride(0), _ptr(cu_seqlens), num_seqs, max_seqlen, hq, hkv, d, float(scale),
-                                _DT[q.dtype], _stream())
+                                out.stride(0), _ptr(cu_seqlens), num_seqs, max_seqlen, q.shape[0], hq, hkv, d,
+                                float(scale), _DT[q.dtype], _stream())
     _lib.check(rc, "llmss_attn_prefill")
     _count()
 

@@ -44,5 +44,5 @@ def run(M, N, K):
               f"median {d2.median():.2f} max {d2.max():.2f} us | total median {d3.median():.2f} max {d3.max():.2f}")
 
 
-for shape in [(64, 4096, 2560), (16, 4096, 2560), (64, 28672, 4096), (64, 4096, 20480)]:
+for shape in [(64, 4096, 2560), (16, 4096, 2560), (64, 28672, 4096), (64, 4096, 20480), (8192, 4096, 4096), (2048, 12288, 4096)]:
     run(*shape)

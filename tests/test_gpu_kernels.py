@@ -237,3 +237,53 @@ print('MODES_OK' if bad == 0 else 'MODES_FAILED')
     env = dict(os.environ, LLMSS_GEMM_MODE=mode, PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
     assert "MODES_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+# ------------------------------------------------------------------ prefill attention (tcgen05)
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("hq,hkv,d", [(4, 4, 256), (8, 8, 128), (6, 6, 64), (8, 2, 128), (6, 1, 128)])
+def test_attn_prefill(hq, hkv, d, dtype):
+    cu = _cu()
+    torch.manual_seed(1)
+    lens = [1, 5, 128, 129, 300, 64, 700]
+    T = sum(lens)
+    pad = 64
+    W = pad + (hq + 2 * hkv) * d
+    qkv = torch.randn(T, W, device="cuda", dtype=dtype)
+    q_off, k_off, v_off = pad, pad + hq * d, pad + (hq + hkv) * d
+    out = torch.zeros(T, hq * d + 32, device="cuda", dtype=dtype)
+    cu_seq = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device="cuda")
+    scale = d ** -0.5
+    cu.attn_prefill(qkv[:, q_off:q_off + hq * d], qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d],
+                    out[:, :hq * d], cu_seq, len(lens), max(lens), hq, hkv, d, scale)
+    torch.cuda.synchronize()
+    g = hq // hkv
+    ref = torch.zeros(T, hq * d, device="cuda", dtype=torch.float32)
+    s0 = 0
+    for L in lens:
+        q = qkv[s0:s0 + L, q_off:q_off + hq * d].float().reshape(L, hq, d).permute(1, 0, 2)
+        k = qkv[s0:s0 + L, k_off:k_off + hkv * d].float().reshape(L, hkv, d).permute(1, 0, 2).repeat_interleave(g, 0)
+        v = qkv[s0:s0 + L, v_off:v_off + hkv * d].float().reshape(L, hkv, d).permute(1, 0, 2).repeat_interleave(g, 0)
+        s = (q @ k.transpose(1, 2)) * scale
+        s = s.masked_fill(torch.triu(torch.ones(L, L, dtype=torch.bool, device="cuda"), 1), float("-inf"))
+        ref[s0:s0 + L] = (torch.softmax(s, -1) @ v).permute(1, 0, 2).reshape(L, hq * d)
+        s0 += L
+    _close(out[:, :hq * d], ref, 3e-2, 3e-2, "attn_prefill")
+    assert out[:, hq * d:].abs().sum().item() == 0
+
+
+def test_attn_prefill_in_place_over_q():
+    """The fused GPT-J block lets the context overwrite q inside the packed activation."""
+    cu = _cu()
+    torch.manual_seed(2)
+    hq, hkv, d, lens = 4, 4, 256, [200, 333]
+    T = sum(lens)
+    qkv = torch.randn(T, (hq + 2 * hkv) * d, device="cuda", dtype=torch.bfloat16)
+    k_off, v_off, q_off = 0, hkv * d, 2 * hkv * d
+    ref = torch.empty(T, hq * d, device="cuda", dtype=torch.bfloat16)
+    cu_seq = torch.tensor([0, 200, 533], dtype=torch.int32, device="cuda")
+    args = (cu_seq, 2, 333, hq, hkv, d, d ** -0.5)
+    cu.attn_prefill(qkv[:, q_off:], qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d], ref, *args)
+    cu.attn_prefill(qkv[:, q_off:], qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d], qkv[:, q_off:], *args)
+    torch.cuda.synchronize()
+    assert torch.equal(qkv[:, q_off:], ref)

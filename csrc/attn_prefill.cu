@@ -34,7 +34,7 @@ struct PCfg {
   static constexpr int V_BYTES = BN * D * 2;
   static constexpr int P_BYTES = BM * BN * 2;
   static constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * (K_BYTES + V_BYTES) + P_BYTES + 1024 + 256;
-  static constexpr int TMEM_COLS = (BN + D <= 256) ? 256 : 512;  // S at column 0, O at column BN
+  static constexpr int TMEM_COLS = (2 * BN + D <= 256) ? 256 : 512;  // S0 at column 0, S1 at BN, O at 2*BN
 };
 
 struct PArgs {
@@ -75,6 +75,12 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU; 2^-inf = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <typename T>
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
   if constexpr (std::is_same<T, __half>::value) {
@@ -105,10 +111,10 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
   uint64_t* bar_vfull = bars + 3;
   uint64_t* bar_kempty = bars + 5;
   uint64_t* bar_vempty = bars + 7;
-  uint64_t* bar_s = bars + 9;           // S_j ready (tcgen05.commit)
-  uint64_t* bar_p = bars + 10;          // P_j written (4 warp arrivals)
-  uint64_t* bar_o = bars + 11;          // PV_j retired (tcgen05.commit)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* bar_s = bars + 9;           // [2] S_j ready in TMEM buffer j & 1 (tcgen05.commit)
+  uint64_t* bar_p = bars + 11;          // P_j written (4 warp arrivals)
+  uint64_t* bar_o = bars + 12;          // PV_j retired (tcgen05.commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int seq = blockIdx.z, head = blockIdx.y;
@@ -129,7 +135,8 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       mbar_init(&bar_kempty[s], 1);
       mbar_init(&bar_vempty[s], 1);
     }
-    mbar_init(bar_s, 1);
+    mbar_init(&bar_s[0], 1);
+    mbar_init(&bar_s[1], 1);
     mbar_init(bar_p, 4);
     mbar_init(bar_o, 1);
     fence_mbar_init();
@@ -142,7 +149,7 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + BN;
+  const uint32_t tS = tmem_base, tO = tmem_base + 2 * BN;  // S buffer b lives at tS + b * BN
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -184,23 +191,32 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       mbar_wait(bar_q, 0, 60);
       int stage = 0;
       uint32_t phase = 0;
-      auto issue_qk = [&](int st) {
+      // S is double-buffered in TMEM: QK_{j+1} is issued *before* waiting for P_j, so the tensor cores
+      // compute the next score tile while the softmax warps work on the current one.
+      auto issue_qk = [&](int st, int buf) {
         const uint32_t k_addr = smem_u32(sK + st * C::K_BYTES);
 #pragma unroll
         for (int c = 0; c < DSUB; ++c)
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_f16_ss(tS, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
+            umma_f16_ss(tS + buf * BN, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
                         umma_desc_k_sw128(k_addr + c * (BN * 128) + k * 32), idesc_s, (c | k) ? 1u : 0u);
-        umma_commit(bar_s);
+        umma_commit(&bar_s[buf]);
         umma_commit(&bar_kempty[st]);
       };
-      // prologue: S_0
       mbar_wait(&bar_kfull[0], 0, 61);
       tcgen05_fence_after();
-      issue_qk(0);
+      issue_qk(0, 0);
+      int kstage = 0;
+      uint32_t kphase = 0;
       for (int j = 0; j < n_tiles; ++j) {
-        // P_j is in shared memory and S_j has been consumed: issue PV_j, then S_{j+1} behind it
+        if (j + 1 < n_tiles) {
+          // S buffer (j+1)&1 was last read by softmax_{j-1}, which finished before bar_p_{j-1} completed
+          if (++kstage == C::KV_STAGES) { kstage = 0; kphase ^= 1; }
+          mbar_wait(&bar_kfull[kstage], kphase, 64);
+          tcgen05_fence_after();
+          issue_qk(kstage, (j + 1) & 1);
+        }
         mbar_wait(bar_p, j & 1, 62);
         mbar_wait(&bar_vfull[stage], phase, 63);
         tcgen05_fence_after();
@@ -215,11 +231,6 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
         umma_commit(bar_o);
         umma_commit(&bar_vempty[stage]);
         if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
-        if (j + 1 < n_tiles) {
-          mbar_wait(&bar_kfull[stage], phase, 64);
-          tcgen05_fence_after();
-          issue_qk(stage);
-        }
       }
     }
   } else {
@@ -230,26 +241,30 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     float m_run = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_tiles; ++j) {
-      mbar_wait(bar_s, j & 1, 70);
+      mbar_wait(&bar_s[j & 1], (j >> 1) & 1, 70);
       tcgen05_fence_after();
       const int kbase = j * BN;
       const bool diag = (kbase + BN - 1) > q0;   // some key of this tile may lie above the diagonal
-      // pass 1: row max
-      float m_tile = -INFINITY;
-#pragma unroll 1
+      // the whole S row lives in registers (one TMEM read): raw scores, masked on diagonal tiles
+      float sc[BN];
+#pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32b_x32(tS + lane_off + c * 32, r);
+        tmem_ld_32x32b_x32(tS + (j & 1) * BN + lane_off + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(r[i]) * a.scale_log2;
-          if (diag && (kbase + c * 32 + i) > qpos) s = -INFINITY;
-          m_tile = fmaxf(m_tile, s);
-        }
+        for (int i = 0; i < 32; ++i) sc[c * 32 + i] = __uint_as_float(r[i]);
       }
-      const float m_new = fmaxf(m_run, m_tile);
-      const float alpha = (m_run == -INFINITY) ? 0.f : exp2f(m_run - m_new);
+      if (diag) {
+#pragma unroll
+        for (int i = 0; i < BN; ++i)
+          if (kbase + i > qpos) sc[i] = -INFINITY;
+      }
+      float m_tile = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < BN; ++i) m_tile = fmaxf(m_tile, sc[i]);
+      const float m_new = fmaxf(m_run, m_tile * a.scale_log2);  // scale > 0: max commutes with scaling
+      const float alpha = (m_run == -INFINITY) ? 0.f : ex2_approx(m_run - m_new);
       // PV_{j-1} must have retired before O is rescaled and before P is overwritten
       if (j > 0) {
         mbar_wait(bar_o, (j - 1) & 1, 71);
@@ -269,25 +284,19 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       }
       l_run *= alpha;
       m_run = m_new;
-      // pass 2: p = exp2(s - m), row sum, P -> shared memory (K-major, 128B swizzle: chunk ^= row & 7)
+      // p = 2^(s*scale - m): one FFMA + one MUFU per element; P -> shared memory (K-major, chunk ^= row & 7)
+      const float neg_m = (m_new == -INFINITY) ? 0.f : -m_new;
       float l_tile = 0.f;
-#pragma unroll 1
+#pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tS + lane_off + c * 32, r);
-        tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float s0 = __uint_as_float(r[i]) * a.scale_log2, s1 = __uint_as_float(r[i + 1]) * a.scale_log2;
-          if (diag && (kbase + c * 32 + i) > qpos) s0 = -INFINITY;
-          if (diag && (kbase + c * 32 + i + 1) > qpos) s1 = -INFINITY;
-          const float p0 = (m_new == -INFINITY) ? 0.f : exp2f(s0 - m_new);
-          const float p1 = (m_new == -INFINITY) ? 0.f : exp2f(s1 - m_new);
+          const float p0 = ex2_approx(fmaf(sc[c * 32 + i], a.scale_log2, neg_m));
+          const float p1 = ex2_approx(fmaf(sc[c * 32 + i + 1], a.scale_log2, neg_m));
           l_tile += p0 + p1;
           pk[i >> 1] = pack2<T>(p0, p1);
         }
-        // this 32-key chunk = 64 bytes = 4 x 16-byte chunks of the row inside sub-tile (c / 2)
         uint8_t* sub = sP + (c >> 1) * (BM * 128) + row * 128;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {

@@ -67,7 +67,12 @@ struct GemmArgs {
   int aligned;            // stream-K kernel: cut CTA ranges at tile boundaries (no partial tiles)
   float* sk_ws;           // stream-K partial slots: [2 * grid][BN][128] fp32 (first / last segment of a CTA)
   uint32_t* sk_counters;  // [tiles], zero between launches
-  int ar;                 // fused all-reduce over ws
+  int ar;                 // fused collective over ws: 0 none, 1 all-reduce, 2 reduce-scatter (token rows)
+  int rs_rows;            // ar == 2 / ag: token rows owned by each rank (M / nranks, multiple of BN)
+  int ag;                 // x rows are sharded over the ranks' symmetric buffers (all-gather fused into the loads)
+  const void* ag_src;     // ag: this rank's [rs_rows, K] shard (row stride ag_ld), staged into the symmetric buffer
+  int64_t ag_ld;
+  const CUtensorMap* ag_maps;  // ag: device array [2 parities][kSymmMaxRanks] of maps over the ranks' staged shards
   unsigned long long* dbg;  // optional per-CTA phase timestamps [grid][8] (globaltimer ns), see llmss_gemm_set_debug
   SymmWs ws;
 };
@@ -152,8 +157,8 @@ __device__ __forceinline__ float act_fast(float x, int act) {
 
 template <typename T>
 __device__ __forceinline__ void epilogue_store8(const GemmArgs& a, const float (&v)[8], int n, int mb, int lane,
-                                                float bval) {
-  const int rows = a.M - mb;  // valid token rows in this group (may be <= 0 or >= 8)
+                                                float bval, int m_limit) {
+  const int rows = m_limit - mb;  // valid token rows in this group (may be <= 0 or >= 8)
   const bool n_ok = n < a.N;
   switch (a.epi) {
     case EPI_PLAIN: {
@@ -270,11 +275,34 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   if (threadIdx.x == 0) LLMSS_STAMP(0);
 
   uint32_t epoch = 0;
-  if (a.ar) epoch = *a.ws.epoch + 1;
+  if (a.ar || a.ag) epoch = *a.ws.epoch + 1;
+
+  if (a.ag) {
+    // ---- fused all-gather, step 1: publish this rank's activation shard in its symmetric buffer.
+    // Peers (and this rank) then pull token tiles straight out of the owners' HBM with TMA, tile by
+    // tile as the main loop needs them, so the transfer overlaps the math (K3: all-gather -> GEMM).
+    const int par_ag = epoch & 1;
+    const int kvec = a.K / 8;  // 16-byte vectors per row
+    uint4* dst = symm_buf<uint4>(a.ws, a.ws.rank, par_ag);
+    const int64_t nvec = (int64_t)a.rs_rows * kvec;
+    for (int64_t v = (int64_t)blockIdx.x * kNumThreads + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * kNumThreads) {
+      const int64_t r = v / kvec, c = v % kvec;
+      dst[v] = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(a.ag_src) + r * a.ag_ld + c * 8);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (atomicAdd(a.ws.ticket + 1, 1u) == gridDim.x - 1) {  // last CTA: the whole shard is staged
+        a.ws.ticket[1] = 0;
+        __threadfence_system();
+        for (int r = 0; r < a.ws.nranks; ++r) st_release_sys(symm_flag(a.ws, r, 1, 0) + a.ws.rank, epoch);
+      }
+    }
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_w);
-    tma_prefetch_desc(&tmap_x);
+    if (!a.ag) tma_prefetch_desc(&tmap_x);
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -304,14 +332,27 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       uint32_t phase = 0;
       SegIter it(g, G, tiles, a.kb_total, a.aligned != 0);
       Segment sg;
+      uint32_t acquired = 0;  // ag: bit q set once rank q's shard is known to be staged
       while (it.next(sg)) {
         const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
+        const void* xmap = &tmap_x;
+        int xrow = tm * BN;
+        if (a.ag) {
+          const int q = xrow / a.rs_rows;  // owner of these token rows
+          if (!(acquired & (1u << q))) {
+            wait_flag_ge(symm_flag(a.ws, a.ws.rank, 1, 0) + q, epoch, 11);
+            asm volatile("fence.proxy.async.global;" ::: "memory");  // peer's generic stores -> our TMA reads
+            acquired |= 1u << q;
+          }
+          xmap = a.ag_maps + (epoch & 1) * kSymmMaxRanks + q;
+          xrow -= q * a.rs_rows;
+        }
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, 10);
           uint8_t* sw = smem + stage * C::STAGE_BYTES;
           mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
           tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
-          tma_load_2d(sw + C::W_BYTES, &tmap_x, &full_bar[stage], kb * BK, tm * BN, pol_x);
+          tma_load_2d(sw + C::W_BYTES, xmap, &full_bar[stage], kb * BK, xrow, pol_x);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -364,7 +405,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     const T* bias = reinterpret_cast<const T*>(a.bias);
     constexpr int NG = BN / 8;               // column groups per tile
     int seg_idx = -1;
-    const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
+    const size_t ar_slot_bytes = (size_t)(a.ar == 2 ? tiles / a.ws.nranks : tiles) * BM * BN * sizeof(T);
     const int par = epoch & 1;
 
     while (it.next(sg)) {
@@ -421,7 +462,11 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         // pass 0: produce the rank-local tile (from TMEM or from the stream-K partials) and either
         //         store it (no AR) or push it to every rank's exchange buffer (AR);
         // pass 1: (AR only) after the per-tile handshake, sum the ranks' tiles and store.
-        const int n_pass = a.ar ? 2 : 1;
+        // reduce-scatter: the tile goes only to the rank that owns its token rows, which alone runs pass 1
+        const int owner = (a.ar == 2) ? m0 / a.rs_rows : -1;
+        const int n_pass = (a.ar == 1 || (a.ar == 2 && owner == a.ws.rank)) ? 2 : 1;
+        // exchange-buffer tile index: global for all-reduce, compact (tiles owned by one rank) for reduce-scatter
+        const int xtile = (a.ar == 2) ? (tm - owner * (a.rs_rows / BN)) * a.tiles_n + tn : sg.tile;
 #pragma unroll 1
         for (int pass = 0; pass < n_pass; ++pass) {
           if (pass == 1 && full_tile) {
@@ -432,7 +477,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
 #pragma unroll 1
           for (int cg = 0; cg < NG; ++cg) {
             float v[8];
-            const size_t xoff = ((size_t)sg.tile * NG + cg) * (BM * 16) + (size_t)f * 16;  // exchange-buffer offset
+            const size_t xoff = ((size_t)xtile * NG + cg) * (BM * 16) + (size_t)f * 16;  // exchange-buffer offset
             if (pass == 0) {
               if (full_tile) {
                 uint32_t r[8];
@@ -469,10 +514,14 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
               if (a.ar) {
                 // round to T, one 16-byte vector per thread per group, tile-blocked + coalesced
                 const uint4 vec = lam_sanitize<2>(pack8<T>(v));
+                if (a.ar == 2) {
+                  *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, owner, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                } else {
 #pragma unroll 1
-                for (int p = 0; p < a.ws.nranks; ++p) {
-                  const int peer = (a.ws.rank + p) % a.ws.nranks;
-                  *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                  for (int p = 0; p < a.ws.nranks; ++p) {
+                    const int peer = (a.ws.rank + p) % a.ws.nranks;
+                    *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                  }
                 }
                 continue;
               }
@@ -488,10 +537,11 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 for (int j = 0; j < 8; ++j) v[j] += t8[j];
               }
             }
-            epilogue_store8<T>(a, v, n, m0 + cg * 8, lane, bval);
+            if (a.ar == 2) epilogue_store8<T>(a, v, n, m0 - a.ws.rank * a.rs_rows + cg * 8, lane, bval, a.rs_rows);
+            else epilogue_store8<T>(a, v, n, m0 + cg * 8, lane, bval, a.M);
           }
         }
-        if (full_tile && !a.ar) {
+        if (full_tile && n_pass == 1) {
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty_bar[as]);
@@ -509,7 +559,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
   }
-  if (a.ar) symm_finish(a.ws, epoch);
+  if (a.ar || a.ag) symm_finish(a.ws, epoch);
   if (threadIdx.x == 0) LLMSS_STAMP(7);
 }
 
@@ -675,7 +725,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
           }
         }
         const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-        epilogue_store8<T>(a, v, n, tm * BN + cg * 8, lane, bval);
+        epilogue_store8<T>(a, v, n, tm * BN + cg * 8, lane, bval, a.M);
       }
     }
   }
@@ -866,9 +916,10 @@ LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_b
 LLMSS_API int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p) {
   return llmss_gemm_plan_query2(M, N, K, nranks, elem_bytes, max_ctas, LLMSS_BF16, p);
 }
+static int g_force_bn = 0;  // set (host-side, transiently) by the reduce-scatter / all-gather modes
 LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype,
                                      llmss_gemm_plan* p) {
-  const int bn = pick_bn(M);
+  const int bn = g_force_bn > 0 ? g_force_bn : pick_bn(M);
   const int tiles_n = (N + BM - 1) / BM, tiles_m = (M + bn - 1) / bn;
   const int tiles = tiles_n * tiles_m;
   const int kb_total = (K + BK - 1) / BK;
@@ -895,18 +946,57 @@ LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_b
 // out = epilogue(x @ w^T).  x: [M,K] row stride ldx; w: [N,K] row stride ldw; both 16-bit `dtype`.
 // gated: rows of w interleave (gate, up); out has N/2 columns.  ar: fused all-reduce over `ws`
 // (bias/residual are applied once, after the reduction).  sk_ws / sk_counters: see plan query.
+LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
+                            const void* residual, int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype,
+                            int out_f32, int act, int act_start, int gated, float* sk_ws, uint32_t* sk_counters,
+                            SymmWs* ws, int max_ctas, int collective, void* ag_maps_dev, cudaStream_t stream);
+
 LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
                          const void* residual, int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype,
                          int out_f32, int act, int act_start, int gated, float* sk_ws, uint32_t* sk_counters,
                          SymmWs* ws, int max_ctas, cudaStream_t stream) {
+  return llmss_gemm_ex(x, ldx, w, ldw, bias, residual, ldr, out, ldo, M, N, K, dtype, out_f32, act, act_start, gated,
+                       sk_ws, sk_counters, ws, max_ctas, (ws != nullptr && ws->nranks > 1) ? 1 : 0, nullptr, stream);
+}
+
+// collective: 0 none | 1 GEMM -> all-reduce | 2 GEMM -> reduce-scatter over token rows (out / residual are this
+// rank's [M/t, N] shard) | 3 all-gather -> GEMM (x is this rank's [M/t, K] shard; M is the gathered row count;
+// ag_maps_dev: 64-byte aligned device scratch of 2 * 8 * 128 bytes for the peer tensor maps).
+LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
+                            const void* residual, int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype,
+                            int out_f32, int act, int act_start, int gated, float* sk_ws, uint32_t* sk_counters,
+                            SymmWs* ws, int max_ctas, int collective, void* ag_maps_dev, cudaStream_t stream) {
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "gemm: dtype must be f16/bf16");
   LLMSS_REQUIRE(M > 0 && N > 0 && K > 0 && K % 8 == 0, "gemm: bad shape M=%d N=%d K=%d (K must be a multiple of 8)", M, N, K);
   LLMSS_REQUIRE(!gated || (N % 2 == 0), "gemm: gated epilogue needs even N");
   LLMSS_REQUIRE(!(gated && out_f32), "gemm: gated epilogue with fp32 output is not supported");
-  const bool ar = (ws != nullptr && ws->nranks > 1);
-  LLMSS_REQUIRE(!(ar && (gated || act != LLMSS_ACT_NONE || out_f32)), "gemm: fused all-reduce supports bias/residual epilogues only");
+  if (ws == nullptr || ws->nranks <= 1) collective = 0;
+  const bool ar = collective == 1, rs = collective == 2, ag = collective == 3;
+  LLMSS_REQUIRE(!((ar || rs) && (gated || act != LLMSS_ACT_NONE || out_f32)),
+                "gemm: fused all-reduce / reduce-scatter support bias/residual epilogues only");
   llmss_gemm_plan p;
-  llmss_gemm_plan_query2(M, N, K, ar ? ws->nranks : 1, 2, max_ctas, dtype, &p);
+  int rs_rows = 0;
+  if (rs || ag) {
+    // token rows are owned by ranks in contiguous blocks; tiles must not straddle two owners, so the
+    // token tile is the largest power of two (16..256) that divides the rows per rank
+    LLMSS_REQUIRE(M % ws->nranks == 0, "gemm: M=%d is not divisible by %d ranks", M, ws->nranks);
+    rs_rows = M / ws->nranks;
+    int bn = 256;
+    while (bn > 16 && rs_rows % bn != 0) bn >>= 1;
+    LLMSS_REQUIRE(rs_rows % bn == 0, "gemm: rows per rank (%d) must be a multiple of 16", rs_rows);
+    g_force_bn = bn;
+  }
+  llmss_gemm_plan_query2(M, N, K, (ar || rs) ? ws->nranks : 1, 2, max_ctas, dtype, &p);
+  g_force_bn = 0;
+  if (rs || ag) {
+    p.split = 0;  // these modes live in the persistent stream-K kernel
+    int sms = max_ctas > 0 ? max_ctas : num_sms();
+    int64_t work = (int64_t)p.tiles * p.kb_total, grid = work / 4;
+    if (grid < p.tiles && p.tiles <= sms) grid = p.tiles;
+    if (grid < 1) grid = 1;
+    if (grid > sms) grid = sms;
+    p.grid = (int)grid;
+  }
   const bool aligned = p.split == 0 && p.tiles >= 4 * p.grid;    // many tiles per CTA: plain data-parallel
   const bool need_sk = p.split == 0 && !aligned && (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
   LLMSS_REQUIRE(!need_sk || (sk_ws != nullptr && sk_counters != nullptr), "gemm: stream-K workspace required for this shape");
@@ -916,9 +1006,31 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
     LLMSS_REQUIRE((size_t)p.ar_bytes <= ws->lam_bytes, "gemm: fused all-reduce needs %lld bytes of Lamport buffer (have %zu)",
                   (long long)p.ar_bytes, ws->lam_bytes);
   }
+  if (rs) {
+    const size_t need = (size_t)p.tiles * BM * p.bn * 2;  // nranks sources x (tiles / nranks) owned tiles
+    LLMSS_REQUIRE(need <= ws->lam_bytes, "gemm: fused reduce-scatter needs %zu bytes of Lamport buffer (have %zu)", need,
+                  ws->lam_bytes);
+  }
   CUtensorMap tw, tx;
+  memset(&tx, 0, sizeof(tx));
   if (int e = make_tmap(&tw, w, dtype, N, K, ldw, BM)) return e;
-  if (int e = make_tmap(&tx, x, dtype, M, K, ldx, p.bn)) return e;
+  if (ag) {
+    // x is this rank's [rs_rows, K] shard; every rank stages its shard in its symmetric bulk buffer and the
+    // kernel's TMA producer pulls token tiles from the owners (peer HBM over NVLink).
+    LLMSS_REQUIRE(ag_maps_dev != nullptr && ((uintptr_t)ag_maps_dev % 64) == 0, "gemm: all-gather mode needs a 64-byte aligned map scratch");
+    LLMSS_REQUIRE((size_t)rs_rows * K * 2 <= ws->buf_bytes, "gemm: all-gather shard of %zu bytes exceeds the symmetric bulk buffer (%zu)",
+                  (size_t)rs_rows * K * 2, ws->buf_bytes);
+    CUtensorMap maps[2 * kSymmMaxRanks];
+    memset(maps, 0, sizeof(maps));
+    for (int par = 0; par < 2; ++par)
+      for (int q = 0; q < ws->nranks; ++q) {
+        const char* base = ws->peer_base[q] + kSymmDataOffset + 2 * ws->lam_bytes + (size_t)par * ws->buf_bytes;
+        if (int e = make_tmap(&maps[par * kSymmMaxRanks + q], base, dtype, rs_rows, K, K, p.bn)) return e;
+      }
+    LLMSS_CHECK_CUDA(cudaMemcpyAsync(ag_maps_dev, maps, sizeof(maps), cudaMemcpyHostToDevice, stream));
+  } else {
+    if (int e = make_tmap(&tx, x, dtype, M, K, ldx, p.bn)) return e;
+  }
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.M = M; a.N = N; a.K = K;
@@ -932,9 +1044,14 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
   a.aligned = aligned ? 1 : 0;
   a.epi = gated ? EPI_GATED : (out_f32 ? EPI_F32 : (act != LLMSS_ACT_NONE ? EPI_ACT : EPI_PLAIN));
   a.sk_ws = sk_ws; a.sk_counters = sk_counters;
-  a.ar = ar ? 1 : 0;
+  a.ar = ar ? 1 : (rs ? 2 : 0);
+  a.rs_rows = rs_rows;
+  a.ag = ag ? 1 : 0;
+  a.ag_src = x;
+  a.ag_ld = ldx;
+  a.ag_maps = reinterpret_cast<const CUtensorMap*>(ag_maps_dev);
   a.dbg = g_dbg;
-  if (ar) a.ws = *ws;
+  if (collective) a.ws = *ws;
 #define LLMSS_LAUNCH(T_, BN_) \
   return p.split > 0 ? launch_cluster<T_, BN_>(tw, tx, a, p.tiles, p.split, stream) : launch<T_, BN_>(tw, tx, a, p.grid, stream)
   if (dtype == LLMSS_F16) {

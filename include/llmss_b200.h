@@ -59,6 +59,13 @@ int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const voi
                int act_start, int gated, float* sk_ws, uint32_t* sk_counters, llmss_symm_t* ws, int max_ctas,
                llmss_stream_t stream);
 
+/* collective: 0 none | 1 GEMM -> all-reduce | 2 GEMM -> reduce-scatter over token rows (K2) |
+ * 3 all-gather -> GEMM (K3: x is this rank's row shard, tiles are pulled from peers with TMA). */
+int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias, const void* residual,
+                  int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype, int out_f32, int act,
+                  int act_start, int gated, float* sk_ws, uint32_t* sk_counters, llmss_symm_t* ws, int max_ctas,
+                  int collective, void* ag_maps_dev, llmss_stream_t stream);
+
 /* ---- K6 fused residual add + LayerNorm / RMSNorm (G2, G13, G18; layers.py:12-36,217-256) ---- */
 int llmss_norm_residual(const void* x, const void* x2, const void* residual_in, void* residual_out,
                         const void* weight, const void* bias, void* out, int M, int H, int64_t ldx, int64_t ldx2,

@@ -39,6 +39,7 @@ class _Arena:
         self.sk_ws = torch.empty(self.SK_FLOATS, dtype=torch.float32, device=device)
         self.sk_counters = torch.zeros(self.SK_COUNTERS, dtype=torch.int32, device=device)
         self.attn = None
+        self.ag_maps = None
         self._retired = []  # outgrown buffers stay alive: captured CUDA graphs may still point at them
 
     def attn_scratch(self, nfloats: int, device):
@@ -92,6 +93,45 @@ def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start:
                         M, N, K, _DT[x.dtype], out_f32, act, act_start, 1 if gated else 0,
                         _ptr(a.sk_ws), _ptr(a.sk_counters), symm.handle if ar else None, max_ctas, _stream())
     _lib.check(rc, "llmss_gemm")
+    _count()
+    return out
+
+
+def linear_reduce_scatter(x, w, symm, bias=None, residual_shard=None):
+    """K2: row-parallel GEMM whose epilogue reduce-scatters over token rows.  Returns this rank's
+    [M / t, N] shard of sum_r(x_r @ w_r.T) (+ bias, + residual_shard)."""
+    lib = _lib.load()
+    M, K, ldx = _rows2d(x)
+    N = w.shape[0]
+    rows = M // symm.nranks
+    out = torch.empty(rows, N, dtype=x.dtype, device=x.device)
+    a = arena(x.device)
+    rc = lib.llmss_gemm_ex(_ptr(x), ldx, _ptr(w), w.stride(0), _ptr(bias), _ptr(residual_shard),
+                           residual_shard.stride(0) if residual_shard is not None else 0, _ptr(out), out.stride(0),
+                           M, N, K, _DT[x.dtype], 0, ACT_NONE, 0, 0, _ptr(a.sk_ws), _ptr(a.sk_counters), symm.handle, 0,
+                           2, None, _stream())
+    _lib.check(rc, "llmss_gemm_ex(reduce-scatter)")
+    _count()
+    return out
+
+
+def allgather_linear(x_shard, w, symm, bias=None, act: int = ACT_NONE, gated: bool = False, act_start: int = 0,
+                     out_dtype=None):
+    """K3: column-parallel GEMM over the all-gather of the ranks' row shards; the gather is fused into
+    the kernel's TMA loads (token tiles are pulled from the owning rank's HBM over NVLink)."""
+    lib = _lib.load()
+    rows, K, ldx = _rows2d(x_shard)
+    M, N = rows * symm.nranks, w.shape[0]
+    out_f32 = 1 if out_dtype == torch.float32 else 0
+    out = torch.empty(M, N // 2 if gated else N, dtype=torch.float32 if out_f32 else x_shard.dtype, device=x_shard.device)
+    a = arena(x_shard.device)
+    if a.ag_maps is None:
+        a.ag_maps = torch.zeros(2 * 8 * 128 + 64, dtype=torch.uint8, device=x_shard.device)
+    maps_ptr = (a.ag_maps.data_ptr() + 63) // 64 * 64
+    rc = lib.llmss_gemm_ex(_ptr(x_shard), ldx, _ptr(w), w.stride(0), _ptr(bias), None, 0, _ptr(out), out.stride(0),
+                           M, N, K, _DT[x_shard.dtype], out_f32, act, act_start, 1 if gated else 0, _ptr(a.sk_ws),
+                           _ptr(a.sk_counters), symm.handle, 0, 3, C.c_void_p(maps_ptr), _stream())
+    _lib.check(rc, "llmss_gemm_ex(all-gather)")
     _count()
     return out
 

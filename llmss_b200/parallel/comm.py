@@ -35,13 +35,13 @@ class Communicator:
         self.stats = {"all_reduce": 0, "all_gather": 0, "broadcast": 0, "symm_all_reduce": 0}
 
     # ------------------------------------------------------------------ setup
-    def attach_symmetric(self, max_bytes: int = 32 << 20):
+    def attach_symmetric(self, max_bytes: int = 32 << 20, lamport_bytes: int = 16 << 20):
         """Allocate + exchange the NVLink peer-mapped workspace (CUDA, size > 1 only)."""
         if self.size == 1 or self.fake or self.device is None or self.device.type != "cuda":
             return None
         from .symm import SymmetricWorkspace
 
-        self.symm = SymmetricWorkspace(self.group, self.device, max_bytes=max_bytes)
+        self.symm = SymmetricWorkspace(self.group, self.device, max_bytes=max_bytes, lamport_bytes=lamport_bytes)
         return self.symm
 
     @property

@@ -32,7 +32,7 @@ def main():
     pg, rank, world = initialize_torch_distributed(timeout_s=120)
     dev = torch.device("cuda", torch.cuda.current_device())
     comm = comm_for(pg, dev)
-    symm = comm.attach_symmetric(64 << 20)
+    symm = comm.attach_symmetric(64 << 20)  # bulk; Lamport area default 16 MiB
     assert symm is not None
     ok = True
 
@@ -105,6 +105,44 @@ def main():
                 ok = False
                 log(f"FAIL gemm+AR not bit-identical across ranks M={M} N={N} K={K}")
     log("fused GEMM+AR done", "OK" if ok else "FAILED")
+
+    # ---- 3b. fused GEMM -> reduce-scatter (K2) and all-gather -> GEMM (K3), prefill-size token counts
+    for (M, N, K) in [(world * 256, 1024, 512), (world * 512, 4096, 1024), (world * 128, 768, 2048)]:
+        torch.manual_seed(11 + rank)
+        xr = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+        wr = torch.randn(N, K, device=dev, dtype=torch.bfloat16) / math.sqrt(K * world)
+        torch.manual_seed(5)
+        bias = torch.randn(N, device=dev, dtype=torch.bfloat16)
+        res = torch.randn(M, N, device=dev, dtype=torch.bfloat16)
+        full = xr.float() @ wr.float().t()
+        dist.all_reduce(full)
+        rows = M // world
+        want = full[rank * rows:(rank + 1) * rows] + bias.float() + res[rank * rows:(rank + 1) * rows].float()
+        for rep in range(2):
+            got = cu.linear_reduce_scatter(xr, wr, symm, bias=bias, residual_shard=res[rank * rows:(rank + 1) * rows])
+            torch.cuda.synchronize()
+            err = (got.float() - want).abs().max().item()
+            if err > 0.1:
+                ok = False
+                log(f"FAIL gemm+RS M={M} N={N} K={K} rep={rep} max err {err}")
+        # all-gather -> GEMM: every rank contributes `rows` token rows, weights are rank-local (column parallel)
+        torch.manual_seed(21 + rank)
+        xs = torch.randn(rows, K, device=dev, dtype=torch.bfloat16)
+        wc = torch.randn(N, K, device=dev, dtype=torch.bfloat16) / math.sqrt(K)
+        bc = torch.randn(N, device=dev, dtype=torch.bfloat16)
+        gathered = [torch.empty_like(xs) for _ in range(world)]
+        dist.all_gather(gathered, xs)
+        xfull = torch.cat(gathered, 0)
+        from llmss_b200.ops import reference as R
+        want2 = R.linear(xfull, wc, bc, act=R.ACT_GELU_TANH, out_dtype=torch.float32)
+        for rep in range(2):
+            got2 = cu.allgather_linear(xs, wc, symm, bias=bc, act=R.ACT_GELU_TANH)
+            torch.cuda.synchronize()
+            err = (got2.float() - want2).abs().max().item()
+            if err > 0.08:
+                ok = False
+                log(f"FAIL AG+gemm M={M} N={N} K={K} rep={rep} max err {err}")
+    log("fused GEMM+reduce-scatter / all-gather+GEMM done", "OK" if ok else "FAILED")
 
     # ---- 4. CUDA graph replay of a GEMM+AR / all-reduce chain
     M, N, K = 64, 4096, 2048

@@ -31,6 +31,8 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version banner there)
 
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
@@ -151,7 +153,7 @@ def run_ours(args, rank, world, local):
     t0 = time.time()
     eng = Engine.from_pretrained(path, dtype=dtype, device=torch.device("cuda", local), process_group=pg,
                                  max_batch=B, max_seq_len=S + total_new + 16, use_cuda_graph=not args.no_graph,
-                                 max_prefill_tokens=16384, symmetric_bytes=128 << 20)
+                                 max_prefill_tokens=8192, symmetric_bytes=128 << 20, lamport_bytes=64 << 20)
     load_s = time.time() - t0
     runner = eng.runner
     prompts = synthetic_prompts(B, S, eng.core.spec.vocab)

@@ -25,7 +25,7 @@ class BatchInput:
 
     @staticmethod
     def build(token_lists: Sequence[Sequence[int]], context_lens: Sequence[int], block_tables: Sequence[Sequence[int]],
-              block_size: int, device, max_blocks: Optional[int] = None) -> "BatchInput":
+              block_size: int, device, max_blocks: Optional[int] = None, pad_to: int = 1) -> "BatchInput":
         """Host-side construction: ``token_lists[i]`` are the new tokens of sequence i, which
         already has ``context_lens[i]`` tokens in the cache blocks ``block_tables[i]``."""
         toks: List[int] = []
@@ -41,6 +41,12 @@ class BatchInput:
                 slots.append(bt[p // block_size] * block_size + p % block_size)
             cu.append(len(toks))
             seq_lens.append(ctx + len(new))
+        # inert padding rows (token 0, slot -1, owned by no sequence) so that the packed length is a
+        # multiple of `pad_to` (sequence-parallel prefill shards the rows evenly over the ranks)
+        while len(toks) % pad_to:
+            toks.append(0)
+            pos.append(0)
+            slots.append(-1)
         B = len(token_lists)
         mb = max_blocks or max(1, max(len(b) for b in block_tables))
         bt_t = torch.zeros(B, mb, dtype=torch.int32)

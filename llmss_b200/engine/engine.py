@@ -72,7 +72,8 @@ class Engine:
     # ------------------------------------------------------------------ construction
     @classmethod
     def from_pretrained(cls, path: str, dtype=torch.bfloat16, device=None, process_group=None,
-                        symmetric_bytes: int = 64 << 20, fuse_parallel: bool = True, **kw) -> "Engine":
+                        symmetric_bytes: int = 128 << 20, lamport_bytes: int = 64 << 20, fuse_parallel: bool = True,
+                        **kw) -> "Engine":
         from transformers import AutoConfig
 
         if process_group is None:
@@ -85,7 +86,7 @@ class Engine:
         config = AutoConfig.from_pretrained(path)
         comm = comm_for(process_group, device)
         if device.type == "cuda" and comm.size > 1 and comm.symm is None:
-            comm.attach_symmetric(symmetric_bytes)
+            comm.attach_symmetric(symmetric_bytes, lamport_bytes)
         weights = Weights(weight_files(path), device=device, dtype=dtype, process_group=process_group)
         if config.model_type not in MODEL_REGISTRY:
             raise KeyError(f"model_type {config.model_type!r} is not supported; have {sorted(MODEL_REGISTRY)}")

@@ -140,7 +140,8 @@ class ModelRunner:
             s.prompt = s.prompt[-(self.max_seq_len - 1):]  # left-truncate like the reference tokenizer call
             self._grow(s, len(s.prompt))
         batch = BatchInput.build([s.prompt for s in seqs], [0] * len(seqs), [s.blocks for s in seqs],
-                                 self.block_size, self.device, max_blocks=self.max_blocks_per_seq)
+                                 self.block_size, self.device, max_blocks=self.max_blocks_per_seq,
+                                 pad_to=self.core.tp * 16 if self.core.tp > 1 else 1)
         logits = self.core.forward(batch, self.kv, last_only=True)
         B = len(seqs)
         dev = self.device

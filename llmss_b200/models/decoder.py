@@ -112,6 +112,7 @@ class DecoderLM(nn.Module):
         self.d = spec.head_dim
         self.q_dim, self.kv_dim = self.hq * self.d, self.hkv * self.d
         self.fuse_parallel = bool(fuse_parallel and spec.parallel_residual)
+        self.sp_prefill = True  # sequence-parallel prefill dataflow when the shapes / buffers allow it
         self.vocab_blk = -(-spec.vocab // self.tp)
         self.layers: List[LayerWeights] = []
         self.wte = self.wpe = self.lnf_w = self.lnf_b = self.w_head = self.b_head = None
@@ -182,6 +183,86 @@ class DecoderLM(nn.Module):
             out = ops.linear(y[:, q_off:], L.w2, L.b2, comm=self.comm)       # one GEMM + one all-reduce
         return out, resid
 
+    # ------------------------------------------------------------------ sequence-parallel prefill
+    def _sp_ok(self, batch: BatchInput) -> bool:
+        """Sequence-parallel dataflow (north-star items 1+2): GEMM -> reduce-scatter after the row-parallel
+        layers, all-gather -> GEMM before the column-parallel ones, norms / residuals on T/t rows per rank.
+        Used for fresh prefill on CUDA when the shards fit the symmetric buffers; decode keeps the
+        latency-optimal fused all-reduce."""
+        symm = self.comm.symm
+        T = batch.tokens.numel()
+        if symm is None or self.tp == 1 or batch.is_decode or not batch.is_fresh_prefill or not self.sp_prefill:
+            return False
+        if T % (self.tp * 16) != 0 or T < self.tp * 64:
+            return False
+        s = self.spec
+        k_max = max(s.hidden, self.q_dim + self.ffn_r if self.fuse_parallel else max(self.q_dim, self.ffn_r))
+        if (T // self.tp) * k_max * 2 > symm.buf_bytes:
+            return False
+        return T * s.hidden * 2 <= symm.lam_bytes  # reduce-scatter exchange: one padded [T, H] tile set per parity
+
+    def _forward_hidden_sp(self, batch: BatchInput, kv) -> torch.Tensor:
+        from ..ops import cuda_impl as cu
+
+        s, symm = self.spec, self.comm.symm
+        T = batch.tokens.numel()
+        rows = T // self.tp
+        lo, hi = self.rank * rows, (self.rank + 1) * rows
+        x = ops.embed(batch.tokens[lo:hi], self.wte, batch.positions[lo:hi] if s.learned_pos else None,
+                      self.wpe if s.learned_pos else None, s.pos_offset)                   # [T/t, H] shard
+        resid = None
+        for li, L in enumerate(self.layers):
+            kc, vc = kv.k(li), kv.v(li)
+            if self.fuse_parallel:
+                with trace("norm_residual"):
+                    hn, resid = ops.norm_residual(x, resid, L.ln1_w, L.ln1_b, s.eps, s.norm)
+                qkv_dim = self.q_dim + 2 * self.kv_dim
+                with trace("allgather_gemm_qkv_up"):
+                    y = cu.allgather_linear(hn, L.w1, symm, bias=L.b1, act=s.act, act_start=qkv_dim)
+                k_off, v_off, q_off = 0, self.kv_dim, 2 * self.kv_dim
+                ops.rope_kv_write(y, batch.positions, batch.slot_mapping, kc, vc, self.hq, self.hkv, self.d,
+                                  s.rotary_dim, s.rope, s.rope_base, q_off, k_off, v_off)
+                with trace("attention"):
+                    ops.attention(y, y, batch, kc, vc, self.hq, self.hkv, self.d, s.scale, q_off, k_off, v_off,
+                                  out_off=q_off)
+                with trace("gemm_out_down_reduce_scatter"):
+                    x = cu.linear_reduce_scatter(y[:, q_off:], L.w2, symm, bias=L.b2)
+            else:
+                hn, resid = ops.norm_residual(x, resid, L.ln1_w, L.ln1_b, s.eps, s.norm)
+                qkv = cu.allgather_linear(hn, L.wqkv, symm, bias=L.bqkv)
+                q_off, k_off, v_off = 0, self.q_dim, self.q_dim + self.kv_dim
+                ops.rope_kv_write(qkv, batch.positions, batch.slot_mapping, kc, vc, self.hq, self.hkv, self.d,
+                                  s.rotary_dim, s.rope, s.rope_base, q_off, k_off, v_off)
+                ctx = torch.empty(T, self.q_dim, dtype=qkv.dtype, device=qkv.device)
+                ops.attention(qkv, ctx, batch, kc, vc, self.hq, self.hkv, self.d, s.scale, q_off, k_off, v_off)
+                if s.parallel_residual:
+                    o = cu.linear_reduce_scatter(ctx, L.wo, symm, bias=L.bo)
+                    u = cu.allgather_linear(hn, L.wup, symm, bias=L.bup, act=s.act, gated=s.gated)
+                    dn = cu.linear_reduce_scatter(u, L.wdown, symm, bias=L.bdown)
+                    x = o + dn
+                else:
+                    o = cu.linear_reduce_scatter(ctx, L.wo, symm, bias=L.bo)
+                    hn2, resid = ops.norm_residual(o, resid, L.ln2_w, L.ln2_b, s.eps, s.norm)
+                    u = cu.allgather_linear(hn2, L.wup, symm, bias=L.bup, act=s.act, gated=s.gated)
+                    x = cu.linear_reduce_scatter(u, L.wdown, symm, bias=L.bdown)
+        hn, _ = ops.norm_residual(x, resid, self.lnf_w, self.lnf_b, s.eps, s.norm)        # [T/t, H] shard
+        return hn
+
+    def _gather_last_rows(self, hn_shard: torch.Tensor, batch: BatchInput) -> torch.Tensor:
+        """[B, H] last-token hidden states from the row shards: each rank fills the rows it owns, one
+        small all-reduce makes them identical everywhere."""
+        rows = hn_shard.shape[0]
+        lo = self.rank * rows
+        idx = batch.last_idx
+        mine = (idx >= lo) & (idx < lo + rows)
+        out = torch.zeros(idx.numel(), hn_shard.shape[1], dtype=hn_shard.dtype, device=hn_shard.device)
+        sel = torch.nonzero(mine, as_tuple=False).flatten()
+        if sel.numel():
+            out[sel] = hn_shard.index_select(0, idx[sel] - lo)
+        pad = (-out.numel() * out.element_size()) % 16
+        self.comm.all_reduce(out if pad == 0 else out)  # [B, H] rows are 16-byte multiples (H % 8 == 0)
+        return out
+
     def forward_hidden(self, batch: BatchInput, kv) -> torch.Tensor:
         """Final-normed hidden states for every packed token: [T, H]."""
         s = self.spec
@@ -210,6 +291,8 @@ class DecoderLM(nn.Module):
             return self.comm.all_gather_cat(local, dim=-1)
 
     def forward(self, batch: BatchInput, kv, last_only: bool = True) -> torch.Tensor:
+        if last_only and self._sp_ok(batch):
+            return self.logits(self._gather_last_rows(self._forward_hidden_sp(batch, kv), batch))
         h = self.forward_hidden(batch, kv)
         if last_only:
             h = h.index_select(0, batch.last_idx)

@@ -213,12 +213,16 @@ def main():
     if rank == 0:
         write_random_checkpoint(path, "gptj-tiny8", dtype=torch.float16, device="cuda", std=0.05)
     dist.barrier()
-    prompts = [[3, 14, 15, 92, 65], [35, 89, 79], [32, 38, 46, 26, 43, 38, 32], [7] * 20]
+    g = torch.Generator().manual_seed(77)
+    # short prompts (fused all-reduce path) + long ones (>= tp*64 packed tokens: sequence-parallel prefill path)
+    prompts = [[3, 14, 15, 92, 65], [35, 89, 79], torch.randint(1, 500, (150,), generator=g).tolist(),
+               torch.randint(1, 500, (97,), generator=g).tolist()]
     sp = SamplingParams(max_new_tokens=10, is_greedy=True)
     tp = Engine.from_pretrained(path, dtype=torch.bfloat16, device=dev, process_group=pg, max_batch=4, max_seq_len=128)
-    got = tp.generate(prompts, sp)
+    got = tp.generate(prompts[:2], sp) + tp.generate(prompts[2:], sp)
+    sp_used = tp.core._sp_ok.__self__ is tp.core  # (path selection itself is asserted below via the collective counters)
     single = Engine.from_pretrained(path, dtype=torch.bfloat16, device=dev, process_group=FakeGroup(0, 1), max_batch=4, max_seq_len=128)
-    want_t = single.generate(prompts, sp)
+    want_t = single.generate(prompts[:2], sp) + single.generate(prompts[2:], sp)
     agree = sum(g[:4] == w[:4] for g, w in zip(got, want_t))
     all_out = [None] * world
     dist.all_gather_object(all_out, got)

@@ -72,7 +72,8 @@ struct GemmArgs {
   int ag;                 // x rows are sharded over the ranks' symmetric buffers (all-gather fused into the loads)
   const void* ag_src;     // ag: this rank's [rs_rows, K] shard (row stride ag_ld), staged into the symmetric buffer
   int64_t ag_ld;
-  const CUtensorMap* ag_maps;  // ag: device array [2 parities][kSymmMaxRanks] of maps over the ranks' staged shards
+  const CUtensorMap* ag_maps;  // ag: device array [2 parities] of maps over the gathered [M, K] activation (local)
+  int tm_rot;                  // token-tile rotation: with ag, every rank starts on the tiles of its own shard
   unsigned long long* dbg;  // optional per-CTA phase timestamps [grid][8] (globaltimer ns), see llmss_gemm_set_debug
   SymmWs ws;
 };
@@ -277,32 +278,9 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   uint32_t epoch = 0;
   if (a.ar || a.ag) epoch = *a.ws.epoch + 1;
 
-  if (a.ag) {
-    // ---- fused all-gather, step 1: publish this rank's activation shard in its symmetric buffer.
-    // Peers (and this rank) then pull token tiles straight out of the owners' HBM with TMA, tile by
-    // tile as the main loop needs them, so the transfer overlaps the math (K3: all-gather -> GEMM).
-    const int par_ag = epoch & 1;
-    const int kvec = a.K / 8;  // 16-byte vectors per row
-    uint4* dst = symm_buf<uint4>(a.ws, a.ws.rank, par_ag);
-    const int64_t nvec = (int64_t)a.rs_rows * kvec;
-    for (int64_t v = (int64_t)blockIdx.x * kNumThreads + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * kNumThreads) {
-      const int64_t r = v / kvec, c = v % kvec;
-      dst[v] = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(a.ag_src) + r * a.ag_ld + c * 8);
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      if (atomicAdd(a.ws.ticket + 1, 1u) == gridDim.x - 1) {  // last CTA: the whole shard is staged
-        a.ws.ticket[1] = 0;
-        __threadfence_system();
-        for (int r = 0; r < a.ws.nranks; ++r) st_release_sys(symm_flag(a.ws, r, 1, 0) + a.ws.rank, epoch);
-      }
-    }
-  }
-
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_w);
-    if (!a.ag) tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_x);
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -334,18 +312,19 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       Segment sg;
       uint32_t acquired = 0;  // ag: bit q set once rank q's shard is known to be staged
       while (it.next(sg)) {
-        const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
+        const int tn = sg.tile % a.tiles_n, tm = (sg.tile / a.tiles_n + a.tm_rot) % a.tiles_m;
         const void* xmap = &tmap_x;
         int xrow = tm * BN;
-        if (a.ag) {
-          const int q = xrow / a.rs_rows;  // owner of these token rows
+        if (a.ag && xrow / a.rs_rows == a.ws.rank) {
+          xrow -= a.ws.rank * a.rs_rows;  // own shard: tmap_x covers it in place, no waiting
+        } else if (a.ag) {
+          const int q = xrow / a.rs_rows;  // rank whose shard holds these token rows
           if (!(acquired & (1u << q))) {
             wait_flag_ge(symm_flag(a.ws, a.ws.rank, 1, 0) + q, epoch, 11);
-            asm volatile("fence.proxy.async.global;" ::: "memory");  // peer's generic stores -> our TMA reads
+            asm volatile("fence.proxy.async.global;" ::: "memory");  // peers' generic stores -> our TMA reads
             acquired |= 1u << q;
           }
-          xmap = a.ag_maps + (epoch & 1) * kSymmMaxRanks + q;
-          xrow -= q * a.rs_rows;
+          xmap = a.ag_maps + (epoch & 1);  // the gathered [M, K] activation in this rank's own bulk buffer
         }
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, 10);
@@ -408,9 +387,37 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     const size_t ar_slot_bytes = (size_t)(a.ar == 2 ? tiles / a.ws.nranks : tiles) * BM * BN * sizeof(T);
     const int par = epoch & 1;
 
+    if (a.ag) {
+      // ---- fused all-gather (K3): while the TMA / MMA warps already work on the token tiles of this
+      // rank's own shard, the (still idle) epilogue warps push that shard into every rank's gathered
+      // activation buffer over NVLink; the last CTA to finish raises the "shard landed" flags.  Readers
+      // then fetch tiles from their *local* copy (L2-cacheable; peer memory would bypass L2).
+      const int kvec = a.K / 8;
+      const int64_t nvec = (int64_t)a.rs_rows * kvec;
+      const int64_t base = (int64_t)a.ws.rank * nvec;
+      for (int64_t v = (int64_t)blockIdx.x * 128 + epi_tid; v < nvec; v += (int64_t)gridDim.x * 128) {
+        const int64_t r = v / kvec, c = v % kvec;
+        const uint4 val = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(a.ag_src) + r * a.ag_ld + c * 8);
+#pragma unroll 1
+        for (int p = 0; p < a.ws.nranks; ++p) {
+          const int peer = (a.ws.rank + p) % a.ws.nranks;
+          symm_buf<uint4>(a.ws, peer, par)[base + v] = val;
+        }
+      }
+      __threadfence_system();
+      epi_bar();
+      if (epi_tid == 0) {
+        if (atomicAdd(a.ws.ticket + 1, 1u) == gridDim.x - 1) {
+          a.ws.ticket[1] = 0;
+          __threadfence_system();
+          for (int r = 0; r < a.ws.nranks; ++r) st_release_sys(symm_flag(a.ws, r, 1, 0) + a.ws.rank, epoch);
+        }
+      }
+    }
+
     while (it.next(sg)) {
       ++seg_idx;
-      const int tn = sg.tile % a.tiles_n, tm = sg.tile / a.tiles_n;
+      const int tn = sg.tile % a.tiles_n, tm = (sg.tile / a.tiles_n + a.tm_rot) % a.tiles_m;
       const int n = tn * BM + f;
       const int m0 = tm * BN;
       const bool n_ok = n < a.N;
@@ -1018,16 +1025,16 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
     // x is this rank's [rs_rows, K] shard; every rank stages its shard in its symmetric bulk buffer and the
     // kernel's TMA producer pulls token tiles from the owners (peer HBM over NVLink).
     LLMSS_REQUIRE(ag_maps_dev != nullptr && ((uintptr_t)ag_maps_dev % 64) == 0, "gemm: all-gather mode needs a 64-byte aligned map scratch");
-    LLMSS_REQUIRE((size_t)rs_rows * K * 2 <= ws->buf_bytes, "gemm: all-gather shard of %zu bytes exceeds the symmetric bulk buffer (%zu)",
-                  (size_t)rs_rows * K * 2, ws->buf_bytes);
-    CUtensorMap maps[2 * kSymmMaxRanks];
+    LLMSS_REQUIRE((size_t)M * K * 2 <= ws->buf_bytes, "gemm: gathered activation of %zu bytes exceeds the symmetric bulk buffer (%zu)",
+                  (size_t)M * K * 2, ws->buf_bytes);
+    CUtensorMap maps[2];
     memset(maps, 0, sizeof(maps));
-    for (int par = 0; par < 2; ++par)
-      for (int q = 0; q < ws->nranks; ++q) {
-        const char* base = ws->peer_base[q] + kSymmDataOffset + 2 * ws->lam_bytes + (size_t)par * ws->buf_bytes;
-        if (int e = make_tmap(&maps[par * kSymmMaxRanks + q], base, dtype, rs_rows, K, K, p.bn)) return e;
-      }
+    for (int par = 0; par < 2; ++par) {
+      const char* base = ws->peer_base[ws->rank] + kSymmDataOffset + 2 * ws->lam_bytes + (size_t)par * ws->buf_bytes;
+      if (int e = make_tmap(&maps[par], base, dtype, M, K, K, p.bn)) return e;
+    }
     LLMSS_CHECK_CUDA(cudaMemcpyAsync(ag_maps_dev, maps, sizeof(maps), cudaMemcpyHostToDevice, stream));
+    if (int e = make_tmap(&tx, x, dtype, rs_rows, K, ldx, p.bn)) return e;  // this rank's own shard, read in place
   } else {
     if (int e = make_tmap(&tx, x, dtype, M, K, ldx, p.bn)) return e;
   }
@@ -1050,6 +1057,7 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   a.ag_src = x;
   a.ag_ld = ldx;
   a.ag_maps = reinterpret_cast<const CUtensorMap*>(ag_maps_dev);
+  a.tm_rot = ag ? ws->rank * (rs_rows / p.bn) : 0;
   a.dbg = g_dbg;
   if (collective) a.ws = *ws;
 #define LLMSS_LAUNCH(T_, BN_) \

@@ -112,7 +112,11 @@ class DecoderLM(nn.Module):
         self.d = spec.head_dim
         self.q_dim, self.kv_dim = self.hq * self.d, self.hkv * self.d
         self.fuse_parallel = bool(fuse_parallel and spec.parallel_residual)
-        self.sp_prefill = True  # sequence-parallel prefill dataflow when the shapes / buffers allow it
+        # sequence-parallel prefill dataflow (GEMM->reduce-scatter, all-gather->GEMM).  Opt-in for now
+        # (LLMSS_SP_PREFILL=1): measured at TP=2 on GPT-J-6B it is still slower than the fused all-reduce
+        # path (814 ms vs 608 ms for 64 x 1024-token prompts); see profiles/bench_results.md.
+        import os
+        self.sp_prefill = os.environ.get("LLMSS_SP_PREFILL", "0") == "1"
         self.vocab_blk = -(-spec.vocab // self.tp)
         self.layers: List[LayerWeights] = []
         self.wte = self.wpe = self.lnf_w = self.lnf_b = self.w_head = self.b_head = None
@@ -196,8 +200,8 @@ class DecoderLM(nn.Module):
         if T % (self.tp * 16) != 0 or T < self.tp * 64:
             return False
         s = self.spec
-        k_max = max(s.hidden, self.q_dim + self.ffn_r if self.fuse_parallel else max(self.q_dim, self.ffn_r))
-        if (T // self.tp) * k_max * 2 > symm.buf_bytes:
+        k_max = s.hidden  # every all-gathered operand is a [T, hidden] activation
+        if T * k_max * 2 > symm.buf_bytes:  # gathered activation lives in the bulk buffer
             return False
         return T * s.hidden * 2 <= symm.lam_bytes  # reduce-scatter exchange: one padded [T, H] tile set per parity
 

@@ -219,8 +219,9 @@ def main():
                torch.randint(1, 500, (97,), generator=g).tolist()]
     sp = SamplingParams(max_new_tokens=10, is_greedy=True)
     tp = Engine.from_pretrained(path, dtype=torch.bfloat16, device=dev, process_group=pg, max_batch=4, max_seq_len=128)
-    got = tp.generate(prompts[:2], sp) + tp.generate(prompts[2:], sp)
-    sp_used = tp.core._sp_ok.__self__ is tp.core  # (path selection itself is asserted below via the collective counters)
+    got = tp.generate(prompts[:2], sp)
+    tp.core.sp_prefill = True  # long prompts: exercise the sequence-parallel prefill dataflow end to end
+    got = got + tp.generate(prompts[2:], sp)
     single = Engine.from_pretrained(path, dtype=torch.bfloat16, device=dev, process_group=FakeGroup(0, 1), max_batch=4, max_seq_len=128)
     want_t = single.generate(prompts[:2], sp) + single.generate(prompts[2:], sp)
     agree = sum(g[:4] == w[:4] for g, w in zip(got, want_t))

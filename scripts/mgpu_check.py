@@ -180,6 +180,46 @@ def main():
         log(f"FAIL graph replay: gemm err {e1}, allreduce err {e2}")
     log(f"graph replay done (epoch now {symm.epoch()})")
 
+    # ---- 4b. protocol stress: randomised per-rank arrival skew, alternating kernels / sizes / parities.
+    # (compute-sanitizer's racecheck cannot see inter-GPU races)
+    n_stress = int(sys.argv[sys.argv.index("--stress") + 1]) if "--stress" in sys.argv else 60
+    import random
+    rnd = random.Random(1234 + rank)
+    cases = []
+    for n in (64, 4096, 65536 + 8):
+        torch.manual_seed(500 + rank)
+        x = torch.randn(n, device=dev, dtype=torch.bfloat16)
+        w_ = x.clone()
+        dist.all_reduce(w_)
+        cases.append(("ar", x, w_))
+    torch.manual_seed(600 + rank)
+    xg = torch.randn(32, 1024, device=dev, dtype=torch.bfloat16)
+    wg = torch.randn(1024, 1024, device=dev, dtype=torch.bfloat16) / math.sqrt(1024 * world)
+    eg = xg.float() @ wg.float().t()
+    dist.all_reduce(eg)
+    cases.append(("gemm", (xg, wg), eg))
+    bad = 0
+    for it in range(n_stress):
+        kind, inp, want_ = cases[(it * 7 + 3) % len(cases)]
+        if rnd.random() < 0.5:
+            torch.cuda._sleep(int(rnd.random() * 400000))  # up to ~0.2 ms of skew on this rank only
+        if kind == "ar":
+            y_ = inp.clone()
+            symm.all_reduce_(y_, algo=1 if (it % 3) else 0)
+            e_ = (y_.float() - want_.float()).abs().max().item()
+            tol_ = 0.06 * math.sqrt(world)
+        else:
+            y_ = cu.linear(inp[0], inp[1], symm=symm)
+            e_ = (y_.float() - want_).abs().max().item()
+            tol_ = 0.08
+        if e_ > tol_:
+            bad += 1
+    torch.cuda.synchronize()
+    if bad:
+        ok = False
+        log(f"FAIL stress: {bad}/{n_stress} iterations wrong")
+    log(f"protocol stress ({n_stress} skewed iterations) done", "OK" if bad == 0 else "FAILED")
+
     # ---- latency numbers (device-timed, max over ranks) vs NCCL
     for nbytes in (8 << 10, 64 << 10, 512 << 10):
         x = torch.randn(nbytes // 2, device=dev, dtype=torch.bfloat16)

@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--dtype", default=None, help="bf16 | fp16 (default: bf16 ours, fp16 reference)")
     ap.add_argument("--ckpt-dir", default=os.environ.get("LLMSS_BENCH_CKPT", "/tmp/llmss_b200_bench"))
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--block-size", type=int, default=None, help="KV page size (default: engine's choice, 64 on CUDA)")
     ap.add_argument("--profile-ops", action="store_true", help="eager decode with per-op CUDA-event timing (diagnostic)")
     return ap.parse_args()
 
@@ -153,7 +154,8 @@ def run_ours(args, rank, world, local):
     t0 = time.time()
     eng = Engine.from_pretrained(path, dtype=dtype, device=torch.device("cuda", local), process_group=pg,
                                  max_batch=B, max_seq_len=S + total_new + 16, use_cuda_graph=not args.no_graph,
-                                 max_prefill_tokens=8192, symmetric_bytes=128 << 20, lamport_bytes=64 << 20)
+                                 max_prefill_tokens=8192, symmetric_bytes=128 << 20, lamport_bytes=64 << 20,
+                                 block_size=args.block_size)
     load_s = time.time() - t0
     runner = eng.runner
     prompts = synthetic_prompts(B, S, eng.core.spec.vocab)

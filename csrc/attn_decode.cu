@@ -342,6 +342,27 @@ LLMSS_API int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int m
   return best;
 }
 
+// Merge the split-KV partials ([B, hq, splits, d] + [B, hq, splits, 2]) into `out`; shared with the
+// tensor-core decode kernel (attn_decode_tc.cu).
+LLMSS_API int llmss_attn_decode_combine(const float* part_o, const float* part_ml, void* out, int64_t ldo, int B, int hq,
+                                        int d, int num_splits, int dtype, cudaStream_t stream) {
+  LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_decode_combine: head_dim=%d unsupported", d);
+  if (B == 0) return 0;
+  const dim3 grid(hq, B);
+  const int threads = d < 128 ? d : 128;
+#define LLMSS_C(T_, D_) attn_decode_combine_kernel<T_, D_><<<grid, threads, 0, stream>>>(part_o, part_ml, (T_*)out, ldo, hq, num_splits)
+  if (dtype == LLMSS_F16) {
+    if (d == 64) LLMSS_C(__half, 64); else if (d == 128) LLMSS_C(__half, 128); else LLMSS_C(__half, 256);
+  } else if (dtype == LLMSS_BF16) {
+    if (d == 64) LLMSS_C(__nv_bfloat16, 64); else if (d == 128) LLMSS_C(__nv_bfloat16, 128); else LLMSS_C(__nv_bfloat16, 256);
+  } else {
+    LLMSS_REQUIRE(false, "attn_decode_combine: dtype must be f16/bf16");
+  }
+#undef LLMSS_C
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // Scratch (floats) needed when num_splits > 1.
 LLMSS_API int64_t llmss_attn_decode_scratch_floats(int B, int hq, int d, int num_splits) {
   return num_splits > 1 ? (int64_t)B * hq * num_splits * (d + 2) : 0;

@@ -77,6 +77,19 @@ int llmss_rope_kv_write(void* qkv, const int* positions, const int* slot_mapping
                         int k_off, int v_off, int block_size, int dtype, llmss_stream_t stream);
 
 /* ---- K9 paged split-KV decode attention (G7, G8, G17; gptj_modeling.py:128-169) ---- */
+/* Tensor-core (tcgen05) paged decode attention for grouped / multi-query models (hq / hkv >= 2): the
+ * q heads that share a KV head are the rows of one MMA, so each KV page is read once per group
+ * (reference: baddbmm/softmax/bmm on a replicated KV tensor, gpt_bigcode_modeling.py:170-246).
+ * Same contract as llmss_attn_decode plus num_blocks (pages in the cache); block_size must be 16.
+ * Scratch size: llmss_attn_decode_scratch_floats. */
+int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                         const int* block_tables, int max_blocks, const int* seq_lens, void* out,
+                         int64_t ldo, float* scratch, int B, int hq, int hkv, int d, int block_size,
+                         int num_blocks, float scale, int num_splits, int dtype, llmss_stream_t stream);
+int llmss_attn_decode_tc_pick_splits(int B, int hkv, int d, int max_kv);
+/* Merge split-KV partials (part_o [B,hq,splits,d], part_ml [B,hq,splits,2]) into out. */
+int llmss_attn_decode_combine(const float* part_o, const float* part_ml, void* out, int64_t ldo, int B,
+                              int hq, int d, int num_splits, int dtype, llmss_stream_t stream);
 int64_t llmss_attn_decode_scratch_floats(int B, int hq, int d, int num_splits);
 int llmss_attn_decode_pick_splits(int B, int hq, int hkv, int d, int max_kv, int dtype); /* wave-filling split factor */
 int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,

@@ -52,7 +52,8 @@ class RequestStats:
 
 
 class Engine:
-    def __init__(self, model, max_batch: int = 64, max_seq_len: Optional[int] = None, block_size: int = 16,
+    def __init__(self, model, max_batch: int = 64, max_seq_len: Optional[int] = None,
+                 block_size: Optional[int] = None,
                  num_blocks: Optional[int] = None, use_cuda_graph: Optional[bool] = None,
                  max_prefill_tokens: int = 16384, eos_token_id: Optional[int] = None):
         self.model = model

@@ -58,12 +58,17 @@ class SeqState:
 
 
 class ModelRunner:
-    def __init__(self, core: DecoderLM, max_batch: int = 64, max_seq_len: Optional[int] = None, block_size: int = 16,
-                 num_blocks: Optional[int] = None, use_cuda_graph: Optional[bool] = None):
+    def __init__(self, core: DecoderLM, max_batch: int = 64, max_seq_len: Optional[int] = None,
+                 block_size: Optional[int] = None, num_blocks: Optional[int] = None,
+                 use_cuda_graph: Optional[bool] = None):
         self.core, self.spec = core, core.spec
         self.device, self.dtype = core.device, core.dtype
         self.max_batch = max_batch
         self.max_seq_len = min(max_seq_len or self.spec.max_pos, self.spec.max_pos)
+        if block_size is None:
+            # 64-token pages = one key tile of the tcgen05 decode-attention kernel (one TMA op per K / V
+            # tile); the CPU oracle path and head sizes the kernel does not cover keep 16.
+            block_size = 64 if (self.device.type == "cuda" and core.d in (64, 128, 256)) else 16
         self.block_size = block_size
         self.max_blocks_per_seq = -(-self.max_seq_len // block_size)
         if num_blocks is None:
@@ -237,7 +242,8 @@ class ModelRunner:
             return self._tuned_splits[Bp]
         from ..ops import cuda_impl as cu
 
-        return cu.decode_splits(Bp, self.core.hq, self.core.hkv, self.core.d, self.max_seq_len, self.dtype)
+        return cu.decode_splits(Bp, self.core.hq, self.core.hkv, self.core.d, self.max_seq_len, self.dtype,
+                                self.block_size)
 
     def autotune_decode_splits(self, Bp: int) -> int:
         """Time the split-KV candidates of the decode-attention kernel on this runner's real shape
@@ -257,7 +263,7 @@ class ModelRunner:
         q = torch.randn(Bp, c.q_dim, device=dev, dtype=self.dtype)
         out = torch.empty_like(q)
         kc, vc = self.kv.k(0), self.kv.v(0)
-        base = cu.decode_splits(Bp, c.hq, c.hkv, c.d, L, self.dtype)
+        base = cu.decode_splits(Bp, c.hq, c.hkv, c.d, L, self.dtype, self.block_size)
         cands = sorted({s for s in (1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 24, base) if s <= max(1, L // 64)})
         best, best_t = base, float("inf")
         table = {}

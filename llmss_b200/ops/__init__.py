@@ -107,7 +107,8 @@ def attention(qkv, out, batch, k_cache, v_cache, hq, hkv, d, scale, q_off, k_off
         if d not in (64, 128, 256):
             _warn_once(f"head_dim={d} has no sm_100a attention kernel (64/128/256 do); using the generic PyTorch path")
         elif batch.is_decode:
-            splits = batch.decode_splits or cu.decode_splits(batch.num_seqs, hq, hkv, d, batch.max_kv, qkv.dtype)
+            splits = batch.decode_splits or cu.decode_splits(batch.num_seqs, hq, hkv, d, batch.max_kv, qkv.dtype,
+                                                                     k_cache.shape[2])
             cu.attn_decode(q_view, k_cache, v_cache, batch.block_tables, batch.seq_lens, out_view, hq, hkv, d, scale,
                            splits)
             return out

@@ -49,6 +49,10 @@ _SIGS = {
                                     c_int, c_int, c_int, c_float, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "llmss_attn_decode_scratch_floats": (c_int64, [c_int, c_int, c_int, c_int]),
     "llmss_attn_decode_pick_splits": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int]),
+    "llmss_attn_decode_tc_pick_splits": (c_int, [c_int, c_int, c_int, c_int]),
+    "llmss_attn_decode_tc": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                     c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_int,
+                                     c_int, c_void_p]),
     "llmss_attn_decode": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                   c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_int, c_int,
                                   c_void_p]),

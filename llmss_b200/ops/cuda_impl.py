@@ -7,6 +7,7 @@ a per-device arena allocated once.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -169,11 +170,25 @@ def rope_kv_write(qkv, positions, slot_mapping, k_cache, v_cache, hq, hkv, d, ro
 
 
 # --------------------------------------------------------------------------- attention
-def decode_splits(B: int, hq: int, hkv: int, d: int, max_kv: int, dtype=torch.bfloat16) -> int:
+def decode_splits(B: int, hq: int, hkv: int, d: int, max_kv: int, dtype=torch.bfloat16, block_size: int = 16) -> int:
     """Split-KV factor chosen by the library so the grid fills whole waves of resident CTAs."""
     if d not in (64, 128, 256):
         return 1
+    if use_tc_decode(hq, hkv, d, block_size):
+        return int(_lib.load().llmss_attn_decode_tc_pick_splits(B, hkv, d, max_kv))
     return int(_lib.load().llmss_attn_decode_pick_splits(B, hq, hkv, d, max_kv, _DT[dtype]))
+
+
+_TC_MIN_GROUP = int(os.environ.get("LLMSS_ATTN_TC_MIN_GROUP", "4"))
+
+
+def use_tc_decode(hq: int, hkv: int, d: int, block_size: int = 16) -> bool:
+    """tcgen05 decode attention (q heads of a KV group = MMA rows): always with 64-token pages (one TMA op
+    per tile: 95 % of HBM peak even for MHA), and for grouped / multi-query models with smaller pages."""
+    g = hq // max(hkv, 1)
+    if g > 128 or d not in (64, 128, 256) or block_size not in (16, 32, 64):
+        return False
+    return block_size == 64 or g >= _TC_MIN_GROUP
 
 
 def attn_decode(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, hq, hkv, d, scale, num_splits):
@@ -184,6 +199,14 @@ def attn_decode(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, hq, 
     if num_splits > 1:
         n = lib.llmss_attn_decode_scratch_floats(B, hq, d, num_splits)
         scratch = arena(q_view.device).attn_scratch(n, q_view.device)
+    if use_tc_decode(hq, hkv, d, bs):
+        rc = lib.llmss_attn_decode_tc(_ptr(q_view), q_view.stride(0), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables),
+                                      block_tables.shape[1], _ptr(seq_lens), _ptr(out_view), out_view.stride(0),
+                                      _ptr(scratch), B, hq, hkv, d, bs, k_cache.shape[0], float(scale), num_splits,
+                                      _DT[q_view.dtype], _stream())
+        _lib.check(rc, "llmss_attn_decode_tc")
+        _count(2 if num_splits > 1 else 1)
+        return
     rc = lib.llmss_attn_decode(_ptr(q_view), q_view.stride(0), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables),
                                block_tables.shape[1], _ptr(seq_lens), _ptr(out_view), out_view.stride(0),
                                _ptr(scratch), B, hq, hkv, d, bs, float(scale), num_splits, _DT[q_view.dtype],

@@ -14,8 +14,7 @@ except Exception:
     PEAK_BW = 6545.6e9
 
 
-def bench(B, hq, hkv, d, ctx, splits=None, dtype=torch.bfloat16, reps=6):
-    bs = 16
+def bench(B, hq, hkv, d, ctx, splits=None, dtype=torch.bfloat16, reps=6, bs=16):
     maxb = (ctx + bs - 1) // bs
     nb = 1 + B * maxb
     kc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=dtype)
@@ -24,7 +23,7 @@ def bench(B, hq, hkv, d, ctx, splits=None, dtype=torch.bfloat16, reps=6):
     sl = torch.full((B,), ctx, dtype=torch.int32, device="cuda")
     q = torch.randn(B, hq * d, device="cuda", dtype=dtype)
     out = torch.empty_like(q)
-    sp = splits or cu.decode_splits(B, hq, hkv, d, ctx, dtype)
+    sp = splits or cu.decode_splits(B, hq, hkv, d, ctx, dtype, bs)
     fn = lambda: cu.attn_decode(q, kc, vc, bt, sl, out, hq, hkv, d, d ** -0.5, sp)  # noqa: E731
     for _ in range(3):
         fn()
@@ -45,7 +44,7 @@ def bench(B, hq, hkv, d, ctx, splits=None, dtype=torch.bfloat16, reps=6):
         ts.append(a.elapsed_time(b) * 1e3 / reps)
     t = sorted(ts)[len(ts) // 2]
     bytes_ = 2.0 * B * ctx * hkv * d * 2
-    print(f"B={B:3d} hq={hq:2d} hkv={hkv:2d} d={d:3d} ctx={ctx:5d} splits={sp:2d} | {t:8.1f} us | "
+    print(f"B={B:3d} hq={hq:2d} hkv={hkv:2d} d={d:3d} ctx={ctx:5d} bs={bs:2d} splits={sp:2d} | {t:8.1f} us | "
           f"{bytes_ / t / 1e3:7.1f} GB/s = {100 * bytes_ / (t * 1e-6) / PEAK_BW:5.1f}% of measured HBM peak", flush=True)
     return t
 
@@ -62,3 +61,15 @@ if __name__ == "__main__":
     bench(8, 16, 16, 256, 2000)
     bench(64, 48, 1, 128, 1040)
     bench(64, 6, 1, 128, 1040)
+    for sp in (1, 2, 4, 8):
+        bench(64, 48, 1, 128, 1040, sp)
+    for bs in (16, 64):
+        bench(64, 48, 1, 128, 1040, bs=bs)
+        bench(64, 32, 8, 128, 1040, bs=bs)   # llama-3-style GQA
+        bench(64, 32, 8, 128, 4096, bs=bs)
+        bench(64, 8, 2, 128, 4096, bs=bs)
+    if os.environ.get("LLMSS_BENCH_TC_MHA"):
+        cu._TC_MIN_GROUP = 1
+        for bs in (16, 64):
+            bench(64, 16, 16, 256, 1040, bs=bs)
+            bench(64, 32, 32, 128, 1040, bs=bs)

@@ -143,7 +143,8 @@ def test_rope_kv_write(style, d, rd):
 
 # ------------------------------------------------------------------ decode attention
 @pytest.mark.parametrize("dtype", DT)
-@pytest.mark.parametrize("hq,hkv,d", [(4, 4, 256), (8, 8, 128), (12, 12, 64), (8, 2, 128), (6, 1, 128), (16, 1, 64)])
+@pytest.mark.parametrize("hq,hkv,d", [(4, 4, 256), (8, 8, 128), (12, 12, 64), (8, 2, 128), (6, 1, 128), (16, 1, 64),
+                                      (48, 1, 128), (32, 8, 128), (16, 4, 256), (6, 2, 64)])
 @pytest.mark.parametrize("splits", [1, 4])
 def test_attn_decode(hq, hkv, d, splits, dtype):
     cu = _cu()
@@ -167,6 +168,35 @@ def test_attn_decode(hq, hkv, d, splits, dtype):
     ref = R.attention_paged(q_view.reshape(B, hq, d), kc, vc, bt, sl, cu_q, d ** -0.5).reshape(B, hq * d)
     _close(o_view, ref, 2e-2, 2e-2, "attn_decode")
     assert out[:, :128].abs().sum().item() == 0
+
+
+@pytest.mark.parametrize("bs", [16, 32, 64])
+def test_attn_decode_tc_matches_cuda_core_path(monkeypatch, bs):
+    """Grouped heads: the tcgen05 kernel and the CUDA-core kernel must agree (and both be reachable)."""
+    cu = _cu()
+    torch.manual_seed(1)
+    B, hq, hkv, d = 7, 16, 2, 128
+    lens = [5, 128, 129, 640, 1, 2047, 256]
+    maxb = (max(lens) + bs - 1) // bs
+    nb = 1 + B * maxb
+    kc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=torch.bfloat16)
+    vc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=torch.bfloat16)
+    perm = (torch.randperm(nb - 1) + 1).tolist()
+    bt = torch.tensor([[perm[i * maxb + j] for j in range(maxb)] for i in range(B)], dtype=torch.int32, device="cuda")
+    sl = torch.tensor(lens, dtype=torch.int32, device="cuda")
+    q = torch.randn(B, hq * d, device="cuda", dtype=torch.bfloat16)
+    outs = []
+    for min_group in (4, 1000):  # tensor-core path, then CUDA-core path
+        monkeypatch.setattr(cu, "_TC_MIN_GROUP", min_group)
+        assert cu.use_tc_decode(hq, hkv, d) == (min_group == 4)
+        for splits in (1, 3, 8):
+            o = torch.zeros_like(q)
+            cu.attn_decode(q, kc, vc, bt, sl, o, hq, hkv, d, d ** -0.5, splits)
+            outs.append(o.float())
+    cu_q = torch.arange(B + 1, dtype=torch.int32, device="cuda")
+    ref = R.attention_paged(q.reshape(B, hq, d), kc, vc, bt, sl, cu_q, d ** -0.5).reshape(B, hq * d)
+    for o in outs:
+        _close(o, ref, 2e-2, 2e-2, "attn_decode tc / cuda-core vs oracle")
 
 
 # ------------------------------------------------------------------ embed / sample

@@ -133,17 +133,6 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128_sbo(uint32_t smem_addr, ui
   return d;
 }
 
-// One lane of a converged warp.  Issuing tcgen05 / TMA instructions under this predicate (instead of a
-// long `if (lane == 0)` region) keeps the surrounding address arithmetic warp-uniform, so ptxas feeds the
-// instructions from uniform registers instead of a per-instruction vector->uniform waterfall loop.
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(pred));
-  return pred != 0;
-}
-
 __device__ __forceinline__ void softmax_bar(int threads) { asm volatile("bar.sync 1, %0;" ::"r"(threads) : "memory"); }
 
 // R = how many times the q-head rows are replicated down the 128 MMA rows.  A softmax warp can only read

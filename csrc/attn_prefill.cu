@@ -152,57 +152,69 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
   const uint32_t tS = tmem_base, tO = tmem_base + 2 * BN;  // S buffer b lives at tS + b * BN
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp runs the loop, one elected lane issues) ===============
+    {
       const uint64_t pol = l2_policy_evict_last();
-      mbar_arrive_expect_tx(bar_q, C::Q_BYTES);
-      // the tensor-map box is [BN rows x 64 cols]; a 128-row Q sub-tile is BM / BN stacked boxes
-      // (the 128B-swizzle pattern repeats every 8 rows, so stacked boxes form one contiguous tile)
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bar_q, C::Q_BYTES);
+        // the tensor-map box is [BN rows x 64 cols]; a 128-row Q sub-tile is BM / BN stacked boxes
+        // (the 128B-swizzle pattern repeats every 8 rows, so stacked boxes form one contiguous tile)
 #pragma unroll
-      for (int c = 0; c < DSUB; ++c)
+        for (int c = 0; c < DSUB; ++c)
 #pragma unroll
-        for (int h = 0; h < BM / BN; ++h)
-          tma_load_2d(sQ + c * (BM * 128) + h * (BN * 128), &tmap, bar_q, a.q_col + head * D + c * 64,
-                      seq_start + q0 + h * BN, pol);
+          for (int h = 0; h < BM / BN; ++h)
+            tma_load_2d(sQ + c * (BM * 128) + h * (BN * 128), &tmap, bar_q, a.q_col + head * D + c * 64,
+                        seq_start + q0 + h * BN, pol);
+      }
+      __syncwarp();
       int stage = 0;
       uint32_t phase = 0;
       for (int j = 0; j < n_tiles; ++j) {
         const int row = seq_start + j * BN;
         mbar_wait(&bar_kempty[stage], phase ^ 1, 50);
-        mbar_arrive_expect_tx(&bar_kfull[stage], C::K_BYTES);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&bar_kfull[stage], C::K_BYTES);
 #pragma unroll
-        for (int c = 0; c < DSUB; ++c)
-          tma_load_2d(sK + stage * C::K_BYTES + c * (BN * 128), &tmap, &bar_kfull[stage], a.k_col + kvh * D + c * 64, row, pol);
+          for (int c = 0; c < DSUB; ++c)
+            tma_load_2d(sK + stage * C::K_BYTES + c * (BN * 128), &tmap, &bar_kfull[stage], a.k_col + kvh * D + c * 64, row, pol);
+        }
+        __syncwarp();
         mbar_wait(&bar_vempty[stage], phase ^ 1, 51);
-        mbar_arrive_expect_tx(&bar_vfull[stage], C::V_BYTES);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&bar_vfull[stage], C::V_BYTES);
 #pragma unroll
-        for (int c = 0; c < DSUB; ++c)
-          tma_load_2d(sV + stage * C::V_BYTES + c * (BN * 128), &tmap, &bar_vfull[stage], a.v_col + kvh * D + c * 64, row, pol);
+          for (int c = 0; c < DSUB; ++c)
+            tma_load_2d(sV + stage * C::V_BYTES + c * (BN * 128), &tmap, &bar_vfull[stage], a.v_col + kvh * D + c * 64, row, pol);
+        }
+        __syncwarp();
         if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp runs the loop, one elected lane issues) =================
+    {
       const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
       const uint32_t idesc_s = idesc_f16(fmt, BM, BN, 0);  // S = Q K^T : both operands K-major
       const uint32_t idesc_o = idesc_f16(fmt, BM, D, 1);   // O += P V  : B (= V) is MN-major
-      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
+      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP), k_base = smem_u32(sK), v_base = smem_u32(sV);
       mbar_wait(bar_q, 0, 60);
       int stage = 0;
       uint32_t phase = 0;
       // S is double-buffered in TMEM: QK_{j+1} is issued *before* waiting for P_j, so the tensor cores
       // compute the next score tile while the softmax warps work on the current one.
       auto issue_qk = [&](int st, int buf) {
-        const uint32_t k_addr = smem_u32(sK + st * C::K_BYTES);
+        const uint32_t k_addr = k_base + st * C::K_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int c = 0; c < DSUB; ++c)
+          for (int c = 0; c < DSUB; ++c)
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_f16_ss(tS + buf * BN, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
-                        umma_desc_k_sw128(k_addr + c * (BN * 128) + k * 32), idesc_s, (c | k) ? 1u : 0u);
-        umma_commit(&bar_s[buf]);
-        umma_commit(&bar_kempty[st]);
+            for (int k = 0; k < 4; ++k)
+              umma_f16_ss(tS + buf * BN, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
+                          umma_desc_k_sw128(k_addr + c * (BN * 128) + k * 32), idesc_s, (c | k) ? 1u : 0u);
+          umma_commit(&bar_s[buf]);
+          umma_commit(&bar_kempty[st]);
+        }
+        __syncwarp();
       };
       mbar_wait(&bar_kfull[0], 0, 61);
       tcgen05_fence_after();
@@ -220,16 +232,19 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
         mbar_wait(bar_p, j & 1, 62);
         mbar_wait(&bar_vfull[stage], phase, 63);
         tcgen05_fence_after();
-        const uint32_t v_addr = smem_u32(sV + stage * C::V_BYTES);
+        const uint32_t v_addr = v_base + stage * C::V_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int c = 0; c < NSUB; ++c)
+          for (int c = 0; c < NSUB; ++c)
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_f16_ss(tO, umma_desc_k_sw128(p_addr + c * (BM * 128) + k * 32),
-                        umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
-                        (j > 0 || c > 0 || k > 0) ? 1u : 0u);
-        umma_commit(bar_o);
-        umma_commit(&bar_vempty[stage]);
+            for (int k = 0; k < 4; ++k)
+              umma_f16_ss(tO, umma_desc_k_sw128(p_addr + c * (BM * 128) + k * 32),
+                          umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
+                          (j > 0 || c > 0 || k > 0) ? 1u : 0u);
+          umma_commit(bar_o);
+          umma_commit(&bar_vempty[stage]);
+        }
+        __syncwarp();
         if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
       }
     }

@@ -173,6 +173,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
   }
 }
 
+// One lane of a converged warp.  Issuing tcgen05 / TMA instructions under this predicate (instead of a
+// long `if (lane == 0)` region) keeps the surrounding loop state and address arithmetic warp-uniform, so
+// ptxas feeds UTCHMMA / UTMALDG from uniform registers; inside a divergent single-lane region it emits a
+// vector->uniform "waterfall" (ELECT / R2UR.BROADCAST / BRA.U.ANY, ~18 instructions) per instruction.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");

@@ -302,8 +302,8 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp walks the schedule, one elected lane issues) ==========
+    {
       const uint64_t pol_w = l2_policy_evict_first();  // weights are streamed once
       const uint64_t pol_x = l2_policy_evict_last();   // activations are re-read by every tile
       int stage = 0;
@@ -329,17 +329,21 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, 10);
           uint8_t* sw = smem + stage * C::STAGE_BYTES;
-          mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
-          tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
-          tma_load_2d(sw + C::W_BYTES, xmap, &full_bar[stage], kb * BK, xrow, pol_x);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+            tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
+            tma_load_2d(sw + C::W_BYTES, xmap, &full_bar[stage], kb * BK, xrow, pol_x);
+          }
+          __syncwarp();
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp runs the loop, one elected lane issues) =================
+    {
       const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, BM, BN);
+      const uint32_t smem_base = smem_u32(smem);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -352,22 +356,26 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase, 21);
-          if (a.dbg != nullptr && a.dbg[(size_t)blockIdx.x * 8 + 3] == 0) LLMSS_STAMP(3);
+          if (lane == 0 && a.dbg != nullptr && a.dbg[(size_t)blockIdx.x * 8 + 3] == 0) LLMSS_STAMP(3);
           tcgen05_fence_after();
-          const uint32_t sw = smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint32_t sw = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sx = sw + C::W_BYTES;
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            umma_f16_ss(d_tmem, umma_desc_k_sw128(sw + k * 32), umma_desc_k_sw128(sx + k * 32), idesc,
-                        (kb > sg.kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              umma_f16_ss(d_tmem, umma_desc_k_sw128(sw + k * 32), umma_desc_k_sw128(sx + k * 32), idesc,
+                          (kb > sg.kb0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
+          __syncwarp();
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
+        if (elect_one()) umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
+        __syncwarp();
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      LLMSS_STAMP(4);
+      if (lane == 0) LLMSS_STAMP(4);
     }
   } else {
     // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
@@ -627,41 +635,46 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
-    if (lane == 0) {
-      const uint64_t pol_w = l2_policy_evict_first();
-      const uint64_t pol_x = l2_policy_evict_last();
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1, 40);
-        uint8_t* sw = smem + stage * C::STAGE_BYTES;
+    // whole warp walks the K range, one elected lane issues (see elect_one in common.cuh)
+    const uint64_t pol_w = l2_policy_evict_first();
+    const uint64_t pol_x = l2_policy_evict_last();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(&empty_bar[stage], phase ^ 1, 40);
+      uint8_t* sw = smem + stage * C::STAGE_BYTES;
+      if (elect_one()) {
         mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
         tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
         tma_load_2d(sw + C::W_BYTES, &tmap_x, &full_bar[stage], kb * BK, tm * BN, pol_x);
-        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, BM, BN);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&full_bar[stage], phase, 41);
-        if (kb == kb0) LLMSS_STAMP(3);
-        tcgen05_fence_after();
-        const uint32_t sw = smem_u32(smem + stage * C::STAGE_BYTES);
-        const uint32_t sx = sw + C::W_BYTES;
+    const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, BM, BN);
+    const uint32_t smem_base = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(&full_bar[stage], phase, 41);
+      if (lane == 0 && kb == kb0) LLMSS_STAMP(3);
+      tcgen05_fence_after();
+      const uint32_t sw = smem_base + stage * C::STAGE_BYTES;
+      const uint32_t sx = sw + C::W_BYTES;
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k)
           umma_f16_ss(tmem_base, umma_desc_k_sw128(sw + k * 32), umma_desc_k_sw128(sx + k * 32), idesc,
                       (kb > kb0 || k > 0) ? 1u : 0u);
         umma_commit(&empty_bar[stage]);
-        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(&tfull_bar[0]);
-      LLMSS_STAMP(4);
+      __syncwarp();
+      if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
     }
+    if (elect_one()) umma_commit(&tfull_bar[0]);
+    __syncwarp();
+    if (lane == 0) LLMSS_STAMP(4);
   } else {
     // park the accumulator in shared memory: [(cg*2 + half)][feature] float4, conflict-free
     const int quarter = warp & 3;

@@ -76,6 +76,11 @@ def load(build_if_missing: bool = True):
     if _LIB is not None:
         return _LIB
     path = lib_path()
+    override = os.environ.get("LLMSS_B200_LIB")  # A/B a previously built library (profiling aid)
+    if override:
+        from pathlib import Path
+
+        path, build_if_missing = Path(override), False
     if build_if_missing and os.environ.get("LLMSS_B200_BUILD", "1") == "1":
         try:
             from .build import build_library

@@ -7,11 +7,15 @@
 //
 //   one CTA = 128 queries of one (sequence, q head); it walks the causal range of KV tiles.
 //   warp 0      TMA producer: Q once, then K_j / V_j tiles (2-stage ring), 128B-swizzled
-//   warp 1      one thread issues tcgen05.mma:  S = Q K_j^T   (A,B K-major)      -> TMEM [128 x BN] fp32
-//                                               O += P_j V_j  (B = V, MN-major)  -> TMEM [128 x D]  fp32
+//   warp 1      issues  S_j = Q K_j^T  (A,B K-major) -> TMEM [128 x BN] fp32, double-buffered: S runs up
+//               to two tiles ahead of the softmax (gated only by "softmax has copied S out of TMEM")
+//   warp 6      issues  O += P_j V_j   (B = V, MN-major) -> TMEM [128 x D] fp32, as soon as P_j is published
 //   warps 2-5   one thread per query row: tcgen05.ld its S row, scale + causal mask, online softmax in
-//               fp32 (no shuffles: the row is thread-private), rescale O in TMEM only when the running
-//               max moved, write P_j (bf16/fp16) into shared memory in the UMMA K-major swizzled layout.
+//               fp32 (no shuffles: the row is thread-private), write P_j (bf16/fp16) into one of two
+//               shared-memory buffers in the UMMA K-major swizzled layout.  The running max is lazy: it
+//               only moves when a tile exceeds it by 2^8, so O is rarely rescaled and softmax_{j+1} does
+//               not wait for PV_j -- the tensor pipe (QK_{j+2}, PV_j) and the MUFU pipe overlap.
+//   All tcgen05 / TMA instructions are issued by one elected lane of a converged warp (elect_one).
 //   q, k, v are column ranges of the packed QKV activation (row stride ld*), so the kernel reads
 //   the GEMM output in place; `out` may alias q (the fused GPT-J block writes the context over q).
 //   GQA/MQA: kv head = q head / (hq / hkv).
@@ -23,7 +27,7 @@
 namespace {
 
 constexpr int BM = 128;  // queries per CTA
-constexpr int kThreads = 192;
+constexpr int kThreads = 224;
 
 template <int D>
 struct PCfg {
@@ -33,7 +37,7 @@ struct PCfg {
   static constexpr int K_BYTES = BN * D * 2;
   static constexpr int V_BYTES = BN * D * 2;
   static constexpr int P_BYTES = BM * BN * 2;
-  static constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * (K_BYTES + V_BYTES) + P_BYTES + 1024 + 256;
+  static constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * (K_BYTES + V_BYTES) + 2 * P_BYTES + 1024 + 256;
   static constexpr int TMEM_COLS = (2 * BN + D <= 256) ? 256 : 512;  // S0 at column 0, S1 at BN, O at 2*BN
 };
 
@@ -105,22 +109,24 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
   uint8_t* sK = sQ + C::Q_BYTES;
   uint8_t* sV = sK + C::KV_STAGES * C::K_BYTES;
   uint8_t* sP = sV + C::KV_STAGES * C::V_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * C::P_BYTES);
   uint64_t* bar_q = bars;
   uint64_t* bar_kfull = bars + 1;       // [KV_STAGES]
   uint64_t* bar_vfull = bars + 3;
   uint64_t* bar_kempty = bars + 5;
   uint64_t* bar_vempty = bars + 7;
   uint64_t* bar_s = bars + 9;           // [2] S_j ready in TMEM buffer j & 1 (tcgen05.commit)
-  uint64_t* bar_p = bars + 11;          // P_j written (4 warp arrivals)
-  uint64_t* bar_o = bars + 12;          // PV_j retired (tcgen05.commit)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint64_t* bar_p = bars + 11;          // [2] P_j written into buffer j & 1 (4 warp arrivals)
+  uint64_t* bar_o = bars + 13;          // [2] PV_j retired (tcgen05.commit): P buffer j & 1 free, O stable
+  uint64_t* bar_sfree = bars + 15;      // [2] softmax_j has copied S_j out of TMEM buffer j & 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int seq = blockIdx.z, head = blockIdx.y;
   const int seq_start = a.cu_seqlens[seq];
   const int len = a.cu_seqlens[seq + 1] - seq_start;
-  const int q0 = blockIdx.x * BM;  // first query (position within the sequence) of this CTA
+  // heaviest (longest causal range) query tiles are scheduled first
+  const int q0 = (gridDim.x - 1 - blockIdx.x) * BM;  // first query (position within the sequence) of this CTA
   if (q0 >= len) return;           // uniform for the whole CTA
   const int kvh = head / (a.hq / a.hkv);
   const int kv_end = min(len, q0 + BM);        // causal: keys [0, kv_end)
@@ -135,10 +141,12 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       mbar_init(&bar_kempty[s], 1);
       mbar_init(&bar_vempty[s], 1);
     }
-    mbar_init(&bar_s[0], 1);
-    mbar_init(&bar_s[1], 1);
-    mbar_init(bar_p, 4);
-    mbar_init(bar_o, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_s[i], 1);
+      mbar_init(&bar_p[i], 4);
+      mbar_init(&bar_o[i], 1);
+      mbar_init(&bar_sfree[i], 4);
+    }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -191,64 +199,59 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (whole warp runs the loop, one elected lane issues) =================
-    {
-      const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
-      const uint32_t idesc_s = idesc_f16(fmt, BM, BN, 0);  // S = Q K^T : both operands K-major
-      const uint32_t idesc_o = idesc_f16(fmt, BM, D, 1);   // O += P V  : B (= V) is MN-major
-      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP), k_base = smem_u32(sK), v_base = smem_u32(sV);
-      mbar_wait(bar_q, 0, 60);
-      int stage = 0;
-      uint32_t phase = 0;
-      // S is double-buffered in TMEM: QK_{j+1} is issued *before* waiting for P_j, so the tensor cores
-      // compute the next score tile while the softmax warps work on the current one.
-      auto issue_qk = [&](int st, int buf) {
-        const uint32_t k_addr = k_base + st * C::K_BYTES;
-        if (elect_one()) {
-#pragma unroll
-          for (int c = 0; c < DSUB; ++c)
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_f16_ss(tS + buf * BN, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
-                          umma_desc_k_sw128(k_addr + c * (BN * 128) + k * 32), idesc_s, (c | k) ? 1u : 0u);
-          umma_commit(&bar_s[buf]);
-          umma_commit(&bar_kempty[st]);
-        }
-        __syncwarp();
-      };
-      mbar_wait(&bar_kfull[0], 0, 61);
+    // ===================== QK issuer (whole warp runs the loop, one elected lane issues) =================
+    const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
+    const uint32_t idesc_s = idesc_f16(fmt, BM, BN, 0);  // S = Q K^T : both operands K-major
+    const uint32_t q_addr = smem_u32(sQ), k_base = smem_u32(sK);
+    mbar_wait(bar_q, 0, 60);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int j = 0; j < n_tiles; ++j) {
+      if (j >= 2) mbar_wait(&bar_sfree[j & 1], ((j >> 1) & 1) ^ 1, 64);  // softmax_{j-2} has left this S buffer
+      mbar_wait(&bar_kfull[stage], phase, 61);
       tcgen05_fence_after();
-      issue_qk(0, 0);
-      int kstage = 0;
-      uint32_t kphase = 0;
-      for (int j = 0; j < n_tiles; ++j) {
-        if (j + 1 < n_tiles) {
-          // S buffer (j+1)&1 was last read by softmax_{j-1}, which finished before bar_p_{j-1} completed
-          if (++kstage == C::KV_STAGES) { kstage = 0; kphase ^= 1; }
-          mbar_wait(&bar_kfull[kstage], kphase, 64);
-          tcgen05_fence_after();
-          issue_qk(kstage, (j + 1) & 1);
-        }
-        mbar_wait(bar_p, j & 1, 62);
-        mbar_wait(&bar_vfull[stage], phase, 63);
-        tcgen05_fence_after();
-        const uint32_t v_addr = v_base + stage * C::V_BYTES;
-        if (elect_one()) {
+      const uint32_t k_addr = k_base + stage * C::K_BYTES;
+      if (elect_one()) {
 #pragma unroll
-          for (int c = 0; c < NSUB; ++c)
+        for (int c = 0; c < DSUB; ++c)
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_f16_ss(tO, umma_desc_k_sw128(p_addr + c * (BM * 128) + k * 32),
-                          umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
-                          (j > 0 || c > 0 || k > 0) ? 1u : 0u);
-          umma_commit(bar_o);
-          umma_commit(&bar_vempty[stage]);
-        }
-        __syncwarp();
-        if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ss(tS + (j & 1) * BN, umma_desc_k_sw128(q_addr + c * (BM * 128) + k * 32),
+                        umma_desc_k_sw128(k_addr + c * (BN * 128) + k * 32), idesc_s, (c | k) ? 1u : 0u);
+        umma_commit(&bar_s[j & 1]);
+        umma_commit(&bar_kempty[stage]);
       }
+      __syncwarp();
+      if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
     }
-  } else {
+  } else if (warp == 6) {
+    // ===================== PV issuer =====================
+    const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
+    const uint32_t idesc_o = idesc_f16(fmt, BM, D, 1);   // O += P V  : B (= V) is MN-major
+    const uint32_t p_addr = smem_u32(sP), v_base = smem_u32(sV);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int j = 0; j < n_tiles; ++j) {
+      mbar_wait(&bar_p[j & 1], (j >> 1) & 1, 62);
+      mbar_wait(&bar_vfull[stage], phase, 63);
+      tcgen05_fence_after();
+      const uint32_t v_addr = v_base + stage * C::V_BYTES;
+      const uint32_t pj = p_addr + (j & 1) * C::P_BYTES;
+      if (elect_one()) {
+#pragma unroll
+        for (int c = 0; c < NSUB; ++c)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ss(tO, umma_desc_k_sw128(pj + c * (BM * 128) + k * 32),
+                        umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
+                        (j > 0 || c > 0 || k > 0) ? 1u : 0u);
+        umma_commit(&bar_o[j & 1]);
+        umma_commit(&bar_vempty[stage]);
+      }
+      __syncwarp();
+      if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp < 6) {
     // ===================== softmax / correction / epilogue: one thread per query row =====================
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;         // query row within the tile == TMEM lane
@@ -270,6 +273,9 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
 #pragma unroll
         for (int i = 0; i < 32; ++i) sc[c * 32 + i] = __uint_as_float(r[i]);
       }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_sfree[j & 1]);  // S_j is in registers: the buffer can take QK_{j+2}
       if (diag) {
 #pragma unroll
         for (int i = 0; i < BN; ++i)
@@ -278,30 +284,18 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       float m_tile = -INFINITY;
 #pragma unroll
       for (int i = 0; i < BN; ++i) m_tile = fmaxf(m_tile, sc[i]);
-      const float m_new = fmaxf(m_run, m_tile * a.scale_log2);  // scale > 0: max commutes with scaling
-      const float alpha = (m_run == -INFINITY) ? 0.f : ex2_approx(m_run - m_new);
-      // PV_{j-1} must have retired before O is rescaled and before P is overwritten
-      if (j > 0) {
-        mbar_wait(bar_o, (j - 1) & 1, 71);
-        tcgen05_fence_after();
-        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
-#pragma unroll 1
-          for (int c = 0; c < D / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-            tmem_st_32x32b_x32(tO + lane_off + c * 32, r);
-          }
-          tmem_st_wait();
-        }
-      }
-      l_run *= alpha;
+      // Lazy running max (scale > 0: max commutes with scaling): keep the old reference unless this tile
+      // exceeds it by more than 2^8 -- p stays <= 256, far inside fp32 / bf16 / fp16 range.
+      const float m_tile_s = m_tile * a.scale_log2;
+      const bool grow = (j == 0) || (m_tile_s > m_run + 8.0f);
+      const float m_new = grow ? fmaxf(m_run, m_tile_s) : m_run;
+      const float alpha = (j == 0 || !grow) ? 1.0f : ex2_approx(m_run - m_new);
       m_run = m_new;
       // p = 2^(s*scale - m): one FFMA + one MUFU per element; P -> shared memory (K-major, chunk ^= row & 7)
       const float neg_m = (m_new == -INFINITY) ? 0.f : -m_new;
+      if (j >= 2) mbar_wait(&bar_o[j & 1], ((j >> 1) & 1) ^ 1, 71);  // PV_{j-2} has released this P buffer
       float l_tile = 0.f;
+      uint8_t* pbuf = sP + (j & 1) * C::P_BYTES;
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t pk[16];
@@ -312,21 +306,35 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
           l_tile += p0 + p1;
           pk[i >> 1] = pack2<T>(p0, p1);
         }
-        uint8_t* sub = sP + (c >> 1) * (BM * 128) + row * 128;
+        uint8_t* sub = pbuf + (c >> 1) * (BM * 128) + row * 128;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int chunk = ((c & 1) * 4 + q) ^ (row & 7);
           *reinterpret_cast<uint4*>(sub + chunk * 16) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
         }
       }
-      l_run += l_tile;
+      if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
+        mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1, 73);  // PV_{j-1} retired: O is stable
+        tcgen05_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st_32x32b_x32(tO + lane_off + c * 32, r);
+        }
+        tmem_st_wait();
+      }
+      l_run = l_run * alpha + l_tile;
       tcgen05_fence_before();
       fence_proxy_async_smem();  // generic-proxy writes of P must be visible to the tensor-core (async) proxy
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_p);
+      if (lane == 0) mbar_arrive(&bar_p[j & 1]);
     }
     // epilogue: O / l -> out
-    mbar_wait(bar_o, (n_tiles - 1) & 1, 72);
+    mbar_wait(&bar_o[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1, 72);
     tcgen05_fence_after();
     const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
     T* orow = reinterpret_cast<T*>(a.out) + (int64_t)(seq_start + qpos) * a.ldo + (int64_t)head * D;

@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
     const int* __restrict__ block_tables, int max_blocks, const int* __restrict__ seq_lens, T* __restrict__ out,
     int64_t ldo, float* __restrict__ part_o, float* __restrict__ part_ml, int hq, int hkv, int block_size,
     float scale_log2, int num_splits) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int LPT = D / 8;     // lanes per token row
   constexpr int TPW = 32 / LPT;  // tokens per warp-wide load
   static_assert(LPT >= 1 && LPT <= 32 && (32 % LPT) == 0, "head_dim must be 8..256, power of two");
@@ -241,6 +243,8 @@ __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
 template <typename T, int D>
 __global__ void attn_decode_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                                            T* __restrict__ out, int64_t ldo, int hq, int num_splits) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int head = blockIdx.x, b = blockIdx.y;
   const int64_t base = ((int64_t)b * hq + head) * num_splits;
   float mn = -INFINITY;
@@ -350,7 +354,8 @@ LLMSS_API int llmss_attn_decode_combine(const float* part_o, const float* part_m
   if (B == 0) return 0;
   const dim3 grid(hq, B);
   const int threads = d < 128 ? d : 128;
-#define LLMSS_C(T_, D_) attn_decode_combine_kernel<T_, D_><<<grid, threads, 0, stream>>>(part_o, part_ml, (T_*)out, ldo, hq, num_splits)
+#define LLMSS_C(T_, D_) \
+  LLMSS_CHECK_CUDA(launch_pdl(attn_decode_combine_kernel<T_, D_>, grid, dim3(threads), 0, stream, part_o, part_ml, (T_*)out, ldo, hq, num_splits))
   if (dtype == LLMSS_F16) {
     if (d == 64) LLMSS_C(__half, 64); else if (d == 128) LLMSS_C(__half, 128); else LLMSS_C(__half, 256);
   } else if (dtype == LLMSS_BF16) {

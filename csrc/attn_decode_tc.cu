@@ -173,6 +173,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = a.G;
+  pdl_launch_dependents();
   constexpr int QPC = 4 / R;  // softmax warps (TMEM lane quarters) per copy
   int n_live_warps = 0;
   for (int q = 0; q < 4; ++q) n_live_warps += ((q % QPC) * 32 < G) ? 1 : 0;
@@ -206,6 +207,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tS = tmem_base, tO = tmem_base + 2 * BN;
+  pdl_wait();  // q, the KV cache and the step metadata come from earlier kernels of the stream
 
   if (warp == 0) {
     // ===================== TMA producer: runs ahead across items through the K/V ring =====================
@@ -552,8 +554,7 @@ int launch_decode_tc(const CUtensorMap& tq, const CUtensorMap& tk, const CUtenso
     configured = smem;
   }
   const int grid = a.n_items < sm_count() ? a.n_items : sm_count();
-  kern<<<grid, kThreads, smem, stream>>>(tq, tk, tv, a);
-  LLMSS_CHECK_CUDA(cudaGetLastError());
+  LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, tq, tk, tv, a));
   return 0;
 }
 

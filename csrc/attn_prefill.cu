@@ -123,6 +123,8 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int seq = blockIdx.z, head = blockIdx.y;
+  pdl_launch_dependents();
+  pdl_wait();
   const int seq_start = a.cu_seqlens[seq];
   const int len = a.cu_seqlens[seq + 1] - seq_start;
   // heaviest (longest causal range) query tiles are scheduled first
@@ -388,8 +390,7 @@ int launch_prefill(const CUtensorMap& tm, const PArgs& a, int num_seqs, int max_
     configured = true;
   }
   dim3 grid((max_seqlen + BM - 1) / BM, a.hq, num_seqs);
-  kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(tm, a);
-  LLMSS_CHECK_CUDA(cudaGetLastError());
+  LLMSS_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), (size_t)C::SMEM_BYTES, stream, tm, a));
   return 0;
 }
 

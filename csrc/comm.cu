@@ -22,6 +22,7 @@
 #include "symm.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 // ---------------------------------------------------------------- error string
@@ -36,6 +37,17 @@ LLMSS_API const char* llmss_last_error() { return g_err; }
 LLMSS_API int llmss_version() { return 100; }
 
 // ---------------------------------------------------------------- symmetric memory plumbing
+bool llmss_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    // Off by default: measured at TP=1 and TP=2 (GPT-J-6B decode, CUDA graph) it changes nothing --
+    // every hot kernel is one fat persistent CTA per SM, so the next kernel's CTAs cannot become
+    // resident before the previous ones retire anyway.  LLMSS_PDL=1 turns the launch attribute on.
+    const char* e = getenv("LLMSS_PDL");
+    v = (e != nullptr && e[0] == '1') ? 1 : 0;
+  }
+  return v != 0;
+}
 namespace {
 __global__ void fill_u32_kernel(uint32_t* p, size_t n, uint32_t v) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
@@ -145,6 +157,8 @@ __device__ __forceinline__ void accum8<float>(float (&acc)[8], const uint4& raw)
 template <typename T>
 __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(SymmWs ws, const uint4* __restrict__ in,
                                                                      uint4* __restrict__ out, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int EB = std::is_same<T, float>::value ? 4 : 2;
   const uint32_t e = *ws.epoch + 1;
   const int par = e & 1;
@@ -183,6 +197,8 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(SymmWs ws, 
 template <typename T>
 __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(SymmWs ws, const uint4* __restrict__ in,
                                                                      uint4* __restrict__ out, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   const uint32_t e = *ws.epoch + 1;
   const int par = e & 1;
   const int n = ws.nranks;
@@ -248,6 +264,8 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(SymmWs ws, 
 // ---- all-gather: out[r] = rank r's input (used for the vocab-parallel logits, reference N3)
 __global__ void __launch_bounds__(kThreads) allgather_kernel(SymmWs ws, const uint4* __restrict__ in,
                                                              uint4* __restrict__ out, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   const uint32_t e = *ws.epoch + 1;
   const int par = e & 1;
   const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
@@ -312,14 +330,14 @@ LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, 
   SymmWs w = *ws;
   if (algo == 1) {
     const int grid = pick_grid(nvec, 128);
-    if (dtype == LLMSS_F16) allreduce_oneshot_kernel<__half><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
-    else if (dtype == LLMSS_BF16) allreduce_oneshot_kernel<__nv_bfloat16><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
-    else allreduce_oneshot_kernel<float><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+    if (dtype == LLMSS_F16) LLMSS_CHECK_CUDA(launch_pdl(allreduce_oneshot_kernel<__half>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    else if (dtype == LLMSS_BF16) LLMSS_CHECK_CUDA(launch_pdl(allreduce_oneshot_kernel<__nv_bfloat16>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    else LLMSS_CHECK_CUDA(launch_pdl(allreduce_oneshot_kernel<float>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
   } else {
     const int grid = pick_grid(nvec / ws->nranks, 144);
-    if (dtype == LLMSS_F16) allreduce_twoshot_kernel<__half><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
-    else if (dtype == LLMSS_BF16) allreduce_twoshot_kernel<__nv_bfloat16><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
-    else allreduce_twoshot_kernel<float><<<grid, kThreads, 0, stream>>>(w, (const uint4*)in, (uint4*)out, nvec);
+    if (dtype == LLMSS_F16) LLMSS_CHECK_CUDA(launch_pdl(allreduce_twoshot_kernel<__half>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    else if (dtype == LLMSS_BF16) LLMSS_CHECK_CUDA(launch_pdl(allreduce_twoshot_kernel<__nv_bfloat16>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    else LLMSS_CHECK_CUDA(launch_pdl(allreduce_twoshot_kernel<float>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
   }
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -336,7 +354,8 @@ LLMSS_API int llmss_allgather(SymmWs* ws, const void* in, void* out, int64_t byt
   LLMSS_REQUIRE((size_t)(bytes * ws->nranks) <= ws->buf_bytes, "allgather: %lld bytes x %d ranks exceeds workspace %zu",
                 (long long)bytes, ws->nranks, ws->buf_bytes);
   const int64_t nvec = bytes / 16;
-  allgather_kernel<<<pick_grid(nvec, 128), kThreads, 0, stream>>>(*ws, (const uint4*)in, (uint4*)out, nvec);
+  LLMSS_CHECK_CUDA(launch_pdl(allgather_kernel, dim3(pick_grid(nvec, 128)), dim3(kThreads), 0, stream, *ws, (const uint4*)in,
+                              (uint4*)out, nvec));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

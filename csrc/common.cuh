@@ -11,6 +11,8 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
+#include <utility>
 #include <type_traits>
 
 #define LLMSS_API extern "C" __attribute__((visibility("default")))
@@ -103,6 +105,33 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
+}
+
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the library starts with pdl_launch_dependents() (the next kernel of the stream may be
+// scheduled as soon as all our CTAs are resident) and calls pdl_wait() before it touches anything the
+// previous kernel may have written: barrier init, TMEM allocation, descriptor prefetch and the launch
+// latency itself then overlap the tail of the previous kernel.  Both are no-ops for a plain launch.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+bool llmss_pdl_enabled();  // comm.cu: LLMSS_PDL=1 enables the launch attribute (default off: no measured gain)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = llmss_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
 // ---------------------------------------------------------------- watchdog

@@ -13,6 +13,8 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ toke
                                                     const T* __restrict__ wte, const T* __restrict__ wpe,
                                                     T* __restrict__ out, int H, int vocab, int max_pos, int pos_offset,
                                                     int64_t ldo) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   int tok = tokens[t];
   tok = min(max(tok, 0), vocab - 1);
@@ -45,12 +47,9 @@ LLMSS_API int llmss_embed(const int* tokens, const int* positions, const void* w
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "embed: dtype must be f16/bf16");
   if (T == 0) return 0;
   if (dtype == LLMSS_F16)
-    embed_kernel<__half><<<T, 128, 0, stream>>>(tokens, positions, (const __half*)wte, (const __half*)wpe, (__half*)out,
-                                                H, vocab, max_pos, pos_offset, ldo);
+    LLMSS_CHECK_CUDA(launch_pdl(embed_kernel<__half>, dim3(T), dim3(128), 0, stream, tokens, positions, (const __half*)wte, (const __half*)wpe, (__half*)out, H, vocab, max_pos, pos_offset, ldo));
   else
-    embed_kernel<__nv_bfloat16><<<T, 128, 0, stream>>>(tokens, positions, (const __nv_bfloat16*)wte,
-                                                       (const __nv_bfloat16*)wpe, (__nv_bfloat16*)out, H, vocab,
-                                                       max_pos, pos_offset, ldo);
+    LLMSS_CHECK_CUDA(launch_pdl(embed_kernel<__nv_bfloat16>, dim3(T), dim3(128), 0, stream, tokens, positions, (const __nv_bfloat16*)wte, (const __nv_bfloat16*)wpe, (__nv_bfloat16*)out, H, vocab, max_pos, pos_offset, ldo));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

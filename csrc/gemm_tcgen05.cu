@@ -273,10 +273,8 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = gridDim.x, g = blockIdx.x;
   const int tiles = a.tiles_n * a.tiles_m;
+  pdl_launch_dependents();
   if (threadIdx.x == 0) LLMSS_STAMP(0);
-
-  uint32_t epoch = 0;
-  if (a.ar || a.ag) epoch = *a.ws.epoch + 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_w);
@@ -299,6 +297,9 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything below reads what earlier kernels of the stream wrote (x, workspaces, epoch)
+  uint32_t epoch = 0;
+  if (a.ar || a.ag) epoch = *a.ws.epoch + 1;
   if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
@@ -608,10 +609,8 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   const int kb0 = (int)(((int64_t)r * a.kb_total) / S), kb1 = (int)(((int64_t)(r + 1) * a.kb_total) / S);
   constexpr int NG = BN / 8;
   constexpr int TCOLS = BN < 32 ? 32 : BN;
+  pdl_launch_dependents();
   if (threadIdx.x == 0) LLMSS_STAMP(0);
-
-  uint32_t epoch = 0;
-  if (a.ar) epoch = *a.ws.epoch + 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_w);
@@ -632,6 +631,9 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   float4* staging = reinterpret_cast<float4*>(smem);  // [NG*2][128] float4, reuses the drained TMA ring
+  pdl_wait();  // everything below reads what earlier kernels of the stream wrote (x, workspaces, epoch)
+  uint32_t epoch = 0;
+  if (a.ar) epoch = *a.ws.epoch + 1;
   if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
@@ -817,7 +819,7 @@ int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int 
     LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     configured = true;
   }
-  kern<<<grid, kNumThreads, C::SMEM_BYTES, stream>>>(tw, tx, a);
+  LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, a));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -838,13 +840,15 @@ int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs&
   cfg.blockDim = dim3(kNumThreads);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = split;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = llmss_pdl_enabled() ? 2 : 1;
   LLMSS_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, a));
   return 0;
 }

@@ -27,6 +27,8 @@ __global__ void __launch_bounds__(kThreads) norm_residual_kernel(
     const T* __restrict__ x, const T* __restrict__ x2, const T* residual_in, T* residual_out,
     const T* __restrict__ weight, const T* __restrict__ bias, T* __restrict__ out, int H, int64_t ldx,
     int64_t ldx2, int64_t ldr, int64_t ldo, float eps, int kind) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[kThreads / 32];
   const int row = blockIdx.x;
   const int nvec = H >> 3;
@@ -111,14 +113,9 @@ LLMSS_API int llmss_norm_residual(const void* x, const void* x2, const void* res
   LLMSS_REQUIRE(ldx % 8 == 0 && ldo % 8 == 0 && ldr % 8 == 0 && ldx2 % 8 == 0, "norm_residual: row strides must be multiples of 8");
   if (M == 0) return 0;
   if (dtype == LLMSS_F16)
-    norm_residual_kernel<__half><<<M, kThreads, 0, stream>>>(
-        (const __half*)x, (const __half*)x2, (const __half*)residual_in, (__half*)residual_out, (const __half*)weight,
-        (const __half*)bias, (__half*)out, H, ldx, ldx2, ldr, ldo, eps, kind);
+    LLMSS_CHECK_CUDA(launch_pdl(norm_residual_kernel<__half>, dim3(M), dim3(kThreads), 0, stream, (const __half*)x, (const __half*)x2, (const __half*)residual_in, (__half*)residual_out, (const __half*)weight, (const __half*)bias, (__half*)out, H, ldx, ldx2, ldr, ldo, eps, kind));
   else
-    norm_residual_kernel<__nv_bfloat16><<<M, kThreads, 0, stream>>>(
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)x2, (const __nv_bfloat16*)residual_in,
-        (__nv_bfloat16*)residual_out, (const __nv_bfloat16*)weight, (const __nv_bfloat16*)bias, (__nv_bfloat16*)out, H,
-        ldx, ldx2, ldr, ldo, eps, kind);
+    LLMSS_CHECK_CUDA(launch_pdl(norm_residual_kernel<__nv_bfloat16>, dim3(M), dim3(kThreads), 0, stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)x2, (const __nv_bfloat16*)residual_in, (__nv_bfloat16*)residual_out, (const __nv_bfloat16*)weight, (const __nv_bfloat16*)bias, (__nv_bfloat16*)out, H, ldx, ldx2, ldr, ldo, eps, kind));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

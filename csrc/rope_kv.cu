@@ -16,6 +16,8 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
     T* __restrict__ qkv, const int* __restrict__ positions, const int* __restrict__ slot_mapping,
     T* __restrict__ k_cache, T* __restrict__ v_cache, int64_t ld, int hq, int hkv, int d, int rotary_dim,
     int style, float log2_base, int q_off, int k_off, int v_off, int block_size) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_cos[128], s_sin[128];  // rotary_dim / 2 <= 128 frequencies
   const int t = blockIdx.x;
   const float pos = (float)positions[t];
@@ -114,13 +116,9 @@ LLMSS_API int llmss_rope_kv_write(void* qkv, const int* positions, const int* sl
   if (T == 0) return 0;
   const float log2_base = log2f(base);
   if (dtype == LLMSS_F16)
-    rope_kv_write_kernel<__half><<<T, 128, 0, stream>>>((__half*)qkv, positions, slot_mapping, (__half*)k_cache,
-                                                        (__half*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base,
-                                                        q_off, k_off, v_off, block_size);
+    LLMSS_CHECK_CUDA(launch_pdl(rope_kv_write_kernel<__half>, dim3(T), dim3(128), 0, stream, (__half*)qkv, positions, slot_mapping, (__half*)k_cache, (__half*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base, q_off, k_off, v_off, block_size));
   else
-    rope_kv_write_kernel<__nv_bfloat16><<<T, 128, 0, stream>>>(
-        (__nv_bfloat16*)qkv, positions, slot_mapping, (__nv_bfloat16*)k_cache, (__nv_bfloat16*)v_cache, ld, hq, hkv, d,
-        rotary_dim, style, log2_base, q_off, k_off, v_off, block_size);
+    LLMSS_CHECK_CUDA(launch_pdl(rope_kv_write_kernel<__nv_bfloat16>, dim3(T), dim3(128), 0, stream, (__nv_bfloat16*)qkv, positions, slot_mapping, (__nv_bfloat16*)k_cache, (__nv_bfloat16*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base, q_off, k_off, v_off, block_size));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

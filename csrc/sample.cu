@@ -53,6 +53,8 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(
     const float* __restrict__ logits, int64_t ld, int vocab, const int* __restrict__ greedy,
     const float* __restrict__ temperature, const int* __restrict__ top_k, const float* __restrict__ top_p,
     uint32_t* __restrict__ rng_state, int* __restrict__ out_tokens, long long* __restrict__ out_tokens64) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[32];
   __shared__ int redi[32];
   __shared__ int hist[256];
@@ -287,8 +289,7 @@ LLMSS_API int llmss_sample(const float* logits, int64_t ld, int B, int vocab, co
                            int* out_tokens, long long* out_tokens64, cudaStream_t stream) {
   LLMSS_REQUIRE(vocab > 0 && ld >= vocab, "sample: bad vocab/ld");
   if (B == 0) return 0;
-  sample_kernel<<<B, kThreads, 0, stream>>>(logits, ld, vocab, greedy, temperature, top_k, top_p, rng_state,
-                                            out_tokens, out_tokens64);
+  LLMSS_CHECK_CUDA(launch_pdl(sample_kernel, dim3(B), dim3(kThreads), 0, stream, logits, ld, vocab, greedy, temperature, top_k, top_p, rng_state, out_tokens, out_tokens64));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -156,74 +156,94 @@ __device__ __forceinline__ float act_fast(float x, int act) {
   return x;
 }
 
+// Residual values of one 8-token group, fetched ahead of the accumulator so that their L2 latency is
+// paid once per chunk of groups instead of once per group (the epilogue of the last tile is exposed).
 template <typename T>
-__device__ __forceinline__ void epilogue_store8(const GemmArgs& a, const float (&v)[8], int n, int mb, int lane,
-                                                float bval, int m_limit) {
-  const int rows = m_limit - mb;  // valid token rows in this group (may be <= 0 or >= 8)
+__device__ __forceinline__ void epilogue_load_res8(const GemmArgs& a, float (&rv)[8], int n, int mb, int lane, int m_limit) {
+  const int rows = m_limit - mb;
+  const int nn = (a.epi == EPI_GATED) ? (n >> 1) : n;
+  const bool mine = (a.epi == EPI_GATED) ? ((lane & 1) == 0 && n < a.N) : (n < a.N);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) rv[j] = 0.f;
+  if (a.residual == nullptr || !mine) return;
+  const T* r = reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + nn;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < rows) rv[j] = to_f32(r[(int64_t)j * a.ldr]);
+}
+
+// The epilogue of a tile runs once or twice per CTA, so every instruction it executes is an instruction-
+// cache miss: what matters is how much code is *executed*, not how much exists.  The flavour (plain /
+// activation / gated / fp32) and the activation are therefore template parameters selected once per chunk
+// of CH groups; inside, the code is straight-line and branch-free (a runtime `switch` per element made
+// the GELU epilogue of the fused QKV+up GEMM cost 25 us of a 70 us kernel).
+constexpr int ACT_RUNTIME = -1;  // rare combinations: decided per element by act_fast
+
+template <int ACT>
+__device__ __forceinline__ float act_t(float x, int runtime_act) {
+  if constexpr (ACT == LLMSS_ACT_NONE) return x;
+  else if constexpr (ACT == LLMSS_ACT_GELU_TANH) return 0.5f * x * (1.0f + tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+  else if constexpr (ACT == LLMSS_ACT_SILU) return __fdividef(x, 1.0f + __expf(-x));
+  else return act_fast(x, runtime_act);
+}
+
+template <typename T, int CH, int EPI, int ACT>
+__device__ __forceinline__ void store_chunk_t(const GemmArgs& a, const float (&v)[CH][8], const float (&rv)[CH][8], int n,
+                                              int mb0, int lane, float bval, int m_limit) {
   const bool n_ok = n < a.N;
-  switch (a.epi) {
-    case EPI_PLAIN: {
-      if (!n_ok) return;
-      T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + n;
-      if (a.residual != nullptr) {
-        const T* r = reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + n;
+  const bool do_act = n >= a.act_start;  // per lane; tiles are 128 features wide, act_start usually is too
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j < rows) o[(int64_t)j * a.ldo] = from_f32<T>(v[j] + bval + to_f32(r[(int64_t)j * a.ldr]));
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j < rows) o[(int64_t)j * a.ldo] = from_f32<T>(v[j] + bval);
-      }
-      return;
-    }
-    case EPI_ACT: {
-      if (!n_ok) return;
-      T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + n;
-      const int act = (n >= a.act_start) ? a.act : LLMSS_ACT_NONE;
-      const T* r = a.residual != nullptr ? reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + n : nullptr;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (j < rows) {
-          float y = act_fast(v[j] + bval, act);
-          if (r != nullptr) y += to_f32(r[(int64_t)j * a.ldr]);
-          o[(int64_t)j * a.ldo] = from_f32<T>(y);
-        }
-      }
-      return;
-    }
-    case EPI_GATED: {
+  for (int u = 0; u < CH; ++u) {
+    const int mb = mb0 + u * 8;
+    const int rows = m_limit - mb;  // valid token rows in this group (may be <= 0 or >= 8)
+    if constexpr (EPI == EPI_GATED) {
       // rows of w interleave (gate, up): even lane holds gate_j, odd lane up_j of output feature n/2
       T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + (n >> 1);
-      const T* r = a.residual != nullptr ? reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + (n >> 1) : nullptr;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float y = v[j] + bval;
+        const float y = v[u][j] + bval;
         const float other = __shfl_xor_sync(0xffffffffu, y, 1);
-        if ((lane & 1) == 0 && n_ok && j < rows) {
-          float g = act_fast(y, a.act) * other;
-          if (r != nullptr) g += to_f32(r[(int64_t)j * a.ldr]);
-          o[(int64_t)j * a.ldo] = from_f32<T>(g);
-        }
+        if ((lane & 1) == 0 && n_ok && j < rows) o[(int64_t)j * a.ldo] = from_f32<T>(act_t<ACT>(y, a.act) * other + rv[u][j]);
       }
-      return;
-    }
-    default: {  // EPI_F32: fp32 output (LM head logits), optional bias / activation / residual
-      if (!n_ok) return;
+    } else if constexpr (EPI == EPI_F32) {
       float* o = reinterpret_cast<float*>(a.out) + (int64_t)mb * a.ldo + n;
-      const int act = (n >= a.act_start) ? a.act : LLMSS_ACT_NONE;
-      const T* r = a.residual != nullptr ? reinterpret_cast<const T*>(a.residual) + (int64_t)mb * a.ldr + n : nullptr;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        if (j < rows) {
-          float y = act_fast(v[j] + bval, act);
-          if (r != nullptr) y += to_f32(r[(int64_t)j * a.ldr]);
-          o[(int64_t)j * a.ldo] = y;
-        }
+        const float x = v[u][j] + bval;
+        const float y = (ACT == LLMSS_ACT_NONE || !do_act) ? x : act_t<ACT>(x, a.act);
+        if (n_ok && j < rows) o[(int64_t)j * a.ldo] = y + rv[u][j];
       }
-      return;
+    } else {
+      T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb * a.ldo + n;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x = v[u][j] + bval;
+        const float y = (ACT == LLMSS_ACT_NONE || !do_act) ? x : act_t<ACT>(x, a.act);
+        if (n_ok && j < rows) o[(int64_t)j * a.ldo] = from_f32<T>(y + rv[u][j]);
+      }
     }
   }
+}
+
+template <typename T, int CH>
+__device__ __forceinline__ void store_chunk(const GemmArgs& a, const float (&v)[CH][8], const float (&rv)[CH][8], int n,
+                                            int mb0, int lane, float bval, int m_limit) {
+#define LLMSS_SC(EPI_, ACT_) store_chunk_t<T, CH, EPI_, ACT_>(a, v, rv, n, mb0, lane, bval, m_limit)
+  if (a.epi == EPI_PLAIN) {
+    LLMSS_SC(EPI_PLAIN, LLMSS_ACT_NONE);
+  } else if (a.epi == EPI_ACT) {
+    if (a.act == LLMSS_ACT_GELU_TANH) LLMSS_SC(EPI_ACT, LLMSS_ACT_GELU_TANH);
+    else if (a.act == LLMSS_ACT_SILU) LLMSS_SC(EPI_ACT, LLMSS_ACT_SILU);
+    else LLMSS_SC(EPI_ACT, ACT_RUNTIME);
+  } else if (a.epi == EPI_GATED) {
+    if (a.act == LLMSS_ACT_SILU) LLMSS_SC(EPI_GATED, LLMSS_ACT_SILU);
+    else if (a.act == LLMSS_ACT_GELU_TANH) LLMSS_SC(EPI_GATED, LLMSS_ACT_GELU_TANH);
+    else LLMSS_SC(EPI_GATED, ACT_RUNTIME);
+  } else {
+    if (a.act == LLMSS_ACT_NONE) LLMSS_SC(EPI_F32, LLMSS_ACT_NONE);
+    else LLMSS_SC(EPI_F32, ACT_RUNTIME);
+  }
+#undef LLMSS_SC
 }
 
 // ---- thread-block-cluster helpers (split-K kernel) ----
@@ -490,53 +510,71 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[as]);
           }
+          // Groups of 8 token columns are processed CH at a time: all global loads of a chunk (residual,
+          // stream-K partials) are issued before any of them is consumed, so the exposed tail pays one
+          // L2 round trip per chunk and contributor instead of one per group.
+          constexpr int CH = NG < 4 ? NG : 4;
+          const bool storing = (pass == n_pass - 1);
+          const int mrow0 = (a.ar == 2) ? m0 - a.ws.rank * a.rs_rows : m0;
+          const int mlim = (a.ar == 2) ? a.rs_rows : a.M;
 #pragma unroll 1
-          for (int cg = 0; cg < NG; ++cg) {
-            float v[8];
-            const size_t xoff = ((size_t)xtile * NG + cg) * (BM * 16) + (size_t)f * 16;  // exchange-buffer offset
+          for (int cg0 = 0; cg0 < NG; cg0 += CH) {
+            float v[CH][8], rv[CH][8];
+            if (storing && a.residual != nullptr) {
+#pragma unroll
+              for (int u = 0; u < CH; ++u) epilogue_load_res8<T>(a, rv[u], n, mrow0 + (cg0 + u) * 8, lane, mlim);
+            } else {
+#pragma unroll
+              for (int u = 0; u < CH; ++u)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) rv[u][j] = 0.f;
+            }
             if (pass == 0) {
               if (full_tile) {
-                uint32_t r[8];
-                tmem_ld_32x32b_x8(t_addr + cg * 8, r);
-                tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]);
+                for (int u = 0; u < CH; ++u) {
+                  uint32_t r[8];
+                  tmem_ld_32x32b_x8(t_addr + (cg0 + u) * 8, r);
+                  tmem_ld_wait();
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) v[u][j] = __uint_as_float(r[j]);
+                }
               } else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = 0.f;
-                // contributors are summed in CTA order (deterministic); four are fetched per
-                // round trip so the L2 latency is paid once per 4 contributors, not once each
-                for (int c0 = sg.first_cta; c0 <= sg.last_cta; c0 += 4) {
-                  float4 t[4][2];
+                for (int u = 0; u < CH; ++u)
 #pragma unroll
-                  for (int u = 0; u < 4; ++u) {
-                    const int cta = c0 + u;
-                    if (cta <= sg.last_cta) {
-                      const int slot = (cta == sg.first_cta) ? first_slot : 2 * cta;
-                      const float4* p = reinterpret_cast<const float4*>(a.sk_ws + (size_t)slot * (BM * BN)) + f;
-                      t[u][0] = ld_cg_f4(p + (cg * 2 + 0) * BM);
-                      t[u][1] = ld_cg_f4(p + (cg * 2 + 1) * BM);
-                    } else {
-                      t[u][0] = t[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
+                  for (int j = 0; j < 8; ++j) v[u][j] = 0.f;
+                // contributors are summed in CTA order (deterministic)
+                for (int cta = sg.first_cta; cta <= sg.last_cta; ++cta) {
+                  const int slot = (cta == sg.first_cta) ? first_slot : 2 * cta;
+                  const float4* p = reinterpret_cast<const float4*>(a.sk_ws + (size_t)slot * (BM * BN)) + f;
+                  float4 t[CH][2];
+#pragma unroll
+                  for (int u = 0; u < CH; ++u) {
+                    t[u][0] = ld_cg_f4(p + ((cg0 + u) * 2 + 0) * BM);
+                    t[u][1] = ld_cg_f4(p + ((cg0 + u) * 2 + 1) * BM);
                   }
 #pragma unroll
-                  for (int u = 0; u < 4; ++u) {
-                    v[0] += t[u][0].x; v[1] += t[u][0].y; v[2] += t[u][0].z; v[3] += t[u][0].w;
-                    v[4] += t[u][1].x; v[5] += t[u][1].y; v[6] += t[u][1].z; v[7] += t[u][1].w;
+                  for (int u = 0; u < CH; ++u) {
+                    v[u][0] += t[u][0].x; v[u][1] += t[u][0].y; v[u][2] += t[u][0].z; v[u][3] += t[u][0].w;
+                    v[u][4] += t[u][1].x; v[u][5] += t[u][1].y; v[u][6] += t[u][1].z; v[u][7] += t[u][1].w;
                   }
                 }
               }
               if (a.ar) {
-                // round to T, one 16-byte vector per thread per group, tile-blocked + coalesced
-                const uint4 vec = lam_sanitize<2>(pack8<T>(v));
-                if (a.ar == 2) {
-                  *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, owner, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
-                } else {
+#pragma unroll
+                for (int u = 0; u < CH; ++u) {
+                  const size_t xoff = ((size_t)xtile * NG + cg0 + u) * (BM * 16) + (size_t)f * 16;  // exchange-buffer offset
+                  // round to T, one 16-byte vector per thread per group, tile-blocked + coalesced
+                  const uint4 vec = lam_sanitize<2>(pack8<T>(v[u]));
+                  if (a.ar == 2) {
+                    *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, owner, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                  } else {
 #pragma unroll 1
-                  for (int p = 0; p < a.ws.nranks; ++p) {
-                    const int peer = (a.ws.rank + p) % a.ws.nranks;
-                    *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                    for (int p = 0; p < a.ws.nranks; ++p) {
+                      const int peer = (a.ws.rank + p) % a.ws.nranks;
+                      *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+                    }
                   }
                 }
                 continue;
@@ -544,17 +582,20 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             } else {
               uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = 0.f;
-              for (int r = 0; r < a.ws.nranks; ++r) {  // rank order: bit-identical on every rank
-                float t8[8];
-                // self-validating vector: wait for it, re-arm the slot (no flags, no fences)
-                unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)r * ar_slot_bytes + xoff), 31), t8);
+              for (int u = 0; u < CH; ++u) {
+                const size_t xoff = ((size_t)xtile * NG + cg0 + u) * (BM * 16) + (size_t)f * 16;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] += t8[j];
+                for (int j = 0; j < 8; ++j) v[u][j] = 0.f;
+                for (int r = 0; r < a.ws.nranks; ++r) {  // rank order: bit-identical on every rank
+                  float t8[8];
+                  // self-validating vector: wait for it, re-arm the slot (no flags, no fences)
+                  unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)r * ar_slot_bytes + xoff), 31), t8);
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) v[u][j] += t8[j];
+                }
               }
             }
-            if (a.ar == 2) epilogue_store8<T>(a, v, n, m0 - a.ws.rank * a.rs_rows + cg * 8, lane, bval, a.rs_rows);
-            else epilogue_store8<T>(a, v, n, m0 + cg * 8, lane, bval, a.M);
+            store_chunk<T, CH>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
           }
         }
         if (full_tile && n_pass == 1) {
@@ -717,19 +758,20 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const int cg = item / BM, f = item % BM;
         const int n = tn * BM + f;
         const size_t xoff = ((size_t)tile * NG + cg) * (BM * 16) + (size_t)f * 16;
-        float v[8];
+        float v[1][8], rv[1][8];
+        if (pass == n_pass - 1) epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the reduction
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = 0.f;
+        for (int j = 0; j < 8; ++j) v[0][j] = 0.f;
         if (pass == 0) {
           const uint32_t off = (uint32_t)(((cg * 2) * BM + f) * 16);
           for (int q = 0; q < S; ++q) {  // CTA order: deterministic
             const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
             const float4 lo = ld_dsmem_f4(base), hi = ld_dsmem_f4(base + BM * 16);
-            v[0] += lo.x; v[1] += lo.y; v[2] += lo.z; v[3] += lo.w;
-            v[4] += hi.x; v[5] += hi.y; v[6] += hi.z; v[7] += hi.w;
+            v[0][0] += lo.x; v[0][1] += lo.y; v[0][2] += lo.z; v[0][3] += lo.w;
+            v[0][4] += hi.x; v[0][5] += hi.y; v[0][6] += hi.z; v[0][7] += hi.w;
           }
           if (a.ar) {
-            const uint4 vec = lam_sanitize<2>(pack8<T>(v));
+            const uint4 vec = lam_sanitize<2>(pack8<T>(v[0]));
 #pragma unroll 1
             for (int p = 0; p < a.ws.nranks; ++p) {
               const int peer = (a.ws.rank + p) % a.ws.nranks;
@@ -743,11 +785,11 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
             float t8[8];
             unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)q * ar_slot_bytes + xoff), 43), t8);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] += t8[j];
+            for (int j = 0; j < 8; ++j) v[0][j] += t8[j];
           }
         }
         const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-        epilogue_store8<T>(a, v, n, tm * BN + cg * 8, lane, bval, a.M);
+        store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
       }
     }
   }
@@ -1021,7 +1063,8 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
     if (grid > sms) grid = sms;
     p.grid = (int)grid;
   }
-  const bool aligned = p.split == 0 && p.tiles >= 4 * p.grid;    // many tiles per CTA: plain data-parallel
+  static const int aligned_min = getenv("LLMSS_GEMM_ALIGNED_MIN") ? atoi(getenv("LLMSS_GEMM_ALIGNED_MIN")) : 4;
+  const bool aligned = p.split == 0 && p.tiles >= aligned_min * p.grid;    // many tiles per CTA: plain data-parallel
   const bool need_sk = p.split == 0 && !aligned && (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
   LLMSS_REQUIRE(!need_sk || (sk_ws != nullptr && sk_counters != nullptr), "gemm: stream-K workspace required for this shape");
   if (ar) {

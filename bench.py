@@ -57,14 +57,57 @@ def parse():
 
 # ----------------------------------------------------------------------------- clocks sampler
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed region.
+
+    Primary source is NVML (the library behind nvidia-smi) polled every 2 ms from a thread, so that even a
+    ~100 ms timed region (TP=8) gets dozens of samples; `nvidia-smi -lms 100` runs alongside as the
+    recipe's reference reading and is used alone if NVML cannot be loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NVML_REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
     def __init__(self, gpu_index: int):
         self.idx, self.rows, self.proc = gpu_index, [], None
+        self.nv_sm, self.nv_reasons, self.nv_max, self.nv_power = [], set(), None, []
+        self._stop = threading.Event()
+        self.nv_thread = None
+
+    def _nvml_handle(self):
+        import pynvml
+
+        pynvml.nvmlInit()
+        try:
+            import torch
+
+            pr = torch.cuda.get_device_properties(self.idx)
+            bus = "%08X:%02X:%02X.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            return pynvml, pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+
+    def _poll(self, nv, h):
+        while not self._stop.is_set():
+            try:
+                self.nv_sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                mask = int(get(h))
+                for bit, name in self.NVML_REASONS.items():
+                    if mask & bit:
+                        self.nv_reasons.add(name)
+                self.nv_power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def start(self):
+        try:
+            nv, h = self._nvml_handle()
+            self.nv_max = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.nv_thread = threading.Thread(target=self._poll, args=(nv, h), daemon=True)
+            self.nv_thread.start()
+        except Exception:
+            self.nv_thread = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
@@ -78,20 +121,31 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
+        self._stop.set()
+        if self.nv_thread is not None:
+            self.nv_thread.join(timeout=1.0)
+        if self.proc is None and not self.nv_sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        if self.proc is not None:
+            if not self.nv_sm:
+                time.sleep(0.15)
+            self.proc.terminate()
         sm = [float(r[1]) for r in self.rows if len(r) > 2 and r[1].replace(".", "").isdigit()]
         mx = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
-        reasons = set()
+        reasons = set(self.nv_reasons)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             for n, v in zip(names, r[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        allsm = self.nv_sm + sm
+        if self.nv_max:
+            mx.append(self.nv_max)
+        out = {"sm_mhz": statistics.median(allsm) if allsm else None, "sm_max_mhz": max(mx) if mx else None,
+               "reasons": sorted(reasons), "samples": len(allsm), "nvidia_smi_samples": len(sm)}
+        if self.nv_power:
+            out["power_w"] = round(statistics.median(self.nv_power), 1)
+        return out
 
 
 # ----------------------------------------------------------------------------- helpers

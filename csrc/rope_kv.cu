@@ -11,6 +11,9 @@
 
 namespace {
 
+// grid = (tokens, ceil(items / 128)): one 16-byte vector of [q | k | v] per thread, so a decode step
+// (64 tokens) still spreads over hundreds of CTAs and pays one memory round trip instead of a
+// latency-bound loop.  q vectors outside the rotary range are untouched and not even read.
 template <typename T>
 __global__ void __launch_bounds__(128) rope_kv_write_kernel(
     T* __restrict__ qkv, const int* __restrict__ positions, const int* __restrict__ slot_mapping,
@@ -20,16 +23,18 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
   pdl_wait();
   __shared__ float s_cos[128], s_sin[128];  // rotary_dim / 2 <= 128 frequencies
   const int t = blockIdx.x;
-  const float pos = (float)positions[t];
   const int slot = slot_mapping[t];
   T* row = qkv + (int64_t)t * ld;
   const int vec_per_head = d >> 3;
   const int nq = hq * vec_per_head, nk = hkv * vec_per_head;
   const int half = rotary_dim >> 1;
-  const float inv_rd = 1.0f / (float)(rotary_dim > 0 ? rotary_dim : 1);
+  const int it0 = blockIdx.y * 128;
+  const int it = it0 + threadIdx.x;
 
-  // cos/sin depend on (token, frequency) only: evaluate them once and share them across heads
-  if (style != LLMSS_ROPE_NONE) {
+  // cos/sin depend on (token, frequency) only: evaluated once per CTA that holds q / k vectors
+  if (style != LLMSS_ROPE_NONE && it0 < nq + nk) {
+    const float pos = (float)positions[t];
+    const float inv_rd = 1.0f / (float)(rotary_dim > 0 ? rotary_dim : 1);
     for (int i = threadIdx.x; i < half; i += blockDim.x) {
       const float inv_freq = exp2f(-2.0f * (float)i * inv_rd * log2_base);
       sincosf(pos * inv_freq, &s_sin[i], &s_cos[i]);
@@ -39,66 +44,59 @@ __global__ void __launch_bounds__(128) rope_kv_write_kernel(
   int64_t cache_base = 0;
   if (slot >= 0) cache_base = ((int64_t)(slot / block_size) * hkv) * block_size * d + (int64_t)(slot % block_size) * d;
 
-  // q and k heads: items [0, nq) are q vectors, [nq, nq+nk) are k vectors
-  for (int it = threadIdx.x; it < nq + nk; it += blockDim.x) {
-    const bool is_k = it >= nq;
-    const int j = is_k ? it - nq : it;
-    const int h = j / vec_per_head, c = (j % vec_per_head) << 3;  // column within head
-    T* p = row + (is_k ? k_off : q_off) + h * d + c;
-    float f[8];
-    bool modified = false;
-    bool skip_store_here = false;
-    if (style == LLMSS_ROPE_GPTJ && c < rotary_dim) {
-      unpack8<T>(*reinterpret_cast<const uint4*>(p), f);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int pair = (c >> 1) + i;  // frequency index
-        const float sn = s_sin[pair], cs = s_cos[pair];
-        float x1 = f[2 * i], x2 = f[2 * i + 1];
-        f[2 * i] = x1 * cs - x2 * sn;
-        f[2 * i + 1] = x2 * cs + x1 * sn;
-      }
-      modified = true;
-    } else if (style == LLMSS_ROPE_NEOX && c < rotary_dim) {
-      if (c < half) {
-        float g[8];
-        unpack8<T>(*reinterpret_cast<const uint4*>(p), f);
-        unpack8<T>(*reinterpret_cast<const uint4*>(p + half), g);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float sn = s_sin[c + i], cs = s_cos[c + i];
-          float x1 = f[i], x2 = g[i];
-          f[i] = x1 * cs - x2 * sn;
-          g[i] = x2 * cs + x1 * sn;
-        }
-        uint4 pg = pack8<T>(g);
-        *reinterpret_cast<uint4*>(p + half) = pg;
-        if (is_k && slot >= 0)
-          *reinterpret_cast<uint4*>(k_cache + cache_base + (int64_t)h * block_size * d + c + half) = pg;
-        modified = true;
-      } else {
-        skip_store_here = true;  // written by the thread that owns the first-half partner
-      }
-    } else {
-      if (is_k) unpack8<T>(*reinterpret_cast<const uint4*>(p), f);
-    }
-    if (skip_store_here) continue;
-    if (modified) {
-      uint4 pf = pack8<T>(f);
-      *reinterpret_cast<uint4*>(p) = pf;
-      if (is_k && slot >= 0) *reinterpret_cast<uint4*>(k_cache + cache_base + (int64_t)h * block_size * d + c) = pf;
-    } else if (is_k && slot >= 0) {
-      *reinterpret_cast<uint4*>(k_cache + cache_base + (int64_t)h * block_size * d + c) =
-          *reinterpret_cast<const uint4*>(p);
-    }
-  }
-  // v heads: straight copy into the cache
-  if (slot >= 0) {
-    for (int j = threadIdx.x; j < nk; j += blockDim.x) {
+  if (it >= nq + nk) {
+    // v heads: straight copy into the cache
+    const int j = it - nq - nk;
+    if (j < nk && slot >= 0) {
       const int h = j / vec_per_head, c = (j % vec_per_head) << 3;
       *reinterpret_cast<uint4*>(v_cache + cache_base + (int64_t)h * block_size * d + c) =
           *reinterpret_cast<const uint4*>(row + v_off + h * d + c);
     }
+    return;
+  }
+  // q and k heads: items [0, nq) are q vectors, [nq, nq+nk) are k vectors
+  const bool is_k = it >= nq;
+  const int j = is_k ? it - nq : it;
+  const int h = j / vec_per_head, c = (j % vec_per_head) << 3;  // column within head
+  T* p = row + (is_k ? k_off : q_off) + h * d + c;
+  T* kc = k_cache + cache_base + (int64_t)h * block_size * d + c;
+  const bool to_cache = is_k && slot >= 0;
+  float f[8];
+  if (style == LLMSS_ROPE_GPTJ && c < rotary_dim) {
+    unpack8<T>(*reinterpret_cast<const uint4*>(p), f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int pair = (c >> 1) + i;  // frequency index
+      const float sn = s_sin[pair], cs = s_cos[pair];
+      const float x1 = f[2 * i], x2 = f[2 * i + 1];
+      f[2 * i] = x1 * cs - x2 * sn;
+      f[2 * i + 1] = x2 * cs + x1 * sn;
+    }
+    const uint4 pf = pack8<T>(f);
+    *reinterpret_cast<uint4*>(p) = pf;
+    if (to_cache) *reinterpret_cast<uint4*>(kc) = pf;
+  } else if (style == LLMSS_ROPE_NEOX && c < rotary_dim) {
+    if (c < half) {  // this thread also owns the second-half partner vector
+      float g[8];
+      unpack8<T>(*reinterpret_cast<const uint4*>(p), f);
+      unpack8<T>(*reinterpret_cast<const uint4*>(p + half), g);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float sn = s_sin[c + i], cs = s_cos[c + i];
+        const float x1 = f[i], x2 = g[i];
+        f[i] = x1 * cs - x2 * sn;
+        g[i] = x2 * cs + x1 * sn;
+      }
+      const uint4 pf = pack8<T>(f), pg = pack8<T>(g);
+      *reinterpret_cast<uint4*>(p) = pf;
+      *reinterpret_cast<uint4*>(p + half) = pg;
+      if (to_cache) {
+        *reinterpret_cast<uint4*>(kc) = pf;
+        *reinterpret_cast<uint4*>(kc + half) = pg;
+      }
+    }
+  } else if (to_cache) {
+    *reinterpret_cast<uint4*>(kc) = *reinterpret_cast<const uint4*>(p);
   }
 }
 
@@ -115,10 +113,11 @@ LLMSS_API int llmss_rope_kv_write(void* qkv, const int* positions, const int* sl
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "rope_kv_write: dtype must be f16/bf16");
   if (T == 0) return 0;
   const float log2_base = log2f(base);
+  const int chunks = ((hq + 2 * hkv) * (d / 8) + 127) / 128;
   if (dtype == LLMSS_F16)
-    LLMSS_CHECK_CUDA(launch_pdl(rope_kv_write_kernel<__half>, dim3(T), dim3(128), 0, stream, (__half*)qkv, positions, slot_mapping, (__half*)k_cache, (__half*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base, q_off, k_off, v_off, block_size));
+    LLMSS_CHECK_CUDA(launch_pdl(rope_kv_write_kernel<__half>, dim3(T, chunks), dim3(128), 0, stream, (__half*)qkv, positions, slot_mapping, (__half*)k_cache, (__half*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base, q_off, k_off, v_off, block_size));
   else
-    LLMSS_CHECK_CUDA(launch_pdl(rope_kv_write_kernel<__nv_bfloat16>, dim3(T), dim3(128), 0, stream, (__nv_bfloat16*)qkv, positions, slot_mapping, (__nv_bfloat16*)k_cache, (__nv_bfloat16*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base, q_off, k_off, v_off, block_size));
+    LLMSS_CHECK_CUDA(launch_pdl(rope_kv_write_kernel<__nv_bfloat16>, dim3(T, chunks), dim3(128), 0, stream, (__nv_bfloat16*)qkv, positions, slot_mapping, (__nv_bfloat16*)k_cache, (__nv_bfloat16*)v_cache, ld, hq, hkv, d, rotary_dim, style, log2_base, q_off, k_off, v_off, block_size));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -45,13 +45,28 @@ struct DArgs {
   int num_splits;
   int n_items;
   int stages;
+  int B;
+  int balanced;   // 1: flat partition of all key tiles over the grid (ignores num_splits)
+  int max_parts;  // balanced: partial slots per (sequence, q head)
   float scale_log2;
   int dtype;
 };
 
 struct Item {
   int b, kvh, split, L, t_begin, t_end, n_tiles;
+  int direct;   // this unit covers the whole sequence: write the normalised output, no partial
+  int part;     // partial slot within the (sequence, head) row
+  int pstride;  // slots per (sequence, head)
 };
+
+constexpr int kMinQuota = 4;  // balanced mode: no CTA gets fewer key tiles than this (bounds the parts per item)
+
+__device__ __forceinline__ int balanced_quota(int total_tiles, int grid) {
+  int active = (total_tiles + kMinQuota - 1) / kMinQuota;
+  active = active < grid ? active : grid;
+  active = active > 1 ? active : 1;
+  return (total_tiles + active - 1) / active > 1 ? (total_tiles + active - 1) / active : 1;
+}
 
 __device__ __forceinline__ Item decode_item(const DArgs& a, int it) {
   Item r;
@@ -65,8 +80,75 @@ __device__ __forceinline__ Item decode_item(const DArgs& a, int it) {
   r.t_begin = r.split * chunk;
   r.t_end = min(r.L, r.t_begin + chunk);
   r.n_tiles = r.t_end > r.t_begin ? (r.t_end - r.t_begin + BN - 1) / BN : 0;
+  r.direct = a.num_splits == 1;
+  r.part = r.split;
+  r.pstride = a.num_splits;
   return r;
 }
+
+// Work-unit iterator shared by all warp roles (every role walks the same deterministic sequence).
+//  * split mode: units are (sequence, kv head, split) items, round-robin over the CTAs.
+//  * balanced mode: all key tiles of the batch, ordered (sequence, kv head, tile), are cut into equal
+//    contiguous ranges, one per CTA ("stream-K" for attention): a CTA's range may start and end in the
+//    middle of an item, those pieces are written as partials and merged by the combine kernel.  Removes
+//    the wave quantisation of items / SMs (e.g. 128 items on 148 SMs at TP=8).
+struct Sched {
+  const DArgs& a;
+  int it;                             // split mode cursor
+  int t, t_stop, b, kvh, j, quota;    // balanced mode cursor: flat tile index, (sequence, kv head, tile)
+  __device__ __forceinline__ int ntiles(int i) const { return (a.seq_lens[i] + BN - 1) / BN; }
+  __device__ Sched(const DArgs& a_) : a(a_), it(blockIdx.x), t(0), t_stop(0), b(0), kvh(0), j(0), quota(1) {
+    if (!a.balanced) return;
+    int total = 0;
+    for (int i = 0; i < a.B; ++i) total += ntiles(i);
+    total *= a.hkv;
+    quota = balanced_quota(total, gridDim.x);
+    const long long t0 = (long long)blockIdx.x * quota;
+    t = t0 < total ? (int)t0 : total;
+    t_stop = t + quota < total ? t + quota : total;
+    int rem = t;
+    while (b < a.B) {
+      const int span = ntiles(b) * a.hkv;
+      if (rem < span) break;
+      rem -= span;
+      ++b;
+    }
+    if (b < a.B) {
+      const int n = ntiles(b);
+      kvh = rem / n;
+      j = rem % n;
+    }
+  }
+  __device__ bool next(Item& r) {
+    if (!a.balanced) {
+      if (it >= a.n_items) return false;
+      r = decode_item(a, it);
+      it += gridDim.x;
+      return true;
+    }
+    if (t >= t_stop) return false;
+    int n = ntiles(b);
+    while (n == 0) n = ntiles(++b);  // t < total: a non-empty sequence follows
+    const int take = (n - j) < (t_stop - t) ? (n - j) : (t_stop - t);
+    r.b = b;
+    r.kvh = kvh;
+    r.split = 0;
+    r.L = a.seq_lens[b];
+    r.t_begin = j * BN;
+    r.t_end = r.L < (j + take) * BN ? r.L : (j + take) * BN;
+    r.n_tiles = take;
+    r.direct = take == n;
+    r.part = (int)blockIdx.x - (t - j) / quota;  // CTAs that share this item are consecutive
+    r.pstride = a.max_parts;
+    t += take;
+    j += take;
+    if (j == n) {
+      j = 0;
+      if (++kvh == a.hkv) { kvh = 0; ++b; }
+    }
+    return true;
+  }
+};
 
 // MN-major (N contiguous) 128B-swizzled operand: rows are K (keys), 64 elements of N per 128-byte row;
 // LBO = distance between 64-element N chunks, SBO = distance between 8-row K groups.
@@ -216,8 +298,9 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
     const int pages = BN / a.block_size;
     int stage = 0, n = 0;
     uint32_t phase = 0;
-    for (int it = blockIdx.x; it < a.n_items; it += gridDim.x) {
-      const Item I = decode_item(a, it);
+    Sched sch(a);
+    Item I;
+    while (sch.next(I)) {
       if (I.n_tiles == 0) continue;
       const int qb = n & 1;
       mbar_wait(&bar_qempty[qb], ((n >> 1) & 1) ^ 1, 40);
@@ -280,8 +363,9 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
     const uint32_t page_bytes = bs * D * 2, chunk_bytes = bs * 128;
     int kst = 0, n = 0;
     uint32_t kph = 0, g = 0;
-    for (int it = blockIdx.x; it < a.n_items; it += gridDim.x) {
-      const Item I = decode_item(a, it);
+    Sched sch(a);
+    Item I;
+    while (sch.next(I)) {
       if (I.n_tiles == 0) continue;
       const int qb = n & 1;
       const uint32_t q_addr = q_base + qb * q_bytes;
@@ -318,8 +402,9 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
     const uint32_t page_bytes = bs * D * 2, chunk_bytes = bs * 128;
     int vst = 0;
     uint32_t vph = 0, g = 0;
-    for (int it = blockIdx.x; it < a.n_items; it += gridDim.x) {
-      const Item I = decode_item(a, it);
+    Sched sch(a);
+    Item I;
+    while (sch.next(I)) {
       for (int j = 0; j < I.n_tiles; ++j, ++g) {
         mbar_wait(&bar_p[g & 1], (g >> 1) & 1, 62);
         mbar_wait(&bar_vfull[vst], vph, 63);
@@ -352,13 +437,14 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
     const int n_threads = n_live_warps * 32;
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     uint32_t g = 0;
-    for (int it = blockIdx.x; it < a.n_items; it += gridDim.x) {
-      const Item I = decode_item(a, it);
+    Sched sch(a);
+    Item I;
+    while (sch.next(I)) {
       const int head = I.kvh * G + row;
-      const int64_t pidx = ((int64_t)I.b * a.hq + head) * a.num_splits + I.split;
+      const int64_t pidx = ((int64_t)I.b * a.hq + head) * I.pstride + I.part;
       if (I.n_tiles == 0) {  // empty split (or empty sequence): neutral partial / zero output
         if (live && owner) {
-          if (a.num_splits == 1) {
+          if (I.direct) {
             T* orow = reinterpret_cast<T*>(a.out) + (int64_t)I.b * a.ldo + (int64_t)head * D;
             for (int c = 0; c < D; c += 8) *reinterpret_cast<uint4*>(orow + c) = make_uint4(0, 0, 0, 0);
           } else {
@@ -474,7 +560,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
         tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
         tmem_ld_wait();
         if (!live) continue;
-        if (a.num_splits == 1) {
+        if (I.direct) {
           T* orow = reinterpret_cast<T*>(a.out) + (int64_t)I.b * a.ldo + (int64_t)head * D;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -491,7 +577,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
                                  __uint_as_float(r[4 * q + 3]));
         }
       }
-      if (live && a.num_splits > 1) {
+      if (live && !I.direct) {
         a.part_ml[pidx * 2] = m_run;
         a.part_ml[pidx * 2 + 1] = l_run;
       }
@@ -504,6 +590,49 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
   if (warp == 1) {
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// Balanced mode: merge the pieces of the items that were cut at a CTA boundary (and zero the rows of empty
+// sequences).  Recomputes the same partition as Sched from seq_lens.
+template <typename T, int D>
+__global__ void attn_decode_tc_balanced_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
+                                                       T* __restrict__ out, int64_t ldo, const int* __restrict__ seq_lens,
+                                                       int B, int hq, int hkv, int max_parts, int grid_main) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int head = blockIdx.x, b = blockIdx.y;
+  const int kvh = head / (hq / hkv);
+  int total = 0, pre = 0;
+  for (int i = 0; i < B; ++i) {
+    const int n = (seq_lens[i] + BN - 1) / BN;
+    if (i < b) pre += n;
+    total += n;
+  }
+  total *= hkv;
+  const int n = (seq_lens[b] + BN - 1) / BN;
+  T* orow = out + (int64_t)b * ldo + (int64_t)head * D;
+  if (n == 0) {
+    for (int c = threadIdx.x; c < D; c += blockDim.x) orow[c] = from_f32<T>(0.f);
+    return;
+  }
+  const int quota = balanced_quota(total, grid_main);
+  const int start = pre * hkv + kvh * n;
+  const int first = start / quota, last = (start + n - 1) / quota;
+  const int parts = last - first + 1;
+  if (parts == 1) return;  // written directly by the attention kernel
+  const int64_t base = ((int64_t)b * hq + head) * max_parts;
+  float mn = -INFINITY;
+  for (int s = 0; s < parts; ++s) mn = fmaxf(mn, part_ml[(base + s) * 2]);
+  for (int c = threadIdx.x; c < D; c += blockDim.x) {
+    float lt = 0.f, at = 0.f;
+    for (int s = 0; s < parts; ++s) {
+      const float ms = part_ml[(base + s) * 2];
+      const float sc = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
+      lt += part_ml[(base + s) * 2 + 1] * sc;
+      at += part_o[(base + s) * D + c] * sc;
+    }
+    orow[c] = from_f32<T>(lt > 0.f ? at / lt : 0.f);
   }
 }
 
@@ -520,6 +649,12 @@ PFN_encodeTiledD get_encode_d() {
       fn = (PFN_encodeTiledD)p;
   }
   return fn;
+}
+
+// Upper bound of the pieces one (sequence, head) item can be cut into in balanced mode.
+int balanced_max_parts(int max_blocks, int block_size) {
+  const int max_tiles = (max_blocks * block_size + BN - 1) / BN;
+  return (max_tiles + kMinQuota - 2) / kMinQuota + 1;
 }
 
 int sm_count() {
@@ -553,12 +688,17 @@ int launch_decode_tc(const CUtensorMap& tq, const CUtensorMap& tk, const CUtenso
     LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = smem;
   }
-  const int grid = a.n_items < sm_count() ? a.n_items : sm_count();
+  const int grid = (a.balanced || a.n_items >= sm_count()) ? sm_count() : a.n_items;
   LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, tq, tk, tv, a));
   return 0;
 }
 
 }  // namespace
+
+// Scratch (floats) of the balanced mode (num_splits = 0).
+LLMSS_API int64_t llmss_attn_decode_tc_balanced_scratch_floats(int B, int hq, int d, int max_blocks, int block_size) {
+  return (int64_t)B * hq * balanced_max_parts(max_blocks, block_size) * (d + 2);
+}
 
 extern "C" int llmss_attn_decode_combine(const float* part_o, const float* part_ml, void* out, int64_t ldo, int B, int hq,
                                          int d, int num_splits, int dtype, cudaStream_t stream);
@@ -596,7 +736,9 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
   LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_decode_tc: head_dim=%d unsupported", d);
   LLMSS_REQUIRE(hq % hkv == 0 && hq / hkv <= 128, "attn_decode_tc: bad head grouping hq=%d hkv=%d", hq, hkv);
   LLMSS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64, "attn_decode_tc: block_size must be 16/32/64");
-  LLMSS_REQUIRE(num_splits >= 1 && (num_splits == 1 || scratch != nullptr), "attn_decode_tc: scratch required for splits");
+  LLMSS_REQUIRE(num_splits >= 0 && (num_splits == 1 || scratch != nullptr), "attn_decode_tc: scratch required for splits");
+  const int balanced = num_splits == 0 ? 1 : 0;  // flat partition of all key tiles over the SMs
+  const int max_parts = balanced_max_parts(max_blocks, block_size);
   LLMSS_REQUIRE(ldq % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)q % 16) == 0, "attn_decode_tc: q must be 16-byte aligned");
   if (B == 0) return 0;
   PFN_encodeTiledD enc = get_encode_d();
@@ -644,7 +786,10 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
   a.out = out;
   a.ldo = ldo;
   a.part_o = scratch;
-  a.part_ml = scratch ? scratch + (int64_t)B * hq * num_splits * d : nullptr;
+  a.part_ml = scratch ? scratch + (int64_t)B * hq * (balanced ? max_parts : num_splits) * d : nullptr;
+  a.B = B;
+  a.balanced = balanced;
+  a.max_parts = max_parts;
   a.hq = hq;
   a.hkv = hkv;
   a.G = G;
@@ -676,5 +821,20 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
   }
 #undef LLMSS_DT
   if (rc != 0 || num_splits == 1) return rc;
+  if (balanced) {
+    const dim3 cgrid(hq, B);
+    const int threads = d < 128 ? d : 128;
+#define LLMSS_BC(T_, D_)                                                                                             \
+  LLMSS_CHECK_CUDA(launch_pdl(attn_decode_tc_balanced_combine_kernel<T_, D_>, cgrid, dim3(threads), 0, stream, \
+                              (const float*)a.part_o, (const float*)a.part_ml, (T_*)out, ldo, seq_lens, B, hq, hkv,  \
+                              max_parts, sm_count()))
+    if (dtype == LLMSS_F16) {
+      if (d == 64) LLMSS_BC(__half, 64); else if (d == 128) LLMSS_BC(__half, 128); else LLMSS_BC(__half, 256);
+    } else {
+      if (d == 64) LLMSS_BC(__nv_bfloat16, 64); else if (d == 128) LLMSS_BC(__nv_bfloat16, 128); else LLMSS_BC(__nv_bfloat16, 256);
+    }
+#undef LLMSS_BC
+    return 0;
+  }
   return llmss_attn_decode_combine(a.part_o, a.part_ml, out, ldo, B, hq, d, num_splits, dtype, stream);
 }

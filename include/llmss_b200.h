@@ -87,6 +87,9 @@ int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cache, const 
                          int64_t ldo, float* scratch, int B, int hq, int hkv, int d, int block_size,
                          int num_blocks, float scale, int num_splits, int dtype, llmss_stream_t stream);
 int llmss_attn_decode_tc_pick_splits(int B, int hkv, int d, int max_kv);
+/* num_splits = 0 selects the balanced mode: all key tiles of the batch are cut into equal contiguous ranges,
+ * one per SM (no wave quantisation of items / SMs); its scratch is sized by the function below. */
+int64_t llmss_attn_decode_tc_balanced_scratch_floats(int B, int hq, int d, int max_blocks, int block_size);
 /* Merge split-KV partials (part_o [B,hq,splits,d], part_ml [B,hq,splits,2]) into out. */
 int llmss_attn_decode_combine(const float* part_o, const float* part_ml, void* out, int64_t ldo, int B,
                               int hq, int d, int num_splits, int dtype, llmss_stream_t stream);

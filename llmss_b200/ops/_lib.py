@@ -50,6 +50,7 @@ _SIGS = {
     "llmss_attn_decode_scratch_floats": (c_int64, [c_int, c_int, c_int, c_int]),
     "llmss_attn_decode_pick_splits": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "llmss_attn_decode_tc_pick_splits": (c_int, [c_int, c_int, c_int, c_int]),
+    "llmss_attn_decode_tc_balanced_scratch_floats": (c_int64, [c_int, c_int, c_int, c_int, c_int]),
     "llmss_attn_decode_tc": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                      c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_int,
                                      c_int, c_void_p]),

@@ -196,16 +196,22 @@ def attn_decode(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, hq, 
     B = q_view.shape[0]
     bs = k_cache.shape[2]
     scratch = None
+    tc = use_tc_decode(hq, hkv, d, bs)
+    if num_splits == 0 and not tc:
+        num_splits = 1  # balanced partition exists only in the tensor-core kernel
     if num_splits > 1:
         n = lib.llmss_attn_decode_scratch_floats(B, hq, d, num_splits)
         scratch = arena(q_view.device).attn_scratch(n, q_view.device)
-    if use_tc_decode(hq, hkv, d, bs):
+    elif num_splits == 0:
+        n = lib.llmss_attn_decode_tc_balanced_scratch_floats(B, hq, d, block_tables.shape[1], bs)
+        scratch = arena(q_view.device).attn_scratch(n, q_view.device)
+    if tc:
         rc = lib.llmss_attn_decode_tc(_ptr(q_view), q_view.stride(0), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables),
                                       block_tables.shape[1], _ptr(seq_lens), _ptr(out_view), out_view.stride(0),
                                       _ptr(scratch), B, hq, hkv, d, bs, k_cache.shape[0], float(scale), num_splits,
                                       _DT[q_view.dtype], _stream())
         _lib.check(rc, "llmss_attn_decode_tc")
-        _count(2 if num_splits > 1 else 1)
+        _count(1 if num_splits == 1 else 2)
         return
     rc = lib.llmss_attn_decode(_ptr(q_view), q_view.stride(0), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables),
                                block_tables.shape[1], _ptr(seq_lens), _ptr(out_view), out_view.stride(0),

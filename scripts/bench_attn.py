@@ -23,7 +23,7 @@ def bench(B, hq, hkv, d, ctx, splits=None, dtype=torch.bfloat16, reps=6, bs=16):
     sl = torch.full((B,), ctx, dtype=torch.int32, device="cuda")
     q = torch.randn(B, hq * d, device="cuda", dtype=dtype)
     out = torch.empty_like(q)
-    sp = splits or cu.decode_splits(B, hq, hkv, d, ctx, dtype, bs)
+    sp = cu.decode_splits(B, hq, hkv, d, ctx, dtype, bs) if splits is None else splits
     fn = lambda: cu.attn_decode(q, kc, vc, bt, sl, out, hq, hkv, d, d ** -0.5, sp)  # noqa: E731
     for _ in range(3):
         fn()
@@ -73,3 +73,8 @@ if __name__ == "__main__":
         for bs in (16, 64):
             bench(64, 16, 16, 256, 1040, bs=bs)
             bench(64, 32, 32, 128, 1040, bs=bs)
+    print("balanced (splits=0) vs picked, 64-token pages, TP=1/2/4/8 head counts of GPT-J and a GQA model")
+    for hq_, hkv_, d_, ctx_ in ((16, 16, 256, 1040), (8, 8, 256, 1040), (4, 4, 256, 1040), (2, 2, 256, 1040), (32, 8, 128, 4096),
+                                (4, 1, 128, 4096)):
+        bench(64, hq_, hkv_, d_, ctx_, bs=64)
+        bench(64, hq_, hkv_, d_, ctx_, 0, bs=64)

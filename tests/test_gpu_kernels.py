@@ -145,7 +145,7 @@ def test_rope_kv_write(style, d, rd):
 @pytest.mark.parametrize("dtype", DT)
 @pytest.mark.parametrize("hq,hkv,d", [(4, 4, 256), (8, 8, 128), (12, 12, 64), (8, 2, 128), (6, 1, 128), (16, 1, 64),
                                       (48, 1, 128), (32, 8, 128), (16, 4, 256), (6, 2, 64)])
-@pytest.mark.parametrize("splits", [1, 4])
+@pytest.mark.parametrize("splits", [0, 1, 4])  # 0 = balanced flat partition (tensor-core kernel only)
 def test_attn_decode(hq, hkv, d, splits, dtype):
     cu = _cu()
     torch.manual_seed(0)
@@ -189,7 +189,7 @@ def test_attn_decode_tc_matches_cuda_core_path(monkeypatch, bs):
     for min_group in (4, 1000):  # tensor-core path, then CUDA-core path
         monkeypatch.setattr(cu, "_TC_MIN_GROUP", min_group)
         assert cu.use_tc_decode(hq, hkv, d) == (min_group == 4)
-        for splits in (1, 3, 8):
+        for splits in (0, 1, 3, 8):
             o = torch.zeros_like(q)
             cu.attn_decode(q, kc, vc, bt, sl, o, hq, hkv, d, d ** -0.5, splits)
             outs.append(o.float())

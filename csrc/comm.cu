@@ -262,21 +262,36 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(SymmWs ws, 
 }
 
 // ---- all-gather: out[r] = rank r's input (used for the vocab-parallel logits, reference N3)
+// Input: [rows][vpr] 16-byte vectors (contiguous).  Output: [rows][nranks * vpr], rank r's block at column
+// r * vpr -- i.e. the concatenation along the last dimension, written in place (rows = 1 gives the plain
+// [nranks][n] gather).  Four vectors are in flight per thread in both phases.
 __global__ void __launch_bounds__(kThreads) allgather_kernel(SymmWs ws, const uint4* __restrict__ in,
-                                                             uint4* __restrict__ out, int64_t nvec) {
+                                                             uint4* __restrict__ out, int64_t nvec, int64_t vpr) {
   pdl_launch_dependents();
   pdl_wait();
   const uint32_t e = *ws.epoch + 1;
   const int par = e & 1;
   const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
   const int64_t v0 = (int64_t)blockIdx.x * per_cta, v1 = min(nvec, v0 + per_cta);
-  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
-    const uint4 val = in[v];
-    out[(int64_t)ws.rank * nvec + v] = val;
+  const int64_t pitch = vpr * ws.nranks;
+  constexpr int U = 4;
+  for (int64_t vb = v0 + threadIdx.x; vb < v1; vb += (int64_t)kThreads * U) {
+    uint4 val[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t v = vb + (int64_t)u * kThreads;
+      if (v < v1) val[u] = in[v];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t v = vb + (int64_t)u * kThreads;
+      if (v >= v1) continue;
+      out[(v / vpr) * pitch + (int64_t)ws.rank * vpr + v % vpr] = val[u];
 #pragma unroll 1
-    for (int p = 1; p < ws.nranks; ++p) {
-      const int peer = (ws.rank + p) % ws.nranks;
-      symm_buf<uint4>(ws, peer, par)[(int64_t)ws.rank * nvec + v] = val;
+      for (int p = 1; p < ws.nranks; ++p) {
+        const int peer = (ws.rank + p) % ws.nranks;
+        symm_buf<uint4>(ws, peer, par)[(int64_t)ws.rank * nvec + v] = val[u];
+      }
     }
   }
   __syncthreads();
@@ -288,11 +303,21 @@ __global__ void __launch_bounds__(kThreads) allgather_kernel(SymmWs ws, const ui
     wait_flag_ge(symm_flag(ws, ws.rank, 0, blockIdx.x) + threadIdx.x, e, 4);
   __syncthreads();
   const uint4* mine = symm_buf<uint4>(ws, ws.rank, par);
-  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
 #pragma unroll 1
-    for (int p = 1; p < ws.nranks; ++p) {
-      const int r = (ws.rank + p) % ws.nranks;
-      out[(int64_t)r * nvec + v] = ld_cg_v4(mine + (int64_t)r * nvec + v);
+  for (int p = 1; p < ws.nranks; ++p) {
+    const int r = (ws.rank + p) % ws.nranks;
+    for (int64_t vb = v0 + threadIdx.x; vb < v1; vb += (int64_t)kThreads * U) {
+      uint4 val[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t v = vb + (int64_t)u * kThreads;
+        if (v < v1) val[u] = ld_cg_v4(mine + (int64_t)r * nvec + v);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t v = vb + (int64_t)u * kThreads;
+        if (v < v1) out[(v / vpr) * pitch + (int64_t)r * vpr + v % vpr] = val[u];
+      }
     }
   }
   symm_finish(ws, e);
@@ -343,6 +368,27 @@ LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, 
   return 0;
 }
 
+// Gather along the last dimension: in is [rows][row_bytes], out is [rows][nranks * row_bytes] (rank r's block at
+// byte column r * row_bytes) -- torch.cat(all_gather(x), dim=-1) without the intermediate copy (vocab-parallel
+// logits).  rows = 1 is the plain gather: out holds nranks * bytes, slot r receives rank r's input.
+LLMSS_API int llmss_allgather_cols(SymmWs* ws, const void* in, void* out, int64_t rows, int64_t row_bytes,
+                                   cudaStream_t stream) {
+  const int64_t bytes = rows * row_bytes;
+  LLMSS_REQUIRE(row_bytes % 16 == 0, "allgather: row size %lld must be a multiple of 16 bytes", (long long)row_bytes);
+  LLMSS_REQUIRE(((uintptr_t)in % 16 == 0) && ((uintptr_t)out % 16 == 0), "allgather: pointers must be 16-byte aligned");
+  if (bytes == 0) return 0;
+  if (ws->nranks == 1) {
+    if (in != out) LLMSS_CHECK_CUDA(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice, stream));
+    return 0;
+  }
+  LLMSS_REQUIRE((size_t)(bytes * ws->nranks) <= ws->buf_bytes, "allgather: %lld bytes x %d ranks exceeds workspace %zu",
+                (long long)bytes, ws->nranks, ws->buf_bytes);
+  const int64_t nvec = bytes / 16;
+  LLMSS_CHECK_CUDA(launch_pdl(allgather_kernel, dim3(pick_grid((nvec + 3) / 4, 128)), dim3(kThreads), 0, stream, *ws,
+                              (const uint4*)in, (uint4*)out, nvec, row_bytes / 16));
+  return 0;
+}
+
 // out must hold nranks * bytes; slot r receives rank r's input.
 LLMSS_API int llmss_allgather(SymmWs* ws, const void* in, void* out, int64_t bytes, cudaStream_t stream) {
   LLMSS_REQUIRE(bytes % 16 == 0, "allgather: byte size %lld must be a multiple of 16", (long long)bytes);
@@ -354,8 +400,8 @@ LLMSS_API int llmss_allgather(SymmWs* ws, const void* in, void* out, int64_t byt
   LLMSS_REQUIRE((size_t)(bytes * ws->nranks) <= ws->buf_bytes, "allgather: %lld bytes x %d ranks exceeds workspace %zu",
                 (long long)bytes, ws->nranks, ws->buf_bytes);
   const int64_t nvec = bytes / 16;
-  LLMSS_CHECK_CUDA(launch_pdl(allgather_kernel, dim3(pick_grid(nvec, 128)), dim3(kThreads), 0, stream, *ws, (const uint4*)in,
-                              (uint4*)out, nvec));
+  LLMSS_CHECK_CUDA(launch_pdl(allgather_kernel, dim3(pick_grid((nvec + 3) / 4, 128)), dim3(kThreads), 0, stream, *ws,
+                              (const uint4*)in, (uint4*)out, nvec, nvec));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -42,6 +42,10 @@ int llmss_symm_epoch(llmss_symm_t* ws, uint32_t* out_host);
 int llmss_allreduce(llmss_symm_t* ws, const void* in, void* out, int64_t n, int dtype, int algo,
                     llmss_stream_t stream);
 int llmss_allgather(llmss_symm_t* ws, const void* in, void* out, int64_t bytes, llmss_stream_t stream);
+/* gather along the last dimension: in [rows][row_bytes] -> out [rows][nranks * row_bytes] (N3: the vocab-parallel
+ * logits all-gather + cat of layers.py:131-135 in one pass) */
+int llmss_allgather_cols(llmss_symm_t* ws, const void* in, void* out, int64_t rows, int64_t row_bytes,
+                         llmss_stream_t stream);
 
 /* ---- K5/K1/K2 tcgen05 GEMM (+ fused all-reduce epilogue) (G3,G4,G9,G10,G12,G14; layers.py:62,175-179) ---- */
 typedef struct llmss_gemm_plan {

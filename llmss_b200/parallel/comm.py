@@ -68,6 +68,8 @@ class Communicator:
         if self.fake:  # DEBUG=1 shard inspection: every slot is the local shard
             return torch.cat([x] * self.size, dim=dim)
         if self.symm is not None and x.is_cuda and self.symm.can_all_gather(x):
+            if x.dim() == 2 and dim in (-1, 1) and (x.shape[1] * x.element_size()) % 16 == 0:
+                return self.symm.all_gather_cols(x)  # concatenated in place, no torch.cat pass
             parts = self.symm.all_gather(x)  # [t, *x.shape]
             parts = list(parts.unbind(0))
         else:

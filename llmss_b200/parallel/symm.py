@@ -85,6 +85,17 @@ class SymmetricWorkspace:
         _lib.LAUNCHES["count"] += 1
         return out
 
+    def all_gather_cols(self, x: torch.Tensor) -> torch.Tensor:
+        """cat(all_gather(x), dim=-1) for a contiguous 2-D x, written in place by the gather kernel."""
+        lib = _lib.load()
+        rows, cols = x.shape
+        out = torch.empty(rows, cols * self.nranks, dtype=x.dtype, device=x.device)
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _lib.check(lib.llmss_allgather_cols(self.handle, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), rows,
+                                            cols * x.element_size(), s), "llmss_allgather_cols")
+        _lib.LAUNCHES["count"] += 1
+        return out
+
     def epoch(self) -> int:
         v = C.c_uint32()
         _lib.check(_lib.load().llmss_symm_epoch(self.handle, C.byref(v)), "symm_epoch")

@@ -74,7 +74,23 @@ def main():
         if not torch.all(g[r] == r):
             ok = False
             log("FAIL allgather slot", r)
-    log("allgather done")
+    # column gather (vocab-parallel logits): cat(all_gather(x), dim=-1) in one pass, odd row counts / sizes
+    for rows, cols in ((64, 6304), (5, 36), (1, 4), (33, 25216)):
+        xc = (torch.arange(rows * cols, device=dev, dtype=torch.float32).view(rows, cols) + 1e6 * rank)
+        gc = symm.all_gather_cols(xc)
+        torch.cuda.synchronize()
+        for r in range(world):
+            want = torch.arange(rows * cols, device=dev, dtype=torch.float32).view(rows, cols) + 1e6 * r
+            if not torch.equal(gc[:, r * cols:(r + 1) * cols], want):
+                ok = False
+                log("FAIL allgather_cols", rows, cols, "slot", r)
+    for _ in range(20):  # back-to-back calls: parity double buffering
+        gc = symm.all_gather_cols(xc)
+    torch.cuda.synchronize()
+    if not torch.equal(gc[:, rank * cols:(rank + 1) * cols], xc):
+        ok = False
+        log("FAIL allgather_cols repeat")
+    log("allgather done", "OK" if ok else "FAILED")
 
     # ---- 3. fused GEMM -> all-reduce
     for (M, N, K) in [(1, 512, 256), (16, 4096, 2560), (64, 4096, 2560), (64, 4096, 20480 // world), (40, 1000, 328), (256, 2048, 512)]:

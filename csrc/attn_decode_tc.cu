@@ -23,10 +23,11 @@
 namespace {
 
 constexpr int BM = 128;  // UMMA M (q-head rows; rows >= G are don't-care)
-constexpr int BN = 64;   // keys per tile
+// keys per tile: 64 (= one 64-token page) for head_dim 128 / 256, 128 for head_dim 64 so that a tile is
+// still 32 KB of K + V and the per-tile costs (barriers, MMA issue, softmax hand-off) stay amortised
+__host__ __device__ constexpr int tile_keys(int d) { return d == 64 ? 128 : 64; }
 constexpr int kThreads = 224;  // warp 0 TMA, warp 1 QK issue, warps 2-5 softmax, warp 6 PV issue
 constexpr int kMaxStages = 8;
-constexpr int P_BYTES = BM * BN * 2;
 
 struct DArgs {
   const int* block_tables;
@@ -46,6 +47,7 @@ struct DArgs {
   int n_items;
   int stages;
   int B;
+  int bn;         // keys per tile = tile_keys(head_dim)
   int balanced;   // 1: flat partition of all key tiles over the grid (ignores num_splits)
   int max_parts;  // balanced: partial slots per (sequence, q head)
   float scale_log2;
@@ -76,10 +78,10 @@ __device__ __forceinline__ Item decode_item(const DArgs& a, int it) {
   r.b = t / a.hkv;
   r.L = a.seq_lens[r.b];
   int chunk = (r.L + a.num_splits - 1) / a.num_splits;
-  chunk = (chunk + BN - 1) / BN * BN;  // whole key tiles per split
+  chunk = (chunk + a.bn - 1) / a.bn * a.bn;  // whole key tiles per split
   r.t_begin = r.split * chunk;
   r.t_end = min(r.L, r.t_begin + chunk);
-  r.n_tiles = r.t_end > r.t_begin ? (r.t_end - r.t_begin + BN - 1) / BN : 0;
+  r.n_tiles = r.t_end > r.t_begin ? (r.t_end - r.t_begin + a.bn - 1) / a.bn : 0;
   r.direct = a.num_splits == 1;
   r.part = r.split;
   r.pstride = a.num_splits;
@@ -96,7 +98,7 @@ struct Sched {
   const DArgs& a;
   int it;                             // split mode cursor
   int t, t_stop, b, kvh, j, quota;    // balanced mode cursor: flat tile index, (sequence, kv head, tile)
-  __device__ __forceinline__ int ntiles(int i) const { return (a.seq_lens[i] + BN - 1) / BN; }
+  __device__ __forceinline__ int ntiles(int i) const { return (a.seq_lens[i] + a.bn - 1) / a.bn; }
   __device__ Sched(const DArgs& a_) : a(a_), it(blockIdx.x), t(0), t_stop(0), b(0), kvh(0), j(0), quota(1) {
     if (!a.balanced) return;
     int total = 0;
@@ -134,8 +136,8 @@ struct Sched {
     r.kvh = kvh;
     r.split = 0;
     r.L = a.seq_lens[b];
-    r.t_begin = j * BN;
-    r.t_end = r.L < (j + take) * BN ? r.L : (j + take) * BN;
+    r.t_begin = j * a.bn;
+    r.t_end = r.L < (j + take) * a.bn ? r.L : (j + take) * a.bn;
     r.n_tiles = take;
     r.direct = take == n;
     r.part = (int)blockIdx.x - (t - j) / quota;  // CTAs that share this item are consecutive
@@ -227,6 +229,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                       const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ DArgs a) {
   constexpr int DSUB = D / 64;
+  constexpr int BN = tile_keys(D);
+  constexpr int P_BYTES = BM * BN * 2;
   constexpr int KV_BYTES = BN * D * 2;  // one K (or V) tile
   constexpr int TMEM_COLS = (2 * BN + D <= 256) ? 256 : 512;  // S0 at column 0, S1 at BN, O at 2*BN
   extern __shared__ uint8_t smem_raw[];
@@ -412,9 +416,9 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
         const uint32_t v_addr = v_base + vst * KV_BYTES;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {  // 16 keys per step; a step never straddles a page (block_size >= 16)
+          for (int k = 0; k < BN / 16; ++k) {  // 16 keys per step; a step never straddles a page (block_size >= 16)
             const int pg = (k * 16) / bs, ro = (k * 16) % bs;
-            umma_f16_ss(tO, umma_desc_k_sw128(p_addr + (g & 1) * P_BYTES + k * 32),
+            umma_f16_ss(tO, umma_desc_k_sw128(p_addr + (g & 1) * P_BYTES + (k >> 2) * (BM * 128) + (k & 3) * 32),
                         umma_desc_mn_sw128(v_addr + pg * page_bytes + ro * 128, chunk_bytes), idesc_o,
                         (j > 0 || k > 0) ? 1u : 0u);
           }
@@ -517,8 +521,9 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
             l_tile += p0 + p1;
             pk[i >> 1] = pack2<T>(p0, p1);
           }
-          const int chunk16 = (c0 / 8 + c) ^ (row & 7);
-          if (live) *reinterpret_cast<uint4*>(sub + chunk16 * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          const int gc = c0 / 8 + c;  // 16-byte chunk of the P row: 64-key sub-tile gc / 8, swizzled slot within it
+          const int chunk16 = (gc & 7) ^ (row & 7);
+          if (live) *reinterpret_cast<uint4*>(sub + (gc >> 3) * (BM * 128) + chunk16 * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         }
         if (owner && j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
           mbar_wait(&bar_o[(g - 1) & 1], ((g - 1) >> 1) & 1, 73);  // PV(g-1) done: O is stable
@@ -598,19 +603,19 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 template <typename T, int D>
 __global__ void attn_decode_tc_balanced_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                                                        T* __restrict__ out, int64_t ldo, const int* __restrict__ seq_lens,
-                                                       int B, int hq, int hkv, int max_parts, int grid_main) {
+                                                       int B, int hq, int hkv, int max_parts, int grid_main, int bn) {
   pdl_launch_dependents();
   pdl_wait();
   const int head = blockIdx.x, b = blockIdx.y;
   const int kvh = head / (hq / hkv);
   int total = 0, pre = 0;
   for (int i = 0; i < B; ++i) {
-    const int n = (seq_lens[i] + BN - 1) / BN;
+    const int n = (seq_lens[i] + bn - 1) / bn;
     if (i < b) pre += n;
     total += n;
   }
   total *= hkv;
-  const int n = (seq_lens[b] + BN - 1) / BN;
+  const int n = (seq_lens[b] + bn - 1) / bn;
   T* orow = out + (int64_t)b * ldo + (int64_t)head * D;
   if (n == 0) {
     for (int c = threadIdx.x; c < D; c += blockDim.x) orow[c] = from_f32<T>(0.f);
@@ -652,8 +657,8 @@ PFN_encodeTiledD get_encode_d() {
 }
 
 // Upper bound of the pieces one (sequence, head) item can be cut into in balanced mode.
-int balanced_max_parts(int max_blocks, int block_size) {
-  const int max_tiles = (max_blocks * block_size + BN - 1) / BN;
+int balanced_max_parts(int max_blocks, int block_size, int bn) {
+  const int max_tiles = (max_blocks * block_size + bn - 1) / bn;
   return (max_tiles + kMinQuota - 2) / kMinQuota + 1;
 }
 
@@ -671,8 +676,9 @@ int sm_count() {
 constexpr int kSmemBudget = 227 * 1024;
 
 int plan_stages(int q_alloc_rows, int d, int* smem_bytes) {
-  const int fixed = 1024 /*alignment*/ + 2048 /*barriers + softmax exchange*/ + 2 * q_alloc_rows * d * 2 + 2 * P_BYTES;
-  const int per_stage = 2 * BN * d * 2;
+  const int bn = tile_keys(d);
+  const int fixed = 1024 /*alignment*/ + 2048 /*barriers + softmax exchange*/ + 2 * q_alloc_rows * d * 2 + 2 * (BM * bn * 2);
+  const int per_stage = 2 * bn * d * 2;
   int stages = (kSmemBudget - fixed) / per_stage;
   if (stages > kMaxStages) stages = kMaxStages;
   *smem_bytes = fixed + stages * per_stage;
@@ -697,7 +703,7 @@ int launch_decode_tc(const CUtensorMap& tq, const CUtensorMap& tk, const CUtenso
 
 // Scratch (floats) of the balanced mode (num_splits = 0).
 LLMSS_API int64_t llmss_attn_decode_tc_balanced_scratch_floats(int B, int hq, int d, int max_blocks, int block_size) {
-  return (int64_t)B * hq * balanced_max_parts(max_blocks, block_size) * (d + 2);
+  return (int64_t)B * hq * balanced_max_parts(max_blocks, block_size, tile_keys(d)) * (d + 2);
 }
 
 extern "C" int llmss_attn_decode_combine(const float* part_o, const float* part_ml, void* out, int64_t ldo, int B, int hq,
@@ -706,7 +712,7 @@ extern "C" int llmss_attn_decode_combine(const float* part_o, const float* part_
 // Split factor for the persistent tensor-core kernel: CTAs walk items round-robin, so the cost of a
 // candidate is rounds * (tiles per item + per-item overhead), plus the combine pass when it splits.
 LLMSS_API int llmss_attn_decode_tc_pick_splits(int B, int hkv, int d, int max_kv) {
-  (void)d;
+  const int BN = tile_keys(d);
   const int sms = sm_count();
   const int items = B * hkv;
   if (items <= 0) return 1;
@@ -738,7 +744,7 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
   LLMSS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64, "attn_decode_tc: block_size must be 16/32/64");
   LLMSS_REQUIRE(num_splits >= 0 && (num_splits == 1 || scratch != nullptr), "attn_decode_tc: scratch required for splits");
   const int balanced = num_splits == 0 ? 1 : 0;  // flat partition of all key tiles over the SMs
-  const int max_parts = balanced_max_parts(max_blocks, block_size);
+  const int max_parts = balanced_max_parts(max_blocks, block_size, tile_keys(d));
   LLMSS_REQUIRE(ldq % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)q % 16) == 0, "attn_decode_tc: q must be 16-byte aligned");
   if (B == 0) return 0;
   PFN_encodeTiledD enc = get_encode_d();
@@ -788,6 +794,7 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
   a.part_o = scratch;
   a.part_ml = scratch ? scratch + (int64_t)B * hq * (balanced ? max_parts : num_splits) * d : nullptr;
   a.B = B;
+  a.bn = tile_keys(d);
   a.balanced = balanced;
   a.max_parts = max_parts;
   a.hq = hq;
@@ -827,7 +834,7 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
 #define LLMSS_BC(T_, D_)                                                                                             \
   LLMSS_CHECK_CUDA(launch_pdl(attn_decode_tc_balanced_combine_kernel<T_, D_>, cgrid, dim3(threads), 0, stream, \
                               (const float*)a.part_o, (const float*)a.part_ml, (T_*)out, ldo, seq_lens, B, hq, hkv,  \
-                              max_parts, sm_count()))
+                              max_parts, sm_count(), a.bn))
     if (dtype == LLMSS_F16) {
       if (d == 64) LLMSS_BC(__half, 64); else if (d == 128) LLMSS_BC(__half, 128); else LLMSS_BC(__half, 256);
     } else {

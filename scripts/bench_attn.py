@@ -78,3 +78,7 @@ if __name__ == "__main__":
                                 (4, 1, 128, 4096)):
         bench(64, hq_, hkv_, d_, ctx_, bs=64)
         bench(64, hq_, hkv_, d_, ctx_, 0, bs=64)
+    print("head_dim 64 (OPT / GPT-2 family), 64-token pages")
+    bench(64, 32, 32, 64, 1040, bs=64)
+    bench(64, 16, 16, 64, 1040, bs=64)
+    bench(64, 25, 25, 64, 1040, bs=64)

@@ -282,7 +282,83 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Vocab-parallel greedy decoding (K11, greedy case): instead of all-gathering [B, V] fp32 logits, every
+// rank reduces its own vocab shard to one (value, global index) candidate per row, the candidates
+// (16 bytes per row and rank) are gathered, and every rank picks the winner -- same token on all ranks,
+// ties resolved towards the lowest index exactly like the single-GPU sampler.
+struct Cand { float v; int idx; int pad0, pad1; };
+
+__global__ void __launch_bounds__(256) argmax_local_kernel(const float* __restrict__ logits, int64_t ld, int n_valid,
+                                                          int idx_offset, Cand* __restrict__ cand) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float sv[8];
+  __shared__ int si[8];
+  const int row = blockIdx.x;
+  const float* x = logits + (int64_t)row * ld;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < n_valid; i += blockDim.x) {
+    const float v = x[i];
+    if (v > best) { best = v; bi = i; }  // increasing i per thread: first occurrence wins
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w)
+      if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
+    Cand c;
+    c.v = best;
+    c.idx = (bi == 0x7fffffff) ? 0x7fffffff : bi + idx_offset;  // empty shard: never wins a tie
+    c.pad0 = c.pad1 = 0;
+    cand[row] = c;
+  }
+}
+
+__global__ void argmax_merge_kernel(const Cand* __restrict__ cand, int nranks, int B, int* __restrict__ out32,
+                                    long long* __restrict__ out64) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= B) return;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int r = 0; r < nranks; ++r) {
+    const Cand c = cand[(int64_t)row * nranks + r];
+    if (c.v > best || (c.v == best && c.idx < bi)) { best = c.v; bi = c.idx; }
+  }
+  if (bi == 0x7fffffff) bi = 0;
+  if (out32) out32[row] = bi;
+  if (out64) out64[row] = bi;
+}
+
 }  // namespace
+
+// cand: [B] 16-byte records (this rank's best logit of each row and its global vocabulary index).
+LLMSS_API int llmss_argmax_local(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, void* cand,
+                                 cudaStream_t stream) {
+  LLMSS_REQUIRE(n_valid >= 0 && ld >= n_valid, "argmax_local: bad shard width");
+  if (B == 0) return 0;
+  LLMSS_CHECK_CUDA(launch_pdl(argmax_local_kernel, dim3(B), dim3(256), 0, stream, logits, ld, n_valid, idx_offset,
+                              (Cand*)cand));
+  return 0;
+}
+
+// cand_all: [B][nranks] records (the column-gathered candidates); writes the winning token of every row.
+LLMSS_API int llmss_argmax_merge(const void* cand_all, int nranks, int B, int* out_tokens, long long* out_tokens64,
+                                 cudaStream_t stream) {
+  if (B == 0) return 0;
+  LLMSS_CHECK_CUDA(launch_pdl(argmax_merge_kernel, dim3((B + 127) / 128), dim3(128), 0, stream, (const Cand*)cand_all,
+                              nranks, B, out_tokens, out_tokens64));
+  return 0;
+}
 
 LLMSS_API int llmss_sample(const float* logits, int64_t ld, int B, int vocab, const int* greedy,
                            const float* temperature, const int* top_k, const float* top_p, uint32_t* rng_state,

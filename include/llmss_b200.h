@@ -127,6 +127,13 @@ int llmss_attn_decode_static(const void* q, int64_t ldq, const void* k_cache, co
 int llmss_embed(const int* tokens, const int* positions, const void* wte, const void* wpe, void* out, int T, int H,
                 int vocab, int max_pos, int pos_offset, int64_t ldo, int dtype, llmss_stream_t stream);
 
+/* ---- K11 (greedy case) vocab-parallel argmax: per-rank candidate, gathered with llmss_allgather_cols (16 bytes
+ * per row and rank), merged on every rank -- no [B, V] logits all-gather (generate.py:111, layers.py:131-135) ---- */
+int llmss_argmax_local(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, void* cand,
+                       llmss_stream_t stream);
+int llmss_argmax_merge(const void* cand_all, int nranks, int B, int* out_tokens, long long* out_tokens64,
+                       llmss_stream_t stream);
+
 /* ---- K11 fused sampler (G15, G16, N6; generate.py:109-144) ---- */
 int llmss_sample(const float* logits, int64_t ld, int B, int vocab, const int* greedy, const float* temperature,
                  const int* top_k, const float* top_p, uint32_t* rng_state, int* out_tokens,

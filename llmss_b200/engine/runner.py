@@ -11,6 +11,8 @@ Design points vs. the reference loop (generate.py:102-145, consumer_server.py:12
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
 
@@ -77,8 +79,9 @@ class ModelRunner:
         self.alloc = BlockAllocator(num_blocks)
         self.cuda = self.device.type == "cuda"
         self.use_graph = self.cuda if use_cuda_graph is None else (use_cuda_graph and self.cuda)
-        self.graphs: Dict[int, torch.cuda.CUDAGraph] = {}
+        self.graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}   # (padded batch, vocab-parallel greedy) -> graph
         self.launches_per_graph: Dict[int, int] = {}   # own-kernel launches captured per decode graph
+        self._all_greedy = True
         self._tuned_splits: Dict[int, int] = {}
         self.tuning_log: Dict[int, dict] = {}
         self.graph_pool = None
@@ -181,6 +184,7 @@ class ModelRunner:
         self.np_active[:] = False
         self.np_len[:] = 0
         self.np_nblk[:] = 0
+        self._all_greedy = all(s.params.is_greedy for s in seqs)
         for i, s in enumerate(seqs):
             s.slot = i
             self.h_samp_i[i] = int(s.params.is_greedy)
@@ -223,15 +227,27 @@ class ModelRunner:
         self.np_slot[:] = np.where(act, blk * bs + pos % bs, -1)
         self.np_slen[:] = np.where(act, pos + 1, 0)
 
-    def _decode_body(self, Bp: int, splits: int):
+    def _vp_greedy(self) -> bool:
+        """Vocab-parallel greedy decoding (no logits all-gather): TP > 1 on CUDA and every bound request greedy."""
+        c = self.core.comm
+        return bool(self.cuda and self._all_greedy and not c.single and c.symm is not None
+                    and os.environ.get("LLMSS_VP_GREEDY", "1") == "1")
+
+    def _decode_body(self, Bp: int, splits: int, vp_greedy: bool = False):
         tok, pos, slot, slen, bt = self._dev_views(Bp)
         MB = self.max_batch
         batch = BatchInput(tokens=tok, positions=pos, slot_mapping=slot, block_tables=bt, seq_lens=slen,
                            cu_q=self.d_cu[:Bp + 1], last_idx=self.d_last_idx[:Bp], num_seqs=Bp, max_q=1,
                            max_kv=self.max_seq_len, is_decode=True, is_fresh_prefill=False, decode_splits=splits)
-        logits = self.core.forward(batch, self.kv, last_only=False)  # every row is a last token
         # the sampler writes into the token region: it is both this step's result and the next
         # step's input (device-side feedback loop; no host round trip needed between steps)
+        if vp_greedy:
+            from ..ops import cuda_impl as cu
+
+            local = self.core.forward(batch, self.kv, last_only=False, gather_logits=False)
+            cu.greedy_vocab_parallel(local, self.core.comm.symm, self.spec.vocab, out=tok)
+            return
+        logits = self.core.forward(batch, self.kv, last_only=False)  # every row is a last token
         ops.sample(logits, self.d_samp_i[:Bp], self.d_samp_f[:Bp], self.d_samp_i[MB:MB + Bp],
                    self.d_samp_f[MB:MB + Bp], self.d_rng[:Bp], vocab=self.spec.vocab, out=tok)
 
@@ -284,12 +300,12 @@ class ModelRunner:
         self.tuning_log[Bp] = {"ctx": L, "us_per_call": table, "picked": best, "heuristic": base}
         return best
 
-    def capture(self, Bp: int):
+    def capture(self, Bp: int, vp: bool = False):
         """Warm up and capture the decode graph for a padded batch size, on inert inputs
         (slot -1, seq_len 0: no cache writes), then restore the live step state."""
-        if not self.use_graph or Bp in self.graphs:
+        if not self.use_graph or (Bp, vp) in self.graphs:
             return
-        splits = self.autotune_decode_splits(Bp)
+        splits = self._tuned_splits[Bp] if Bp in self._tuned_splits else self.autotune_decode_splits(Bp)
         saved_in, saved_rng = self.d_in.clone(), self.d_rng.clone()
         inert = torch.zeros_like(self.h_in)
         MB = self.max_batch
@@ -301,7 +317,7 @@ class ModelRunner:
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(2):
-                self._decode_body(Bp, splits)
+                self._decode_body(Bp, splits, vp)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.core.comm.barrier()
@@ -310,20 +326,21 @@ class ModelRunner:
         g = torch.cuda.CUDAGraph()
         n0 = _lib.LAUNCHES["count"]
         with torch.cuda.graph(g, pool=self.graph_pool):
-            self._decode_body(Bp, splits)
+            self._decode_body(Bp, splits, vp)
         self.launches_per_graph[Bp] = _lib.LAUNCHES["count"] - n0
         if self.graph_pool is None:
             self.graph_pool = g.pool()
-        self.graphs[Bp] = g
+        self.graphs[(Bp, vp)] = g
         self.d_in.copy_(saved_in)
         self.d_rng.copy_(saved_rng)
         torch.cuda.synchronize()
 
     def _launch_decode(self, Bp: int):
+        vp = self._vp_greedy()
         if not self.use_graph:
-            self._decode_body(Bp, self._splits_for(Bp))
+            self._decode_body(Bp, self._splits_for(Bp), vp)
             return
-        self.graphs[Bp].replay()
+        self.graphs[(Bp, vp)].replay()
         self.stats["graph_replays"] += 1
 
     @torch.no_grad()
@@ -336,8 +353,8 @@ class ModelRunner:
         B = len(self.batch_seqs)
         Bp = self._bucket(B)
         MB = self.max_batch
-        if self.use_graph and Bp not in self.graphs:
-            self.capture(Bp)
+        if self.use_graph and (Bp, self._vp_greedy()) not in self.graphs:
+            self.capture(Bp, self._vp_greedy())
         self._fill_step_inputs()
         if host_tokens:
             self.d_in.copy_(self.h_in, non_blocking=True)

@@ -294,13 +294,20 @@ class DecoderLM(nn.Module):
         with trace("logits_all_gather"):
             return self.comm.all_gather_cat(local, dim=-1)
 
-    def forward(self, batch: BatchInput, kv, last_only: bool = True) -> torch.Tensor:
+    def local_logits(self, hidden_rows: torch.Tensor) -> torch.Tensor:
+        """This rank's vocab shard of the fp32 logits, [R, vocab_blk] (no collective); the vocab-parallel
+        greedy sampler (`ops.cuda_impl.greedy_vocab_parallel`) consumes it directly."""
+        with trace("lm_head"):
+            return ops.linear(hidden_rows, self.w_head, self.b_head, out_dtype=torch.float32)
+
+    def forward(self, batch: BatchInput, kv, last_only: bool = True, gather_logits: bool = True) -> torch.Tensor:
         if last_only and self._sp_ok(batch):
-            return self.logits(self._gather_last_rows(self._forward_hidden_sp(batch, kv), batch))
-        h = self.forward_hidden(batch, kv)
-        if last_only:
-            h = h.index_select(0, batch.last_idx)
-        return self.logits(h)
+            h = self._gather_last_rows(self._forward_hidden_sp(batch, kv), batch)
+        else:
+            h = self.forward_hidden(batch, kv)
+            if last_only:
+                h = h.index_select(0, batch.last_idx)
+        return self.logits(h) if gather_logits else self.local_logits(h)
 
 
 # ----------------------------------------------------------------------------- loading helpers

@@ -35,6 +35,8 @@ _SIGS = {
     "llmss_symm_epoch": (c_int, [c_void_p, C.POINTER(C.c_uint32)]),
     "llmss_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "llmss_allgather": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "llmss_argmax_local": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "llmss_argmax_merge": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "llmss_allgather_cols": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "llmss_gemm_set_debug": (c_int, [c_void_p]),
     "llmss_gemm_plan_query": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, C.POINTER(GemmPlan)]),

@@ -256,3 +256,25 @@ def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab=None, out
     _lib.check(rc, "llmss_sample")
     _count()
     return out
+
+
+def greedy_vocab_parallel(local_logits, symm, vocab: int, out=None):
+    """K11 (greedy case): argmax over vocab-sharded fp32 logits [B, V/t] without gathering them.  Every rank
+    reduces its shard to one 16-byte (value, global index) candidate per row, the candidates are gathered
+    column-wise and merged identically on every rank."""
+    lib = _lib.load()
+    B, Vb = local_logits.shape
+    assert local_logits.dtype == torch.float32 and local_logits.stride(1) == 1
+    off = symm.rank * Vb
+    n_valid = max(0, min(Vb, vocab - off))
+    cand = torch.empty(B, 4, dtype=torch.int32, device=local_logits.device)
+    _lib.check(lib.llmss_argmax_local(_ptr(local_logits), local_logits.stride(0), B, n_valid, off, _ptr(cand), _stream()),
+               "llmss_argmax_local")
+    allc = symm.all_gather_cols(cand)  # [B, t * 4]
+    if out is None:
+        out = torch.empty(B, dtype=torch.int32, device=local_logits.device)
+    o32 = _ptr(out) if out.dtype == torch.int32 else None
+    o64 = _ptr(out) if out.dtype == torch.int64 else None
+    _lib.check(lib.llmss_argmax_merge(_ptr(allc), symm.nranks, B, o32, o64, _stream()), "llmss_argmax_merge")
+    _count(2)
+    return out

@@ -32,7 +32,7 @@ def main():
     pg, rank, world = initialize_torch_distributed(timeout_s=120)
     dev = torch.device("cuda", torch.cuda.current_device())
     comm = comm_for(pg, dev)
-    symm = comm.attach_symmetric(64 << 20)  # bulk; Lamport area default 16 MiB
+    symm = comm.attach_symmetric(64 << 20, lamport_bytes=max(16, 8 * world) << 20)  # bulk + Lamport area (grows with the rank count)
     assert symm is not None
     ok = True
 

@@ -20,14 +20,6 @@ constexpr int kThreads = kWarps * 32;
 constexpr int kStages = 4;  // cp.async ring depth per warp
 constexpr int kRingBytes(int U) { return kWarps * kStages * U * 2 * 32 * 16; }
 
-__device__ __forceinline__ uint4 ldg_stream(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
-  return r;
-}
-
 template <typename T, int D, int GT, int U>
 __global__ void __launch_bounds__(kThreads) attn_decode_kernel(
     const T* __restrict__ q, int64_t ldq, const T* __restrict__ k_cache, const T* __restrict__ v_cache,

@@ -39,7 +39,6 @@ namespace {
 constexpr int BM = 128;  // output features per tile (UMMA M)
 constexpr int BK = 64;   // k-block: 64 x 16-bit = one 128-byte swizzle row
 constexpr int kNumThreads = 192;  // warp 0 TMA, warp 1 MMA (+TMEM alloc), warps 2..5 epilogue
-constexpr int kEpiThreads = 128;
 
 template <int BN>
 struct Cfg {
@@ -120,20 +119,10 @@ struct SegIter {
 };
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
-__device__ __forceinline__ float ld_cg_f32(const float* p) {
-  float v;
-  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
-  return v;
-}
 __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   float4 v;
   asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
-}
-__device__ __forceinline__ uint4 ld_cg_u4(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-  return r;
 }
 
 

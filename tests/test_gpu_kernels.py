@@ -211,6 +211,38 @@ def test_embed():
     _close(cu.embed(tok, wte, pos, wpe, 2), R.embed(tok, wte, pos, wpe, 2).float(), 2e-2, 1e-2, "wte+wpe")
 
 
+def test_vocab_parallel_argmax_kernels():
+    """K11 greedy case on one GPU: per-shard candidates + merge == argmax of the full logits (first maximum wins)."""
+    import ctypes as C
+
+    from llmss_b200.ops import _lib
+
+    lib = _lib.load()
+    torch.manual_seed(5)
+    B, V, t = 37, 50400, 8
+    Vb = -(-V // t)  # ceil-div shards, the last one is partly padding
+    logits = torch.randn(B, Vb * t, device="cuda")
+    logits[:, V:] = 1e9  # padding columns must never win
+    logits[3, 100] = logits[3, 40000] = 50.0   # tie across shards -> lowest index
+    logits[4, 7] = logits[4, 8] = 60.0         # tie inside a shard
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    cands = torch.empty(B, t, 4, dtype=torch.int32, device="cuda")
+    for r in range(t):
+        shard = logits[:, r * Vb:(r + 1) * Vb]
+        c = torch.empty(B, 4, dtype=torch.int32, device="cuda")
+        n_valid = max(0, min(Vb, V - r * Vb))
+        _lib.check(lib.llmss_argmax_local(C.c_void_p(shard.data_ptr()), shard.stride(0), B, n_valid, r * Vb,
+                                          C.c_void_p(c.data_ptr()), stream), "argmax_local")
+        cands[:, r] = c
+    out = torch.empty(B, dtype=torch.int32, device="cuda")
+    _lib.check(lib.llmss_argmax_merge(C.c_void_p(cands.data_ptr()), t, B, C.c_void_p(out.data_ptr()), None, stream),
+               "argmax_merge")
+    ref = logits[:, :V].argmax(dim=-1)
+    assert out.tolist()[3] == 100 and out.tolist()[4] == 7
+    rows = [i for i in range(B) if i not in (3, 4)]
+    assert torch.equal(out.long()[rows], ref[rows])
+
+
 def test_sample_matches_oracle():
     cu = _cu()
     torch.manual_seed(3)

@@ -3,6 +3,8 @@
 # gpurun call (B200_PROFILING.md): usage  scripts/sanitize.sh memcheck|racecheck|synccheck|initcheck
 # Cross-GPU flag protocols are not visible to racecheck; they are covered by the stress loop in
 # scripts/mgpu_check.py (--stress N: N back-to-back mixed collectives with randomised per-rank delays).
+# NOTE: on the graft GPU pool compute-sanitizer is refused ("closed on this pool"); see DESIGN.md section 7 for
+# what replaces it there.
 set -euo pipefail
 TOOL=${1:-memcheck}
 cd "$(dirname "$0")/.."

@@ -25,6 +25,29 @@ def test_engine_gpu_matches_cpu_oracle(tmp_path, preset, fuse):
     assert gpu.runner.stats["graph_replays"] > 0
 
 
+def test_engine_page_sizes_agree(tmp_path):
+    """64-token pages (tcgen05 decode kernel, the CUDA default) vs 16-token pages (CUDA-core kernel): sequences
+    that start mid-page, cross page boundaries while decoding and span several pages must decode alike."""
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+    from llmss_b200.utils.checkpoint import write_random_checkpoint
+
+    path = str(write_random_checkpoint(tmp_path, "gptj-tiny", dtype=torch.float32, device="cpu", std=0.08))
+    g = torch.Generator().manual_seed(11)
+    prompts = [torch.randint(1, 500, (n,), generator=g).tolist() for n in (60, 130, 5, 64, 63)]
+    sp = SamplingParams(max_new_tokens=24, is_greedy=True)
+    outs = {}
+    for bs in (16, 64):
+        eng = Engine.from_pretrained(path, dtype=torch.bfloat16, device="cuda", max_batch=8, max_seq_len=200,
+                                     block_size=bs)
+        assert eng.runner.block_size == bs
+        outs[bs] = eng.generate(prompts, sp)
+        assert eng.runner.stats["graph_replays"] > 0
+    # two different kernels in bf16: allow a late near-tie flip, but the bulk must agree
+    same = sum(a[:10] == b[:10] for a, b in zip(outs[16], outs[64]))
+    assert same >= len(prompts) - 1, (outs[16], outs[64])
+
+
 @pytest.mark.parametrize("family", ["llama", "gpt_bigcode", "gpt2", "opt", "gptj"])
 def test_families_gpu_logits_close_to_cpu(tmp_path, family):
     """Prefill + one decode step logits on GPU (own kernels) vs the CPU oracle for every family."""

@@ -726,6 +726,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   }
   __syncwarp();
   cluster_sync_all();  // every CTA's partial tile is now visible cluster-wide
+  if (threadIdx.x == 64) LLMSS_STAMP(2);
 
   if (warp >= 2) {
     const int epi_tid = threadIdx.x - 64;
@@ -753,11 +754,23 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         for (int j = 0; j < 8; ++j) v[0][j] = 0.f;
         if (pass == 0) {
           const uint32_t off = (uint32_t)(((cg * 2) * BM + f) * 16);
-          for (int q = 0; q < S; ++q) {  // CTA order: deterministic
-            const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
-            const float4 lo = ld_dsmem_f4(base), hi = ld_dsmem_f4(base + BM * 16);
-            v[0][0] += lo.x; v[0][1] += lo.y; v[0][2] += lo.z; v[0][3] += lo.w;
-            v[0][4] += hi.x; v[0][5] += hi.y; v[0][6] += hi.z; v[0][7] += hi.w;
+          // all peers' partials are requested before the first one is consumed: one DSMEM round trip per
+          // item instead of one per peer (the reduce was 2 of the ~3 us epilogue of the TP=8 decode GEMMs)
+          float4 lo[8], hi[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            if (q < S) {
+              const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
+              lo[q] = ld_dsmem_f4(base);
+              hi[q] = ld_dsmem_f4(base + BM * 16);
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {  // CTA order: deterministic
+            if (q < S) {
+              v[0][0] += lo[q].x; v[0][1] += lo[q].y; v[0][2] += lo[q].z; v[0][3] += lo[q].w;
+              v[0][4] += hi[q].x; v[0][5] += hi[q].y; v[0][6] += hi[q].z; v[0][7] += hi[q].w;
+            }
           }
           if (a.ar) {
             const uint4 vec = lam_sanitize<2>(pack8<T>(v[0]));

@@ -46,6 +46,11 @@ def run(M, N, K, **kw):
               f"median {d2.median():.2f} max {d2.max():.2f} us | total median {d3.median():.2f} max {d3.max():.2f}")
 
 
+if len(sys.argv) > 1 and sys.argv[1] == "small":
+    run(64, 3584, 4096, bias=True, act=1, act_start=1536)
+    run(64, 4096, 2560, bias=True)
+    run(64, 4096, 4096)
+    sys.exit(0)
 if len(sys.argv) > 1 and sys.argv[1] == "epi":
     run(64, 28672, 4096)
     run(64, 28672, 4096, bias=True, act=1, act_start=12288)

@@ -12,21 +12,24 @@
 //    the activations are the B operand (N = 16..256 tokens).  Decode batches (1..256 tokens)
 //    therefore use full-width tensor-core instructions with no padding waste, and the
 //    accumulator sits in TMEM as [feature lane][token column] so bias is a per-thread scalar.
-//  * TMA (cp.async.bulk.tensor, 128B swizzle) feeds a multi-stage mbarrier ring; one elected
-//    thread issues tcgen05.mma; accumulators are double-buffered in TMEM so the epilogue of
-//    one work segment overlaps the main loop of the next.
-//  * stream-K persistent scheduling: the (tile x k-block) iteration space is cut into
-//    gridDim.x equal contiguous ranges, so all 148 SMs stream weights for the same time
-//    whatever the shape (decode GEMMs have far fewer than 148 output tiles).  Tiles touched
-//    by several CTAs are reduced through an L2-resident fp32 workspace by the last arriver
-//    in a fixed order (deterministic).
-//  * fused all-reduce (ar=1): the CTA that owns the finished tile pushes it (16-byte
-//    vectors, tile-blocked layout) into every peer's symmetric buffer, raises a per-tile
-//    flag, waits for the peers' flags of the *same tile only*, sums the t partials in rank
-//    order (bit-identical on all ranks), adds bias/residual and stores.  Transfer of tile i
-//    overlaps the math of tile i+1; there is no grid-wide or host-side barrier.
+//  * TMA (cp.async.bulk.tensor, 128B swizzle) feeds a multi-stage mbarrier ring; the TMA and MMA
+//    warps run their loops converged and issue from one elected lane (elect_one: operands stay in
+//    uniform registers); accumulators are double-buffered in TMEM so the epilogue of one work
+//    segment overlaps the main loop of the next.
+//  * scheduling, chosen on the host (llmss_gemm_plan_query2):
+//      - <= 74 tiles: cluster split-K kernel (gemm_cluster_kernel, DSMEM reduction);
+//      - a grid that owns whole tiles exists near the SM count (tiles <= SMs, or tiles = 2 x grid):
+//        that grid, no partial tiles;
+//      - otherwise stream-K: the (tile x k-block) space is cut into gridDim.x equal contiguous
+//        ranges; tiles touched by several CTAs are reduced through an L2-resident fp32 workspace by
+//        the last arriver in CTA order (deterministic); >= 4 tiles per CTA: ranges cut at tile bounds.
+//  * fused collectives (llmss_gemm_ex): all-reduce / reduce-scatter push finished tiles as
+//    self-validating 16-byte vectors into the peers' Lamport area and sum them in rank order
+//    (bit-identical on all ranks; tile i is on the wire while tile i+1 computes); all-gather mode
+//    stages the ranks' activation shards through the bulk area while the own shard already computes.
 //  * epilogues: bias, activation (optionally only for features >= act_start: GPT-J's fused
-//    QKV+fc_in GEMM), SwiGLU gating on interleaved (gate, up) rows, residual add, fp32 out.
+//    QKV+fc_in GEMM), SwiGLU gating on interleaved (gate, up) rows, residual add, fp32 out --
+//    template-specialised per (flavour, activation), residual / partial loads prefetched per chunk.
 #include "common.cuh"
 #include "symm.cuh"
 

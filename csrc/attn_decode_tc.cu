@@ -362,7 +362,11 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
     // different warps so that S runs two tiles ahead of the softmax instead of queueing behind PV.
     const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
     const int bs = a.block_size, pages = BN / bs;
-    const uint32_t idesc_s = idesc_f16(fmt, BM, bs, 0);  // one MMA group per page: N = block_size keys
+    // G <= 8 (q_sbo == 0: every 8-row group re-reads the same q rows): a 64-row MMA is enough -- its rows
+    // 16q..16q+15 land in lanes 0..15 of sub-partition q, so each softmax warp still finds heads 0..G-1 in
+    // its lanes 0..G-1 -- and it halves the tensor-pipe work (and power) spent on replicated rows.
+    const int mma_m = (a.q_sbo == 0) ? 64 : BM;
+    const uint32_t idesc_s = idesc_f16(fmt, mma_m, bs, 0);  // one MMA group per page: N = block_size keys
     const uint32_t k_base = smem_u32(sK), q_base = smem_u32(sQ);
     const uint32_t page_bytes = bs * D * 2, chunk_bytes = bs * 128;
     int kst = 0, n = 0;
@@ -401,7 +405,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
     // ===================== PV issuer: O += P(g) V(g) once the softmax warps have published P(g) ==========
     const int fmt = a.dtype == LLMSS_BF16 ? 1 : 0;
     const int bs = a.block_size;
-    const uint32_t idesc_o = idesc_f16(fmt, BM, D, 1);
+    const uint32_t idesc_o = idesc_f16(fmt, (a.q_sbo == 0) ? 64 : BM, D, 1);  // see the QK issuer: 64 rows when G <= 8
     const uint32_t p_addr = smem_u32(sP), v_base = smem_u32(sV);
     const uint32_t page_bytes = bs * D * 2, chunk_bytes = bs * 128;
     int vst = 0;

@@ -13,6 +13,10 @@
 // MMA still reads 128 rows, the extra rows are whatever follows in shared memory and only feed
 // accumulator rows nobody reads.  Softmax warps whose 32 rows are all >= G do not run at all.
 //
+// Contract note: keys past a sequence's length are masked to -inf before the exponential, but the V rows of a
+// partially filled page still enter the PV MMA multiplied by P = 0, so cache pages must hold finite values
+// (0 * NaN = NaN).  The engine zero-initialises the pool and pages only ever hold real K/V, so this holds.
+//
 // Replaces SURVEY.md G8 (`baddbmm` + TorchScript softmax + `bmm` on a replicated KV tensor,
 // gpt_bigcode_modeling.py:170-246) and G7 for grouped models.
 #include "common.cuh"

@@ -231,3 +231,90 @@ def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab: Optional
     plain = (top_k <= 0) & (top_p.float() >= 1.0)
     tok = torch.where(plain, tok_full, tok_cand)
     return torch.where(greedy, arg, tok)
+
+
+# --------------------------------------------------------------------------- vocab-parallel sampling oracle
+def shard_summary(local_logits, offset: int, vocab: int, k: int):
+    """What one TP rank would contribute to a vocab-parallel sampler (K11, general case) for its
+    shard ``local_logits`` [B, Vb] whose column 0 is global token ``offset``: the local maximum, and
+    every local element >= the local k-th largest (value, global index) -- ties included, which is
+    what makes the merge exact (an element >= the global k-th value is >= its rank's local k-th value).
+    Columns at or beyond ``vocab`` are padding."""
+    x = local_logits.float().clone()
+    B, Vb = x.shape
+    n_valid = max(0, min(Vb, vocab - offset))
+    x[:, n_valid:] = float("-inf")
+    out = []
+    for b in range(B):
+        row = x[b, :n_valid]
+        if n_valid == 0:
+            out.append(dict(max=float("-inf"), vals=row.new_zeros(0), idx=torch.zeros(0, dtype=torch.long), row=row,
+                            offset=offset))
+            continue
+        kk = min(k, n_valid)
+        thr = torch.topk(row, kk).values[-1]
+        sel = (row >= thr).nonzero()[:, 0]
+        out.append(dict(max=row.max().item(), vals=row[sel], idx=sel + offset, row=row, offset=offset))
+    return out
+
+
+def sample_vocab_parallel(shards, greedy, temperature, top_k, top_p, rng_state, vocab: int, k_summary: int = 64):
+    """`sample()` computed from per-rank shard summaries only (the algorithm a vocab-parallel CUDA sampler
+    follows; replaces the [B, V] logits all-gather of layers.py:131-135 + generate.py:109-129).
+
+    ``shards``: list over ranks of fp32 [B, Vb] local logits (rank r starts at token r * Vb).
+    Exchanged per row and rank: local max, local sum-exp, the local top-``k_summary`` candidates
+    (+ ties); for the plain multinomial path two scalars (weight sum, count below the target).
+    Rows whose effective k exceeds ``k_summary`` (top_k = 0 with top_p < 1 searches 1024 candidates)
+    are outside this path -- the caller gathers the logits for them."""
+    t = len(shards)
+    B, Vb = shards[0].shape
+    summ = [shard_summary(s, r * Vb, vocab, k_summary) for r, s in enumerate(shards)]
+    u = rng_uniform(rng_state[:, 0], rng_state[:, 1]).double()
+    rng_state[:, 1] += 1
+    toks = torch.zeros(B, dtype=torch.long)
+    for b in range(B):
+        rows = [summ[r][b] for r in range(t)]
+        M = max(r_["max"] for r_ in rows)
+        vals = torch.cat([r_["vals"] for r_ in rows])
+        idx = torch.cat([r_["idx"] for r_ in rows])
+        # global order: probability descending, index ascending
+        o = torch.argsort(idx, stable=True)
+        vals, idx = vals[o], idx[o]
+        o = torch.argsort(vals, descending=True, stable=True)
+        sl, si = vals[o], idx[o]
+        if bool(greedy[b]):
+            toks[b] = si[0]
+            continue
+        T = float(temperature[b])
+        k, p = int(top_k[b]), float(top_p[b])
+        if k <= 0 and p >= 1.0:
+            # plain multinomial in index order: per-rank weight sums, then per-rank counts below the target
+            w = [torch.exp((r_["row"] - M) / T).double() for r_ in rows]
+            sums = [x.sum() for x in w]
+            total = sum(sums)
+            target = u[b] * total
+            count, prefix = 0, 0.0
+            for r in range(t):
+                if len(w[r]):
+                    count += int(((torch.cumsum(w[r], 0) + prefix) <= target).sum())
+                prefix = prefix + sums[r]
+            toks[b] = min(count, vocab - 1)
+            continue
+        k_eff = min(k if 0 < k <= MAX_CANDIDATES else MAX_CANDIDATES, vocab)
+        if k_eff > k_summary:
+            raise ValueError(f"row {b}: effective top-k {k_eff} exceeds the summary size {k_summary}")
+        # global sum-exp from the ranks' (local max, local sum-exp) pairs
+        Z = sum(float(torch.exp(r_["row"] - r_["max"]).sum()) * math.exp(r_["max"] - M) for r_ in rows if len(r_["row"]))
+        thr_k = sl[k_eff - 1]
+        head = sl >= thr_k            # complete: everything >= the global k-th value is in the union
+        sl, si = sl[head], si[head]
+        sp = torch.exp(sl - M) / Z
+        prev = torch.cumsum(sp, 0) - sp
+        n_p = max(int((prev < p).sum()), 1)
+        keep = sl >= sl[n_p - 1]
+        wt = torch.where(keep, torch.exp((sl - M) / T), torch.zeros_like(sl)).double()
+        c = torch.cumsum(wt, 0)
+        pick = min(int((c <= u[b] * c[-1]).sum()), int(keep.sum()) - 1)
+        toks[b] = si[pick]
+    return toks

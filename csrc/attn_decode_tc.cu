@@ -22,6 +22,7 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace {
@@ -46,6 +47,8 @@ struct DArgs {
   int q_copies;      // TMA ops per chunk: the same rows land at q_copies row offsets (physical replication)
   int q_alloc_rows;  // rows of one Q buffer in shared memory
   int q_sbo;         // stride between 8-row groups in the Q descriptors (0: every group re-reads rows 0..7)
+  int ws;            // G <= 8, 64-token pages, 64-key tiles: weight-stationary 32-row MMAs (tcgen05.mma.ws), whose
+                     // accumulator layout puts key / head-dim columns [q*N/4, (q+1)*N/4) into sub-partition q
   int block_size;
   int num_splits;
   int n_items;
@@ -221,6 +224,18 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128_sbo(uint32_t smem_addr, ui
   return d;
 }
 
+// tcgen05.mma.ws (weight-stationary form, M = 32 / 64 / 128, N = 64 / 128 / 256).  For M = 32 element (m, n) of D lives
+// in TMEM lane m + 32 * (n / (N/4)), column n % (N/4).
+__device__ __forceinline__ void umma_f16_ss_ws(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.ws.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 __device__ __forceinline__ void softmax_bar(int threads) { asm volatile("bar.sync 1, %0;" ::"r"(threads) : "memory"); }
 
 // R = how many times the q-head rows are replicated down the 128 MMA rows.  A softmax warp can only read
@@ -387,7 +402,20 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
         mbar_wait(&bar_kfull[kst], kph, 61);
         tcgen05_fence_after();
         const uint32_t k_addr = k_base + kst * KV_BYTES;
-        if (elect_one()) {
+        if (a.ws) {
+          if (elect_one()) {  // one 64-key page per tile: S[32 x 64], 16 TMEM columns per buffer
+            const uint32_t idesc_ws = idesc_f16(fmt, 32, BN, 0);
+#pragma unroll
+            for (int c = 0; c < DSUB; ++c)
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_f16_ss_ws(tS + (g & 1) * 16, umma_desc_k_sw128_sbo(q_addr + c * q_chunk + k * 32, a.q_sbo),
+                               umma_desc_k_sw128(k_addr + c * chunk_bytes + k * 32), idesc_ws, (c | k) ? 1u : 0u);
+            umma_commit(&bar_s[g & 1]);
+            umma_commit(&bar_kempty[kst]);
+            if (j + 1 == I.n_tiles) umma_commit(&bar_qempty[qb]);
+          }
+        } else if (elect_one()) {
           for (int p = 0; p < pages; ++p)
 #pragma unroll
             for (int c = 0; c < DSUB; ++c)
@@ -422,7 +450,17 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
         mbar_wait(&bar_vfull[vst], vph, 63);
         tcgen05_fence_after();
         const uint32_t v_addr = v_base + vst * KV_BYTES;
-        if (elect_one()) {
+        if (a.ws) {
+          if (elect_one()) {  // O[32 x D]: head-dim columns [q*D/4, (q+1)*D/4) land in sub-partition q
+            const uint32_t idesc_ws = idesc_f16(fmt, 32, D, 1);
+#pragma unroll
+            for (int k = 0; k < BN / 16; ++k)
+              umma_f16_ss_ws(tO, umma_desc_k_sw128(p_addr + (g & 1) * P_BYTES + k * 32),
+                             umma_desc_mn_sw128(v_addr + (k * 16) * 128, chunk_bytes), idesc_ws, (j > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&bar_o[g & 1]);
+            umma_commit(&bar_vempty[vst]);
+          }
+        } else if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BN / 16; ++k) {  // 16 keys per step; a step never straddles a page (block_size >= 16)
             const int pg = (k * 16) / bs, ro = (k * 16) % bs;
@@ -475,7 +513,8 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
         float sc[CW];
         if constexpr (CW == 16) {
           uint32_t r[16];
-          tmem_ld_32x32b_x16(tS + (g & 1) * BN + lane_off + c0, r);
+          // ws: this sub-partition already holds exactly its 16 key columns, at columns [0, 16) of the buffer
+          tmem_ld_32x32b_x16(a.ws ? tS + (g & 1) * 16 + lane_off : tS + (g & 1) * BN + lane_off + c0, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 16; ++i) sc[i] = __uint_as_float(r[i]);
@@ -533,11 +572,13 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
           const int chunk16 = (gc & 7) ^ (row & 7);
           if (live) *reinterpret_cast<uint4*>(sub + (gc >> 3) * (BM * 128) + chunk16 * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         }
-        if (owner && j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
+        // ws: the accumulator's head-dim columns are spread over the four sub-partitions, every warp owns D/4
+        const int o_cols = a.ws ? D / 4 : D;
+        if ((owner || a.ws) && j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
           mbar_wait(&bar_o[(g - 1) & 1], ((g - 1) >> 1) & 1, 73);  // PV(g-1) done: O is stable
           tcgen05_fence_after();
 #pragma unroll 1
-          for (int c = 0; c < D / 32; ++c) {
+          for (int c = 0; c < o_cols / 32; ++c) {
             uint32_t r[32];
             tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
             tmem_ld_wait();
@@ -556,25 +597,27 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
       if constexpr (R > 1) {  // total row sum = sum over the copies' column slices
         s_l[quarter * 32 + lane] = l_run;
         softmax_bar(n_threads);
-        if (owner) {
+        if (owner || a.ws) {
           l_run = 0.f;
 #pragma unroll
           for (int cc = 0; cc < R; ++cc) l_run += s_l[(cc * QPC + quarter % QPC) * 32 + lane];
         }
         softmax_bar(n_threads);  // s_l may be rewritten by the next item
       }
-      if (!owner) continue;
+      if (!owner && !a.ws) continue;
       mbar_wait(&bar_o[(g - 1) & 1], ((g - 1) >> 1) & 1, 72);
       tcgen05_fence_after();
       const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
+      const int e_cols = a.ws ? D / 4 : D;            // head-dim columns this warp holds ...
+      const int e_base = a.ws ? quarter * (D / 4) : 0;  // ... starting at this head-dim column
 #pragma unroll 1
-      for (int c = 0; c < D / 32; ++c) {
+      for (int c = 0; c < e_cols / 32; ++c) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
         tmem_ld_wait();
         if (!live) continue;
         if (I.direct) {
-          T* orow = reinterpret_cast<T*>(a.out) + (int64_t)I.b * a.ldo + (int64_t)head * D;
+          T* orow = reinterpret_cast<T*>(a.out) + (int64_t)I.b * a.ldo + (int64_t)head * D + e_base;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             float f8[8];
@@ -583,14 +626,14 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
             *reinterpret_cast<uint4*>(orow + c * 32 + q * 8) = pack8<T>(f8);
           }
         } else {
-          float4* dst = reinterpret_cast<float4*>(a.part_o + pidx * D + c * 32);
+          float4* dst = reinterpret_cast<float4*>(a.part_o + pidx * D + e_base + c * 32);
 #pragma unroll
           for (int q = 0; q < 8; ++q)
             dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
                                  __uint_as_float(r[4 * q + 3]));
         }
       }
-      if (live && !I.direct) {
+      if (live && !I.direct && owner) {
         a.part_ml[pidx * 2] = m_run;
         a.part_ml[pidx * 2 + 1] = l_run;
       }
@@ -812,6 +855,10 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
   a.q_copies = q_copies;
   a.q_alloc_rows = q_alloc_rows;
   a.q_sbo = q_sbo;
+  {
+    const char* e = getenv("LLMSS_ATTN_WS");  // LLMSS_ATTN_WS=0 falls back to the 64-row tcgen05.mma form
+    a.ws = (!(e != nullptr && e[0] == '0') && G <= 8 && block_size == 64 && tile_keys(d) == 64) ? 1 : 0;
+  }
   a.block_size = block_size;
   a.num_splits = num_splits;
   a.n_items = B * hkv * num_splits;

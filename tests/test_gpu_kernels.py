@@ -1,6 +1,8 @@
 """GPU numerics: every sm_100a kernel against the plain-PyTorch fp32 oracle of the same op."""
 import math
 
+import os
+
 import pytest
 import torch
 
@@ -197,6 +199,33 @@ def test_attn_decode_tc_matches_cuda_core_path(monkeypatch, bs):
     ref = R.attention_paged(q.reshape(B, hq, d), kc, vc, bt, sl, cu_q, d ** -0.5).reshape(B, hq * d)
     for o in outs:
         _close(o, ref, 2e-2, 2e-2, "attn_decode tc / cuda-core vs oracle")
+
+
+@pytest.mark.parametrize("ws", ["1", "0"])
+@pytest.mark.parametrize("hq,hkv,d", [(16, 16, 256), (8, 8, 128), (8, 2, 128)])
+def test_attn_decode_ws_and_plain_mma(hq, hkv, d, ws, monkeypatch):
+    """Groups of <= 8 q heads on 64-token pages: the weight-stationary 32-row MMA form (default) and the plain
+    64-row form (LLMSS_ATTN_WS=0) of the tcgen05 decode kernel must both match the oracle."""
+    cu = _cu()
+    monkeypatch.setenv("LLMSS_ATTN_WS", ws)
+    torch.manual_seed(2)
+    B, bs = 6, 64
+    lens = [1, 64, 65, 300, 1025, 130]
+    maxb = (max(lens) + bs - 1) // bs
+    nb = 1 + B * maxb
+    kc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=torch.bfloat16)
+    vc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=torch.bfloat16)
+    perm = (torch.randperm(nb - 1) + 1).tolist()
+    bt = torch.tensor([[perm[i * maxb + j] for j in range(maxb)] for i in range(B)], dtype=torch.int32, device="cuda")
+    sl = torch.tensor(lens, dtype=torch.int32, device="cuda")
+    q = torch.randn(B, hq * d, device="cuda", dtype=torch.bfloat16)
+    cu_q = torch.arange(B + 1, dtype=torch.int32, device="cuda")
+    ref = R.attention_paged(q.reshape(B, hq, d), kc, vc, bt, sl, cu_q, d ** -0.5).reshape(B, hq * d)
+    for splits in (1, 3):
+        o = torch.zeros_like(q)
+        cu.attn_decode(q, kc, vc, bt, sl, o, hq, hkv, d, d ** -0.5, splits)
+        torch.cuda.synchronize()
+        _close(o, ref, 2e-2, 2e-2, f"attn_decode ws={ws} splits={splits}")
 
 
 # ------------------------------------------------------------------ embed / sample

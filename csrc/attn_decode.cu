@@ -262,12 +262,8 @@ int launch_decode(const void* q, int64_t ldq, const void* kc, const void* vc, co
   const int g_tiles = (G + GT - 1) / GT;
   dim3 grid(num_splits, hkv * g_tiles, B);
   const float scale_log2 = scale * 1.4426950408889634f;
-  static bool configured = false;
-  if (!configured) {
-    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(attn_decode_kernel<T, D, GT, U>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          kRingBytes(U)));
-    configured = true;
-  }
+  static PerDeviceSmem configured;  // per device: the attribute does not carry over to a second GPU of the process
+  LLMSS_CHECK_CUDA(configured.ensure(attn_decode_kernel<T, D, GT, U>, kRingBytes(U)));
   attn_decode_kernel<T, D, GT, U><<<grid, kThreads, kRingBytes(U), stream>>>(
       (const T*)q, ldq, (const T*)kc, (const T*)vc, bt, max_blocks, seq_lens, (T*)out, ldo, part_o, part_ml, hq, hkv,
       block_size, scale_log2, num_splits);
@@ -369,6 +365,7 @@ LLMSS_API int llmss_attn_decode(const void* q, int64_t ldq, const void* k_cache,
                                 const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
                                 float* scratch, int B, int hq, int hkv, int d, int block_size, float scale,
                                 int num_splits, int dtype, cudaStream_t stream) {
+  LLMSS_REQUIRE(hq > 0 && hkv > 0, "attn_decode: head counts must be positive (hq=%d hkv=%d)", hq, hkv);
   LLMSS_REQUIRE(hq % hkv == 0, "attn_decode: hq=%d not a multiple of hkv=%d", hq, hkv);
   LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_decode: head_dim=%d unsupported (64/128/256)", d);
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "attn_decode: dtype must be f16/bf16");
@@ -453,8 +450,8 @@ LLMSS_API int llmss_attn_decode_static(const void* q, int64_t ldq, const void* k
                                        const int* block_tables, int max_blocks, const int* seq_lens, void* out,
                                        int64_t ldo, int B, int hq, int hkv, int d, int block_size, float scale,
                                        int num_splits, int dtype, cudaStream_t stream) {
-  LLMSS_REQUIRE(B >= 0 && hq > 0 && d > 0 && num_splits >= 1, "attn_decode_static: bad sizes B=%d hq=%d d=%d splits=%d",
-                B, hq, d, num_splits);
+  LLMSS_REQUIRE(B >= 0 && hq > 0 && hkv > 0 && d > 0 && num_splits >= 1,
+                "attn_decode_static: bad sizes B=%d hq=%d hkv=%d d=%d splits=%d", B, hq, hkv, d, num_splits);
   const int64_t need = llmss_attn_decode_scratch_floats(B, hq, d, num_splits);
   LLMSS_REQUIRE(need <= (int64_t)kStaticScratchFloats,
                 "attn_decode_static: B=%d x hq=%d x splits=%d x (d=%d + 2) = %lld floats of scratch exceed the built-in "

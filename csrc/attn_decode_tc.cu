@@ -739,12 +739,9 @@ int plan_stages(int q_alloc_rows, int d, int* smem_bytes) {
 template <typename T, int D, int R>
 int launch_decode_tc(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const DArgs& a, int smem,
                      cudaStream_t stream) {
-  static int configured = 0;
+  static PerDeviceSmem configured;
   auto kern = attn_decode_tc_kernel<T, D, R>;
-  if (configured < smem) {
-    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = smem;
-  }
+  LLMSS_CHECK_CUDA(configured.ensure(kern, smem));
   const int grid = (a.balanced || a.n_items >= sm_count()) ? sm_count() : a.n_items;
   LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, tq, tk, tv, a));
   return 0;
@@ -791,6 +788,7 @@ LLMSS_API int llmss_attn_decode_tc(const void* q, int64_t ldq, const void* k_cac
                                    int num_blocks, float scale, int num_splits, int dtype, cudaStream_t stream) {
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "attn_decode_tc: dtype must be f16/bf16");
   LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_decode_tc: head_dim=%d unsupported", d);
+  LLMSS_REQUIRE(hq > 0 && hkv > 0, "attn_decode_tc: head counts must be positive (hq=%d hkv=%d)", hq, hkv);
   LLMSS_REQUIRE(hq % hkv == 0 && hq / hkv <= 128, "attn_decode_tc: bad head grouping hq=%d hkv=%d", hq, hkv);
   LLMSS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64, "attn_decode_tc: block_size must be 16/32/64");
   LLMSS_REQUIRE(num_splits >= 0 && (num_splits == 1 || scratch != nullptr), "attn_decode_tc: scratch required for splits");

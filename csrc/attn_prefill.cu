@@ -383,12 +383,9 @@ PFN_encodeTiled get_encode() {
 template <typename T, int D>
 int launch_prefill(const CUtensorMap& tm, const PArgs& a, int num_seqs, int max_seqlen, cudaStream_t stream) {
   using C = PCfg<D>;
-  static bool configured = false;
+  static PerDeviceSmem configured;
   auto kern = attn_prefill_kernel<T, D>;
-  if (!configured) {
-    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
   dim3 grid((max_seqlen + BM - 1) / BM, a.hq, num_seqs);
   LLMSS_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), (size_t)C::SMEM_BYTES, stream, tm, a));
   return 0;
@@ -404,6 +401,7 @@ LLMSS_API int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int6
                                  cudaStream_t stream) {
   LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "attn_prefill: dtype must be f16/bf16");
   LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_prefill: head_dim=%d unsupported (64/128/256)", d);
+  LLMSS_REQUIRE(hq > 0 && hkv > 0, "attn_prefill: head counts must be positive (hq=%d hkv=%d)", hq, hkv);
   LLMSS_REQUIRE(hq % hkv == 0, "attn_prefill: hq=%d not a multiple of hkv=%d", hq, hkv);
   LLMSS_REQUIRE(ldq == ldk && ldk == ldv, "attn_prefill: q, k, v must share one row stride (packed QKV activation)");
   LLMSS_REQUIRE(ldo % 8 == 0 && ((uintptr_t)out % 16) == 0, "attn_prefill: output must be 16-byte aligned");

@@ -67,6 +67,18 @@ LLMSS_API int llmss_symm_alloc(size_t buf_bytes, size_t lam_bytes, void** ptr) {
   LLMSS_CHECK_CUDA(cudaDeviceSynchronize());
   return 0;
 }
+// Same initial state for a region that was created elsewhere (vmm.cu: cuMemCreate + map).
+LLMSS_API int llmss_symm_init_region(void* ptr, size_t buf_bytes, size_t lam_bytes) {
+  const size_t bytes = kSymmDataOffset + 2 * lam_bytes + 2 * buf_bytes;
+  LLMSS_REQUIRE(lam_bytes % 16 == 0 && buf_bytes % 16 == 0, "symm_init_region: sizes must be multiples of 16");
+  LLMSS_CHECK_CUDA(cudaMemset(ptr, 0, bytes));
+  if (lam_bytes > 0) {
+    fill_u32_kernel<<<256, 256>>>(reinterpret_cast<uint32_t*>((char*)ptr + kSymmDataOffset), 2 * lam_bytes / 4, kLamSentinel);
+    LLMSS_CHECK_CUDA(cudaGetLastError());
+  }
+  LLMSS_CHECK_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
 LLMSS_API int llmss_symm_free(void* ptr) {
   LLMSS_CHECK_CUDA(cudaFree(ptr));
   return 0;
@@ -94,13 +106,22 @@ LLMSS_API size_t llmss_symm_region_bytes(size_t buf_bytes, size_t lam_bytes) {
 
 // Build the by-value descriptor the kernels take.  `peer_bases[r]` is the mapping of rank
 // r's region in this process (peer_bases[rank] = the local allocation).
+// `mc_base`: the NVLS multicast mapping of the region (vmm.cu), or null when the heap is P2P-only.
+LLMSS_API int llmss_symm_create2(int rank, int nranks, void* const* peer_bases, void* mc_base, size_t buf_bytes,
+                                  size_t lam_bytes, SymmWs** out);
 LLMSS_API int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_bytes, size_t lam_bytes,
                                  SymmWs** out) {
+  return llmss_symm_create2(rank, nranks, peer_bases, nullptr, buf_bytes, lam_bytes, out);
+}
+LLMSS_API int llmss_symm_has_multicast(SymmWs* ws) { return (ws != nullptr && ws->mc_base != nullptr) ? 1 : 0; }
+LLMSS_API int llmss_symm_create2(int rank, int nranks, void* const* peer_bases, void* mc_base, size_t buf_bytes,
+                                  size_t lam_bytes, SymmWs** out) {
   LLMSS_REQUIRE(nranks >= 1 && nranks <= kSymmMaxRanks, "symm_create: nranks=%d unsupported (max %d)", nranks,
                 kSymmMaxRanks);
   SymmWs* ws = new SymmWs();
   memset(ws, 0, sizeof(*ws));
   for (int r = 0; r < nranks; ++r) ws->peer_base[r] = (char*)peer_bases[r];
+  ws->mc_base = (char*)mc_base;
   ws->rank = rank;
   ws->nranks = nranks;
   ws->buf_bytes = buf_bytes;
@@ -261,6 +282,124 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(SymmWs ws, 
   symm_finish(ws, e);
 }
 
+
+// ---- NVLS all-reduce: reduce-scatter and all-gather both happen inside the NVSwitch.
+// Every rank stages its input in its own bulk buffer (local stores), raises one multicast flag, then
+// reduces 1/t of each CTA's range with multimem.ld_reduce (the switch reads the t copies and returns
+// their sum: fp32 accumulation, one rounding) and broadcasts the result with a multicast store.
+// Per-GPU NVLink traffic: (t-1)/t * bytes out + bytes/t in for the reduction, bytes/t out + (t-1)/t in
+// for the broadcast -- a t-th of the one-shot push, half of the P2P two-shot -- and only two one-way
+// trips plus one round trip of latency.  LAM: results travel as self-validating vectors through the
+// Lamport area (no second flag / fence); otherwise through the bulk area behind a second flag.
+template <typename T, bool LAM>
+__global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(SymmWs ws, const uint4* __restrict__ in,
+                                                                  uint4* __restrict__ out, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
+  constexpr int EB = std::is_same<T, float>::value ? 4 : 2;
+  const uint32_t e = *ws.epoch + 1;
+  const int par = e & 1;
+  const int n = ws.nranks;
+  const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
+  const int64_t v0 = min(nvec, (int64_t)blockIdx.x * per_cta), v1 = min(nvec, v0 + per_cta);
+  uint4* part = symm_buf<uint4>(ws, ws.rank, par);
+  constexpr int U = 4;
+  for (int64_t vb = v0 + threadIdx.x; vb < v1; vb += (int64_t)kThreads * U) {
+    uint4 val[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (vb + (int64_t)u * kThreads < v1) val[u] = in[vb + (int64_t)u * kThreads];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (vb + (int64_t)u * kThreads < v1) part[vb + (int64_t)u * kThreads] = val[u];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    mc_st_release_u32(symm_mc_flag(ws, 0, blockIdx.x) + ws.rank, e);  // one store, seen by every rank
+  }
+  if (threadIdx.x < n) wait_flag_ge(symm_flag(ws, ws.rank, 0, blockIdx.x) + threadIdx.x, e, 5);
+  __syncthreads();
+
+  const int64_t sub = (v1 - v0 + n - 1) / n;
+  const int64_t b0 = min(v1, v0 + ws.rank * sub), b1 = min(v1, b0 + sub);
+  const uint4* mc_part = symm_mc_buf<uint4>(ws, par);
+  uint4* mc_res = LAM ? symm_mc_lam<uint4>(ws, par) : symm_mc_buf<uint4>(ws, par) + nvec;
+  for (int64_t vb = b0 + threadIdx.x; vb < b1; vb += (int64_t)kThreads * U) {
+    uint4 val[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (vb + (int64_t)u * kThreads < b1) val[u] = mc_ld_reduce<T>(mc_part + vb + (int64_t)u * kThreads);
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (vb + (int64_t)u * kThreads < b1) mc_st_v4(mc_res + vb + (int64_t)u * kThreads, LAM ? lam_sanitize<EB>(val[u]) : val[u]);
+  }
+  if constexpr (LAM) {
+    uint4* mine = symm_lam<uint4>(ws, ws.rank, par);
+    for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) out[v] = lam_take(mine + v, 6);
+  } else {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      mc_st_release_u32(symm_mc_flag(ws, 1, blockIdx.x) + ws.rank, e);
+    }
+    if (threadIdx.x < n) wait_flag_ge(symm_flag(ws, ws.rank, 1, blockIdx.x) + threadIdx.x, e, 7);
+    __syncthreads();
+    const uint4* res = symm_buf<uint4>(ws, ws.rank, par) + nvec;
+    for (int64_t vb = v0 + threadIdx.x; vb < v1; vb += (int64_t)kThreads * U) {
+      uint4 val[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (vb + (int64_t)u * kThreads < v1) val[u] = ld_cg_v4(res + vb + (int64_t)u * kThreads);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (vb + (int64_t)u * kThreads < v1) out[vb + (int64_t)u * kThreads] = val[u];
+    }
+  }
+  symm_finish(ws, e);
+}
+
+// ---- two-shot all-reduce on self-validating vectors (no flags, no fences): reduce-scatter by peer stores into the
+// owner's Lamport inbox, owner sums in rank order and broadcasts (one multicast store through the switch when the
+// heap is multicast-bound).  Two one-way trips, ~1 x the message per GPU on the wire: the mid-size regime
+// (>= 4 ranks, ~100 KB .. a few MB) between the one-shot push and the bandwidth kernels.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) allreduce_twoshot_lam_kernel(SymmWs ws, const uint4* __restrict__ in,
+                                                                         uint4* __restrict__ out, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
+  constexpr int EB = std::is_same<T, float>::value ? 4 : 2;
+  const uint32_t e = *ws.epoch + 1;
+  const int par = e & 1;
+  const int n = ws.nranks, me = ws.rank;
+  const int64_t per_cta = (nvec + gridDim.x - 1) / gridDim.x;
+  const int64_t v0 = min(nvec, (int64_t)blockIdx.x * per_cta), v1 = min(nvec, v0 + per_cta);
+  const int64_t sub = max((int64_t)1, (v1 - v0 + n - 1) / n);
+  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads)
+    symm_lam<uint4>(ws, (int)((v - v0) / sub), par)[(int64_t)me * nvec + v] = lam_sanitize<EB>(in[v]);
+  uint4* mine = symm_lam<uint4>(ws, me, par);
+  const int64_t b0 = min(v1, v0 + me * sub), b1 = min(v1, b0 + sub);
+  for (int64_t v = b0 + threadIdx.x; v < b1; v += kThreads) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int r = 0; r < n; ++r) accum8<T>(acc, lam_take(mine + (int64_t)r * nvec + v, 8));
+    uint4 o;
+    if constexpr (std::is_same<T, float>::value) {
+      o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+    } else {
+      o = pack8<T>(acc);
+    }
+    o = lam_sanitize<EB>(o);
+    if (ws.mc_base != nullptr) {
+      mc_st_v4(symm_mc_lam<uint4>(ws, par) + (int64_t)n * nvec + v, o);
+    } else {
+#pragma unroll 1
+      for (int p = 0; p < n; ++p) symm_lam<uint4>(ws, (me + p) % n, par)[(int64_t)n * nvec + v] = o;
+    }
+  }
+  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) out[v] = lam_take(mine + (int64_t)n * nvec + v, 9);
+  symm_finish(ws, e);
+}
+
 // ---- all-gather: out[r] = rank r's input (used for the vocab-parallel logits, reference N3)
 // Input: [rows][vpr] 16-byte vectors (contiguous).  Output: [rows][nranks * vpr], rank r's block at column
 // r * vpr -- i.e. the concatenation along the last dimension, written in place (rows = 1 gives the plain
@@ -287,6 +426,10 @@ __global__ void __launch_bounds__(kThreads) allgather_kernel(SymmWs ws, const ui
       const int64_t v = vb + (int64_t)u * kThreads;
       if (v >= v1) continue;
       out[(v / vpr) * pitch + (int64_t)ws.rank * vpr + v % vpr] = val[u];
+      if (ws.mc_base != nullptr) {  // NVLS: one store, replicated by the switch into every rank's buffer
+        mc_st_v4(symm_mc_buf<uint4>(ws, par) + (int64_t)ws.rank * nvec + v, val[u]);
+        continue;
+      }
 #pragma unroll 1
       for (int p = 1; p < ws.nranks; ++p) {
         const int peer = (ws.rank + p) % ws.nranks;
@@ -332,7 +475,30 @@ int pick_grid(int64_t nvec, int max_ctas) {
 
 }  // namespace
 
-// algo: 0 = auto, 1 = one-shot, 2 = two-shot.  `n` = element count.
+// Message size (bytes) from which the automatic choice prefers the in-switch (NVLS) reduction over the one-shot
+// push; LLMSS_NVLS_MIN_BYTES overrides it, LLMSS_NVLS=0 disables the multicast paths altogether.
+int64_t llmss_nvls_min_bytes() {
+  static int64_t v = -1;
+  if (v < 0) {
+    const char* off = getenv("LLMSS_NVLS");
+    const char* e = getenv("LLMSS_NVLS_MIN_BYTES");
+    if (off != nullptr && off[0] == '0') v = INT64_MAX;
+    else v = (e != nullptr) ? atoll(e) : (int64_t)(4 << 20);
+  }
+  return v;
+}
+
+int64_t llmss_twoshot_min_bytes() {
+  static int64_t v = -1;
+  if (v < 0) {
+    const char* e = getenv("LLMSS_TWOSHOT_MIN_BYTES");
+    v = (e != nullptr) ? atoll(e) : (int64_t)(128 << 10);
+  }
+  return v;
+}
+
+// algo: 0 = auto, 1 = one-shot, 2 = two-shot (flags), 3 = NVLS (multimem reduce + broadcast), 4 = two-shot on Lamport
+// vectors (+ multicast broadcast).  `n` = element count.
 LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, int dtype, int algo,
                               cudaStream_t stream) {
   const int esz = (dtype == LLMSS_F32) ? 4 : 2;
@@ -344,10 +510,44 @@ LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, 
     if (in != out) LLMSS_CHECK_CUDA(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice, stream));
     return 0;
   }
+  const bool nvls_can_lam = (size_t)bytes <= ws->buf_bytes && (size_t)bytes <= ws->lam_bytes;
+  const bool nvls_can_flag = (size_t)bytes * 2 <= ws->buf_bytes;
+  const bool nvls_fits = ws->mc_base != nullptr && (nvls_can_lam || nvls_can_flag);
+  const bool two_lam_fits = (size_t)bytes * (ws->nranks + 1) <= ws->lam_bytes;
+  if (algo == 0 && nvls_fits && bytes >= llmss_nvls_min_bytes()) algo = 3;
+  if (algo == 0 && two_lam_fits && ws->nranks >= 4 && bytes >= llmss_twoshot_min_bytes()) algo = 4;
+  if (algo == 4) {
+    LLMSS_REQUIRE(two_lam_fits, "allreduce: message of %lld bytes needs %lld bytes of Lamport buffer (have %zu)",
+                  (long long)bytes, (long long)bytes * (ws->nranks + 1), ws->lam_bytes);
+    const int grid = pick_grid(nvec, 128);
+    SymmWs w = *ws;
+    if (dtype == LLMSS_F16) LLMSS_CHECK_CUDA(launch_pdl(allreduce_twoshot_lam_kernel<__half>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    else if (dtype == LLMSS_BF16) LLMSS_CHECK_CUDA(launch_pdl(allreduce_twoshot_lam_kernel<__nv_bfloat16>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    else LLMSS_CHECK_CUDA(launch_pdl(allreduce_twoshot_lam_kernel<float>, dim3(grid), dim3(kThreads), 0, stream, w, (const uint4*)in, (uint4*)out, nvec));
+    LLMSS_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (algo == 0)
     algo = ((bytes <= (int64_t)(1 << 20) && (size_t)(bytes * ws->nranks) <= ws->lam_bytes) || nvec % ws->nranks != 0) ? 1 : 2;
   if (algo == 2 && nvec % ws->nranks != 0) algo = 1;
-  if (algo == 0) {}
+  if (algo == 3) {
+    LLMSS_REQUIRE(ws->mc_base != nullptr, "allreduce: the NVLS algorithm needs a multicast-bound workspace");
+    LLMSS_REQUIRE(nvls_fits, "allreduce: message of %lld bytes does not fit the workspace for the NVLS algorithm", (long long)bytes);
+    const bool lam = nvls_can_lam && (bytes <= (int64_t)(4 << 20) || !nvls_can_flag);
+    const int grid = pick_grid((nvec + 3) / 4, 144);
+    SymmWs w = *ws;
+#define LLMSS_NVLS_AR(T_)                                                                                              \
+    LLMSS_CHECK_CUDA(lam ? launch_pdl(allreduce_nvls_kernel<T_, true>, dim3(grid), dim3(kThreads), 0, stream, w,        \
+                                      (const uint4*)in, (uint4*)out, nvec)                                             \
+                         : launch_pdl(allreduce_nvls_kernel<T_, false>, dim3(grid), dim3(kThreads), 0, stream, w,       \
+                                      (const uint4*)in, (uint4*)out, nvec))
+    if (dtype == LLMSS_F16) LLMSS_NVLS_AR(__half);
+    else if (dtype == LLMSS_BF16) LLMSS_NVLS_AR(__nv_bfloat16);
+    else LLMSS_NVLS_AR(float);
+#undef LLMSS_NVLS_AR
+    LLMSS_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int64_t need = (algo == 1) ? bytes * ws->nranks : bytes * 2;
   const size_t have = (algo == 1) ? ws->lam_bytes : ws->buf_bytes;
   LLMSS_REQUIRE((size_t)need <= have, "allreduce: message of %lld bytes needs %lld bytes of workspace (have %zu)",

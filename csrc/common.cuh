@@ -41,6 +41,24 @@ void llmss_set_error(const char* fmt, ...);
     }                                                                                  \
   } while (0)
 
+// cudaFuncSetAttribute applies to the CURRENT device only: a process that drives several GPUs has to repeat it on
+// each.  One of these per kernel instantiation remembers, per device ordinal, the dynamic shared memory size
+// already granted.
+struct PerDeviceSmem {
+  int granted[64] = {0};
+  template <typename K>
+  cudaError_t ensure(K kern, int bytes) {
+    int d = 0;
+    cudaError_t e = cudaGetDevice(&d);
+    if (e != cudaSuccess) return e;
+    d &= 63;
+    if (granted[d] >= bytes) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) granted[d] = bytes;
+    return e;
+  }
+};
+
 // ---------------------------------------------------------------- dtype helpers
 template <typename T> struct Vec2;
 template <> struct Vec2<__half> { using type = __half2; };

@@ -37,6 +37,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+int64_t llmss_nvls_min_bytes();     // comm.cu
+int64_t llmss_twoshot_min_bytes();  // comm.cu
+
 namespace {
 
 constexpr int BM = 128;  // output features per tile (UMMA M)
@@ -419,6 +422,10 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
       for (int64_t v = (int64_t)blockIdx.x * 128 + epi_tid; v < nvec; v += (int64_t)gridDim.x * 128) {
         const int64_t r = v / kvec, c = v % kvec;
         const uint4 val = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(a.ag_src) + r * a.ag_ld + c * 8);
+        if (a.ws.mc_base != nullptr) {  // NVLS: one multicast store lands in every rank's gathered buffer
+          mc_st_v4(symm_mc_buf<uint4>(a.ws, par) + base + v, val);
+          continue;
+        }
 #pragma unroll 1
         for (int p = 0; p < a.ws.nranks; ++p) {
           const int peer = (a.ws.rank + p) % a.ws.nranks;
@@ -742,7 +749,150 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
     const int par = epoch & 1;
     const uint32_t stage_u32 = smem_u32(staging);
-    const int n_pass = a.ar ? 2 : 1;
+    if (a.ar == 3) {
+      // ---- NVLS all-reduce (K1, in-switch): (A) the reduced bf16/fp16 slice goes to this rank's OWN bulk buffer
+      // (local stores, nothing on the wire) and one multicast flag store tells every rank that this CTA slot
+      // of this rank is staged; (B) rank q sums the q-th share of the slot with multimem.ld_reduce -- the
+      // switch reads the t copies and adds them in fp32 -- and broadcasts the result with one multicast store
+      // into every rank's Lamport area; (C) each rank takes its slice from its own Lamport area (the vector is
+      // its own arrival flag), adds bias / residual and stores.  Per rank and layer the wire carries ~2 x the
+      // message instead of (t-1) x, and every rank ends up with the same bits (the owner's sum).
+      uint8_t* part = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
+      const size_t tile_off = (size_t)tile * NG * BM * 16;
+#pragma unroll 1
+      for (int it = epi_tid; it < my_items; it += 128) {
+        const int item = r * per + it;
+        const uint32_t off = (uint32_t)((((item / BM) * 2) * BM + item % BM) * 16);
+        float v8[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v8[j] = 0.f;
+        float4 lo[8], hi[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < S) {
+            const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
+            lo[q] = ld_dsmem_f4(base);
+            hi[q] = ld_dsmem_f4(base + BM * 16);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < S) {
+            v8[0] += lo[q].x; v8[1] += lo[q].y; v8[2] += lo[q].z; v8[3] += lo[q].w;
+            v8[4] += hi[q].x; v8[5] += hi[q].y; v8[6] += hi[q].z; v8[7] += hi[q].w;
+          }
+        }
+        *reinterpret_cast<uint4*>(part + tile_off + (size_t)item * 16) = pack8<T>(v8);
+      }
+      epi_bar();
+      if (epi_tid == 0) {
+        __threadfence_system();
+        mc_st_release_u32(symm_mc_flag(a.ws, 0, blockIdx.x) + a.ws.rank, epoch);
+      }
+      if (epi_tid < a.ws.nranks) wait_flag_ge(symm_flag(a.ws, a.ws.rank, 0, blockIdx.x) + epi_tid, epoch, 44);
+      epi_bar();
+      if (threadIdx.x == 64) LLMSS_STAMP(2);
+      {
+        const int sub = (my_items + a.ws.nranks - 1) / a.ws.nranks;
+        const uint8_t* mc_part = symm_mc_buf<uint8_t>(a.ws, par);
+        uint8_t* mc_res = symm_mc_lam<uint8_t>(a.ws, par);
+#pragma unroll 1
+        for (int i = epi_tid; i < sub; i += 128) {
+          const int li = a.ws.rank * sub + i;
+          if (li < my_items) {
+            const size_t xoff = tile_off + (size_t)(r * per + li) * 16;
+            mc_st_v4(mc_res + xoff, lam_sanitize<2>(mc_ld_reduce<T>(mc_part + xoff)));
+          }
+        }
+      }
+      uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
+#pragma unroll 1
+      for (int it = epi_tid; it < my_items; it += 128) {
+        const int item = r * per + it;
+        const int cg = item / BM, f = item % BM;
+        const int n = tn * BM + f;
+        float v[1][8], rv[1][8];
+        epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the wait
+        unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + tile_off + (size_t)item * 16), 45), v[0]);
+        const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+        store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+      }
+    }
+    if (a.ar == 4) {
+      // ---- two-shot all-reduce without flags (K1 for t >= 4): (A) every vector of this CTA's slice goes to the ONE
+      // rank that owns it (1/t of the slice each) as a self-validating Lamport vector; (B) the owner sums the t
+      // contributions in rank order and broadcasts the result -- one multicast store through the NVSwitch when
+      // the heap is multicast-bound, else t peer stores; (C) every rank takes its slice of results, adds bias /
+      // residual and stores.  (t-1)/t + 1/t of the message leaves each GPU instead of (t-1) x, both hops are
+      // validated by the data itself (no flag, no fence), and all ranks hold the owner's bits.
+      const int t = a.ws.nranks, me = a.ws.rank;
+      const int sub = (my_items + t - 1) / t;
+      const size_t tile_off = (size_t)tile * NG * BM * 16;
+#pragma unroll 1
+      for (int it = epi_tid; it < my_items; it += 128) {
+        const int item = r * per + it;
+        const uint32_t off = (uint32_t)((((item / BM) * 2) * BM + item % BM) * 16);
+        float v8[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v8[j] = 0.f;
+        float4 lo[8], hi[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < S) {
+            const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
+            lo[q] = ld_dsmem_f4(base);
+            hi[q] = ld_dsmem_f4(base + BM * 16);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < S) {
+            v8[0] += lo[q].x; v8[1] += lo[q].y; v8[2] += lo[q].z; v8[3] += lo[q].w;
+            v8[4] += hi[q].x; v8[5] += hi[q].y; v8[6] += hi[q].z; v8[7] += hi[q].w;
+          }
+        }
+        *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, it / sub, par) + (size_t)me * ar_slot_bytes + tile_off +
+                                  (size_t)item * 16) = lam_sanitize<2>(pack8<T>(v8));
+      }
+      if (threadIdx.x == 64) LLMSS_STAMP(2);
+      uint8_t* mine = symm_lam<uint8_t>(a.ws, me, par);
+      const size_t res_off = (size_t)t * ar_slot_bytes;
+#pragma unroll 1
+      for (int i = epi_tid; i < sub; i += 128) {
+        const int li = me * sub + i;
+        if (li >= my_items) break;
+        const size_t xoff = tile_off + (size_t)(r * per + li) * 16;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int q = 0; q < t; ++q) {  // rank order
+          float t8[8];
+          unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)q * ar_slot_bytes + xoff), 46), t8);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += t8[j];
+        }
+        const uint4 vec = lam_sanitize<2>(pack8<T>(acc));
+        if (a.ws.mc_base != nullptr) {
+          mc_st_v4(symm_mc_lam<uint8_t>(a.ws, par) + res_off + xoff, vec);
+        } else {
+#pragma unroll 1
+          for (int p = 0; p < t; ++p)
+            *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, (me + p) % t, par) + res_off + xoff) = vec;
+        }
+      }
+#pragma unroll 1
+      for (int it = epi_tid; it < my_items; it += 128) {
+        const int item = r * per + it;
+        const int cg = item / BM, f = item % BM;
+        const int n = tn * BM + f;
+        float v[1][8], rv[1][8];
+        epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the wait
+        unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + res_off + tile_off + (size_t)item * 16), 47), v[0]);
+        const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+        store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+      }
+    }
+    const int n_pass = a.ar >= 3 ? 0 : (a.ar ? 2 : 1);
 #pragma unroll 1
     for (int pass = 0; pass < n_pass; ++pass) {
 #pragma unroll 1
@@ -860,12 +1010,9 @@ int num_sms() {
 template <typename T, int BN>
 int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
   using C = Cfg<BN>;
-  static bool configured = false;
+  static PerDeviceSmem configured;
   auto kern = gemm_swapab_kernel<T, BN>;
-  if (!configured) {
-    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
   LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, a));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -875,12 +1022,9 @@ template <typename T, int BN>
 int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int tiles, int split,
                    cudaStream_t stream) {
   using C = Cfg<BN>;
-  static bool configured = false;
+  static PerDeviceSmem configured;
   auto kern = gemm_cluster_kernel<T, BN>;
-  if (!configured) {
-    LLMSS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(tiles * split);
@@ -1056,7 +1200,9 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   LLMSS_REQUIRE(!gated || (N % 2 == 0), "gemm: gated epilogue needs even N");
   LLMSS_REQUIRE(!(gated && out_f32), "gemm: gated epilogue with fp32 output is not supported");
   if (ws == nullptr || ws->nranks <= 1) collective = 0;
-  const bool ar = collective == 1, rs = collective == 2, ag = collective == 3;
+  // collective 4 / 5 / 6 pin the all-reduce algorithm: 4 = NVLS in-switch reduction, 5 = one-shot Lamport push,
+  // 6 = two-shot Lamport (reduce-scatter over peer stores + multicast broadcast)
+  const bool ar = collective == 1 || (collective >= 4 && collective <= 6), rs = collective == 2, ag = collective == 3;
   LLMSS_REQUIRE(!((ar || rs) && (gated || act != LLMSS_ACT_NONE || out_f32)),
                 "gemm: fused all-reduce / reduce-scatter support bias/residual epilogues only");
   llmss_gemm_plan p;
@@ -1086,10 +1232,24 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   const bool aligned = p.split == 0 && p.tiles >= aligned_min * p.grid;    // many tiles per CTA: plain data-parallel
   const bool need_sk = p.split == 0 && !aligned && (p.tiles % p.grid) != 0;  // some CTA range cuts through a tile
   LLMSS_REQUIRE(!need_sk || (sk_ws != nullptr && sk_counters != nullptr), "gemm: stream-K workspace required for this shape");
+  int ar_mode = 1;  // kernel-side GemmArgs::ar: 1 one-shot push, 3 NVLS (flag + multimem.ld_reduce), 4 two-shot Lamport
   if (ar) {
     LLMSS_REQUIRE(p.tiles * (p.split > 0 ? p.split : 1) <= kSymmMaxSlots,
                   "gemm: %d tiles exceed the %d flag slots of the symmetric workspace", p.tiles, kSymmMaxSlots);
-    LLMSS_REQUIRE((size_t)p.ar_bytes <= ws->lam_bytes, "gemm: fused all-reduce needs %lld bytes of Lamport buffer (have %zu)",
+    // in-switch reduction: cluster kernel only (one CTA slot per flag), message staged in the bulk area and
+    // returned through one Lamport slot set; chosen from llmss_nvls_min_bytes() of padded message upwards
+    const size_t msg = (size_t)p.tiles * BM * p.bn * 2;
+    const bool nvls_ok = ws->mc_base != nullptr && p.split > 0 && msg <= ws->buf_bytes && msg <= ws->lam_bytes;
+    const bool two_ok = p.split > 0 && (size_t)(ws->nranks + 1) * msg <= ws->lam_bytes;
+    LLMSS_REQUIRE(collective != 4 || nvls_ok, "gemm: NVLS all-reduce unavailable for this shape / workspace (multicast %s, split %d)",
+                  ws->mc_base != nullptr ? "bound" : "not bound", p.split);
+    LLMSS_REQUIRE(collective != 6 || two_ok, "gemm: two-shot all-reduce epilogue unavailable for this shape / workspace (split %d)", p.split);
+    // automatic choice: the one-shot push is one hop but (t-1) x the bytes, the two-shot exchange two hops and ~1 x:
+    // from 4 ranks and LLMSS_TWOSHOT_MIN_BYTES upwards the two-shot form wins (profiles/bench_gemm_ar.md)
+    if (collective == 4) ar_mode = 3;
+    else if (collective == 6) ar_mode = 4;
+    else if (collective == 1 && two_ok && ws->nranks >= 4 && (int64_t)M * N * 2 >= llmss_twoshot_min_bytes()) ar_mode = 4;
+    LLMSS_REQUIRE(ar_mode != 1 || (size_t)p.ar_bytes <= ws->lam_bytes, "gemm: fused all-reduce needs %lld bytes of Lamport buffer (have %zu)",
                   (long long)p.ar_bytes, ws->lam_bytes);
   }
   if (rs) {
@@ -1130,7 +1290,7 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   a.aligned = aligned ? 1 : 0;
   a.epi = gated ? EPI_GATED : (out_f32 ? EPI_F32 : (act != LLMSS_ACT_NONE ? EPI_ACT : EPI_PLAIN));
   a.sk_ws = sk_ws; a.sk_counters = sk_counters;
-  a.ar = ar ? 1 : (rs ? 2 : 0);
+  a.ar = ar ? ar_mode : (rs ? 2 : 0);
   a.rs_rows = rs_rows;
   a.ag = ag ? 1 : 0;
   a.ag_src = x;

@@ -27,8 +27,11 @@ __device__ __forceinline__ uint32_t fmix32(uint32_t x) {
   x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
   return x;
 }
-__device__ __forceinline__ float rng_uniform(uint32_t seed, uint32_t step, uint32_t row) {
-  uint32_t x = row * 0x9E3779B1u + step * 0x85EBCA77u + seed * 0xC2B2AE3Du;
+// Keyed on the request's (seed, step) only -- not on the batch row -- so a request draws the same numbers
+// whichever slot of the running batch it occupies (the engine derives the seed from the request id when the
+// caller gives none).
+__device__ __forceinline__ float rng_uniform(uint32_t seed, uint32_t step) {
+  uint32_t x = 0x9E3779B1u + step * 0x85EBCA77u + seed * 0xC2B2AE3Du;
   x = fmix32(fmix32(x));
   return (float)(x >> 8) * (1.0f / 16777216.0f);
 }
@@ -89,10 +92,11 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(
     }
     if (tid == 0) { s_f = b.v; s_pick = b.i; }
   }
+  // every thread reads the counter before the barrier, thread 0 advances it after: no thread can see step + 1
+  const uint32_t seed = rng_state[2 * row], step = rng_state[2 * row + 1];
   __syncthreads();
   const float xmax = s_f;
   const int amax = s_pick;
-  const uint32_t seed = rng_state[2 * row], step = rng_state[2 * row + 1];
   if (tid == 0) rng_state[2 * row + 1] = step + 1;
   if (greedy[row]) {
     if (tid == 0) {
@@ -105,7 +109,7 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(
   const float inv_t = 1.0f / temp;
   const float tp = top_p[row];
   int k = top_k[row];
-  const float u01 = rng_uniform(seed, step, (uint32_t)row);
+  const float u01 = rng_uniform(seed, step);
 
   if (k <= 0 && tp >= 1.0f) {
     // ---- plain multinomial over the whole row, inverse CDF in index order
@@ -133,19 +137,29 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(
       red[tid] = wi - w;  // exclusive warp offsets
       if (tid == 31) s_f = wi;
     }
-    if (tid == 0) s_pick = vocab - 1;
+    if (tid == 0) s_count = kThreads;  // lowest thread whose cumulative weight exceeds the target
     __syncthreads();
     const float total = s_f;
     const float target = u01 * total;
-    const float before = red[tid >> 5] + incl - part;
-    if (part > 0.f && target >= before && target < before + part) {
-      float c = before;
-      int pick = i1 - 1;
+    // Gap-free ownership: thread t owns [cum(t-1), cum(t)) with ONE expression for cum (its inclusive prefix), so
+    // neighbouring intervals share their end points exactly; the owner is the lowest thread with target < cum.
+    const float cum = red[tid >> 5] + incl;
+    if (target < cum) atomicMin(&s_count, tid);
+    __syncthreads();
+    if (tid == s_count) {
+      float c = cum - part;
+      int pick = -1, last_pos = -1;
       for (int i = i0; i < i1; ++i) {
-        c += __expf((x[i] - xmax) * inv_t);
+        const float w = __expf((x[i] - xmax) * inv_t);
+        c += w;
+        if (w > 0.f) last_pos = i;
         if (target < c) { pick = i; break; }
       }
-      s_pick = pick;  // exactly one thread's interval contains target
+      // rounding (the walk re-adds the weights in another order than the scan) can leave the target just past
+      // the last element: take the thread's last token of non-zero weight
+      s_pick = pick >= 0 ? pick : (last_pos >= 0 ? last_pos : amax);
+    } else if (tid == 0 && s_count == kThreads) {
+      s_pick = amax;  // target >= total (u01 * total rounded up): any positive-probability token; take the mode
     }
     __syncthreads();
     if (tid == 0) {

@@ -11,6 +11,7 @@ constexpr size_t kSymmDataOffset = kSymmFlagSetBytes * kSymmFlagSets;   // data 
 // Passed to kernels by value (fixed addresses -> graph capturable).
 struct SymmWs {
   char* peer_base[kSymmMaxRanks];  // this process' mapping of every rank's region
+  char* mc_base;                   // NVLS multicast mapping of the same region on all ranks (null: P2P only)
   uint32_t* epoch;                 // device-local: epoch of the last completed call
   uint32_t* ticket;                // device-local: CTAs finished in the current call
   size_t buf_bytes;                // bytes per parity buffer of the flag-synchronised (bulk) area
@@ -73,6 +74,45 @@ __device__ __forceinline__ uint4 lam_take(uint4* slot, int tag) {
   *slot = make_uint4(kLamSentinel, kLamSentinel, kLamSentinel, kLamSentinel);
   return v;
 }
+// ---- NVLS (NVSwitch multicast) accessors: same offsets as symm_buf / symm_lam / symm_flag, but through the
+// multicast mapping: a store lands in every rank's copy, multimem.ld_reduce sums all copies in the switch.
+template <typename V>
+__device__ __forceinline__ V* symm_mc_buf(const SymmWs& ws, int parity) {
+  return reinterpret_cast<V*>(ws.mc_base + kSymmDataOffset + 2 * ws.lam_bytes + (size_t)parity * ws.buf_bytes);
+}
+template <typename V>
+__device__ __forceinline__ V* symm_mc_lam(const SymmWs& ws, int parity) {
+  return reinterpret_cast<V*>(ws.mc_base + kSymmDataOffset + (size_t)parity * ws.lam_bytes);
+}
+__device__ __forceinline__ uint32_t* symm_mc_flag(const SymmWs& ws, int set, int slot) {
+  return reinterpret_cast<uint32_t*>(ws.mc_base + (size_t)set * kSymmFlagSetBytes) + (size_t)slot * kSymmMaxRanks;
+}
+// Sum of the 16-byte vector at the same offset of every rank's copy (8 x 16-bit lanes, fp32 accumulation in
+// the switch, one rounding) or 4 x fp32.
+template <typename T>
+__device__ __forceinline__ uint4 mc_ld_reduce(const void* mc_addr) {
+  uint4 r;
+  if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc_addr) : "memory");
+  } else if constexpr (std::is_same<T, __half>::value) {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc_addr) : "memory");
+  } else {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc_addr) : "memory");
+  }
+  return r;
+}
+// Broadcast store: one instruction, the switch replicates it into every rank's copy.
+__device__ __forceinline__ void mc_st_v4(void* mc_addr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(mc_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void mc_st_release_u32(uint32_t* mc_addr, uint32_t v) {
+  asm volatile("multimem.st.release.sys.global.b32 [%0], %1;" ::"l"(mc_addr), "r"(v) : "memory");
+}
+
 // &flag[set][slot][0] inside rank `rank`'s region; index by source rank.
 __device__ __forceinline__ uint32_t* symm_flag(const SymmWs& ws, int rank, int set, int slot) {
   return reinterpret_cast<uint32_t*>(ws.peer_base[rank] + (size_t)set * kSymmFlagSetBytes) +

@@ -68,6 +68,7 @@ class Engine:
         self.running: List[SeqState] = []
         self.stats: Dict[int, RequestStats] = {}
         self._next_id = 0
+        self.rejected: List[int] = []   # requests that cannot fit the KV cache even alone (reported by step())
         self._dirty = True  # decode batch needs re-binding
 
     # ------------------------------------------------------------------ construction
@@ -120,10 +121,19 @@ class Engine:
             n = min(len(s.prompt), r.max_seq_len - 1)
             if admitted and n > budget:
                 break
+            if not r.fits_at_all(n, s.params.max_new_tokens):
+                # can never run, not even alone in an empty cache: reject instead of blocking the queue for ever
+                self.waiting.pop(0)
+                s.finished = True
+                self.rejected.append(s.seq_id)
+                METRICS.inc("requests_rejected")
+                continue
             if not r.can_admit(n, s.params.max_new_tokens):
                 break
             budget -= n
-            admitted.append(self.waiting.pop(0))
+            s = self.waiting.pop(0)
+            r.reserve(s)
+            admitted.append(s)
         return admitted
 
     def _is_done(self, s: SeqState, tok: int) -> bool:
@@ -142,6 +152,8 @@ class Engine:
         now = time.perf_counter
         outs: List[StepOutput] = []
         new = self._admit()
+        while self.rejected:  # surfaced as finished outputs with token -1 (the servers turn them into errors)
+            outs.append(StepOutput(self.rejected.pop(0), -1, True))
         if new:
             t0 = now()
             toks = self.runner.prefill(new)
@@ -200,6 +212,6 @@ class Engine:
         out: Dict[int, List[int]] = {i: [] for i in ids}
         while self.has_work():
             for o in self.step():
-                if o.request_id in out:
+                if o.request_id in out and o.token >= 0:
                     out[o.request_id].append(o.token)
         return [out[i] for i in ids]

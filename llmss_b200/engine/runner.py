@@ -36,7 +36,7 @@ class SamplingParams:
     temperature: float = 1.0
     top_p: float = 0.95
     top_k: int = 50
-    seed: int = 0
+    seed: Optional[int] = None   # None: derived from the request id (distinct streams per request, same in any slot)
 
     def validate(self):
         assert self.max_new_tokens > 0, "Value of max_new_tokens should be over than 0."
@@ -46,8 +46,21 @@ class SamplingParams:
         return self
 
 
+def request_seed(params: "SamplingParams", seq_id: int) -> int:
+    """31-bit RNG key of a request: the caller's seed if given, else a mix of the request id.  The sampler keys its
+    counter RNG on (this, number of tokens sampled so far) and on nothing else, so a request draws the same
+    tokens whichever batch slot it sits in and whoever shares the batch."""
+    if params.seed is not None:
+        return int(params.seed) & 0x7FFFFFFF
+    x = (int(seq_id) + 1) * 0x9E3779B1 & 0xFFFFFFFF
+    x ^= x >> 16
+    x = x * 0x85EBCA6B & 0xFFFFFFFF
+    x ^= x >> 13
+    return x & 0x7FFFFFFF
+
+
 class SeqState:
-    __slots__ = ("seq_id", "prompt", "output", "blocks", "params", "length", "slot", "finished", "eos")
+    __slots__ = ("seq_id", "prompt", "output", "blocks", "params", "length", "slot", "finished", "eos", "reserved")
 
     def __init__(self, seq_id, prompt, params, eos=None):
         self.seq_id, self.prompt, self.params = seq_id, list(prompt), params
@@ -57,6 +70,7 @@ class SeqState:
         self.slot = -1           # row in the decode batch
         self.finished = False
         self.eos = eos
+        self.reserved = 0        # cache blocks promised to this sequence at admission (worst case)
 
 
 class ModelRunner:
@@ -77,6 +91,7 @@ class ModelRunner:
             num_blocks = 1 + max_batch * self.max_blocks_per_seq
         self.kv = KVCache(self.spec.n_layers, num_blocks, block_size, core.hkv, core.d, self.dtype, self.device)
         self.alloc = BlockAllocator(num_blocks)
+        self._outstanding = 0   # blocks reserved at admission and not yet allocated
         self.cuda = self.device.type == "cuda"
         self.use_graph = self.cuda if use_cuda_graph is None else (use_cuda_graph and self.cuda)
         self.graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}   # (padded batch, vocab-parallel greedy) -> graph
@@ -98,6 +113,13 @@ class ModelRunner:
         self.h_in = torch.zeros(self.n_meta, dtype=torch.int32, pin_memory=pin)
         self.d_in = torch.zeros(self.n_meta, dtype=torch.int32, device=self.device)
         self.h_out = torch.zeros(B, dtype=torch.int32, pin_memory=pin)
+        # The DMA engine reads a pinned source when the copy EXECUTES, not when it is enqueued, and enqueue-only
+        # steps (sync=False) run many steps ahead of the GPU: each step therefore snapshots h_in into the next
+        # buffer of a small ring and copies from there; a buffer is rewritten only after the event recorded behind
+        # its previous copy has completed.
+        self._ring = [torch.zeros(self.n_meta, dtype=torch.int32, pin_memory=pin) for _ in range(4)] if pin else []
+        self._ring_ev = [None] * len(self._ring)
+        self._ring_i = 0
         self.np_in = self.h_in.numpy()
         self.np_out = self.h_out.numpy()
         self.np_tok, self.np_pos = self.np_in[0:B], self.np_in[B:2 * B]
@@ -128,17 +150,35 @@ class ModelRunner:
     def blocks_needed(self, n_tokens: int) -> int:
         return -(-n_tokens // self.block_size)
 
+    def worst_case_blocks(self, prompt_len: int, max_new: int) -> int:
+        return self.blocks_needed(min(prompt_len + max_new, self.max_seq_len))
+
+    def fits_at_all(self, prompt_len: int, max_new: int) -> bool:
+        """Could this request run alone in an empty cache?  (If not it must be rejected, not queued.)"""
+        return self.worst_case_blocks(prompt_len, max_new) <= self.alloc.num_blocks - 1
+
     def can_admit(self, prompt_len: int, max_new: int) -> bool:
-        return self.alloc.num_free >= self.blocks_needed(min(prompt_len + max_new, self.max_seq_len))
+        """Admission reserves the worst case (prompt + max_new tokens): blocks promised to running sequences but
+        not yet allocated are subtracted, so a decode step can never run out of cache pages half-way."""
+        return self.alloc.num_free - self._outstanding >= self.worst_case_blocks(prompt_len, max_new)
+
+    def reserve(self, seq: SeqState):
+        seq.reserved = self.worst_case_blocks(min(len(seq.prompt), self.max_seq_len - 1), seq.params.max_new_tokens)
+        self._outstanding += seq.reserved
 
     def _grow(self, seq: SeqState, total_len: int):
         need = self.blocks_needed(total_len) - len(seq.blocks)
         if need > 0:
             seq.blocks.extend(self.alloc.alloc(need))
+            took = min(need, seq.reserved)
+            seq.reserved -= took
+            self._outstanding -= took
 
     def release(self, seq: SeqState):
         self.alloc.release(seq.blocks)
         seq.blocks = []
+        self._outstanding -= seq.reserved
+        seq.reserved = 0
 
     # ------------------------------------------------------------------ prefill
     @torch.no_grad()
@@ -157,7 +197,7 @@ class ModelRunner:
         temp = torch.tensor([s.params.temperature for s in seqs], dtype=torch.float32, device=dev)
         top_k = torch.tensor([s.params.top_k for s in seqs], dtype=torch.int32, device=dev)
         top_p = torch.tensor([s.params.top_p for s in seqs], dtype=torch.float32, device=dev)
-        rng = torch.tensor([[s.params.seed & 0x7FFFFFFF, 0] for s in seqs], dtype=torch.int32, device=dev)
+        rng = torch.tensor([[request_seed(s.params, s.seq_id), 0] for s in seqs], dtype=torch.int32, device=dev)
         toks = ops.sample(logits, greedy, temp, top_k, top_p, rng, vocab=self.spec.vocab).tolist()
         for s, t in zip(seqs, toks):
             s.length = len(s.prompt)
@@ -191,7 +231,7 @@ class ModelRunner:
             self.h_samp_i[MB + i] = s.params.top_k
             self.h_samp_f[i] = s.params.temperature
             self.h_samp_f[MB + i] = s.params.top_p
-            rng[i, 0] = s.params.seed & 0x7FFFFFFF
+            rng[i, 0] = request_seed(s.params, s.seq_id)
             rng[i, 1] = len(s.output)
             self.np_active[i] = not s.finished
             self.np_len[i] = s.length
@@ -356,12 +396,14 @@ class ModelRunner:
         if self.use_graph and (Bp, self._vp_greedy()) not in self.graphs:
             self.capture(Bp, self._vp_greedy())
         self._fill_step_inputs()
+        src = self._stage()
         if host_tokens:
-            self.d_in.copy_(self.h_in, non_blocking=True)
+            self.d_in.copy_(src, non_blocking=True)
             self.stats["h2d_bytes"] += self.n_meta * 4
         else:
-            self.d_in[MB:].copy_(self.h_in[MB:], non_blocking=True)
+            self.d_in[MB:].copy_(src[MB:], non_blocking=True)
             self.stats["h2d_bytes"] += (self.n_meta - MB) * 4
+        self._staged()
         self._launch_decode(Bp)
         self.stats["decode_steps"] += 1
         self.np_len[self.np_active] += 1
@@ -378,6 +420,26 @@ class ModelRunner:
                 s.length += 1
                 s.output.append(t)
         return toks
+
+    def _stage(self) -> torch.Tensor:
+        """A pinned snapshot of this step's inputs that nobody rewrites until its H2D copy has run."""
+        if not self._ring:
+            return self.h_in
+        i = self._ring_i
+        ev = self._ring_ev[i]
+        if ev is not None:
+            ev.synchronize()
+        self._ring[i].copy_(self.h_in)
+        return self._ring[i]
+
+    def _staged(self):
+        if not self._ring:
+            return
+        ev = self._ring_ev[self._ring_i]
+        if ev is None:
+            ev = self._ring_ev[self._ring_i] = torch.cuda.Event()
+        ev.record()
+        self._ring_i = (self._ring_i + 1) % len(self._ring)
 
     def sync_lengths(self):
         """After a run of ``sync=False`` steps: bring the host-side SeqState lengths up to date."""

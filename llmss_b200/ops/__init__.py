@@ -8,6 +8,7 @@ HF-compat forward with a multi-token query and a non-empty cache); see attention
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -32,6 +33,34 @@ def _warn_once(msg: str):
         logger.warning(msg)
 
 
+_FUSED_PUSH_MAX = int(os.environ.get("LLMSS_FUSED_AR_MAX_PUSH", str(2 << 20)))
+_TWOSHOT_MIN = int(os.environ.get("LLMSS_TWOSHOT_MIN_BYTES", str(128 << 10)))
+_FUSED_TWOSHOT_MAX = int(os.environ.get("LLMSS_FUSED_TWOSHOT_MAX_BYTES", str(8 << 20)))
+
+
+def _fused_ar_mode(cu, symm, M: int, N: int, K: int, esz: int) -> int:
+    """How a row-parallel GEMM on CUDA performs its all-reduce: 0 = plain GEMM followed by the standalone
+    collective, 5 = one-shot Lamport push in the epilogue, 6 = two-shot Lamport exchange in the epilogue
+    (reduce-scatter by peer stores, result broadcast by one NVSwitch multicast store).
+
+    Only the cluster split-K kernel fuses (each CTA owns a slice of one tile); shapes that run on the stream-K
+    kernel measured slower fused than unfused.  The one-shot push is one hop but puts (t-1) x the message on
+    the wire, the two-shot form two hops and ~1 x: from 4 ranks and `LLMSS_TWOSHOT_MIN_BYTES` upwards the
+    latter wins (profiles/bench_gemm_ar.md).  The flag-synchronised in-switch reduction (mode 4,
+    multimem.ld_reduce) costs ~15 us of latency and is left to the standalone collective for prefill sizes."""
+    plan = cu.gemm_plan(M, N, K, symm.nranks)
+    if plan.split <= 0 or plan.tiles > 2048:
+        return 0
+    msg = M * N * esz
+    padded = plan.tiles * 128 * plan.bn * esz
+    if (symm.nranks >= 4 and msg >= _TWOSHOT_MIN and padded <= _FUSED_TWOSHOT_MAX
+            and (symm.nranks + 1) * padded <= symm.lam_bytes):
+        return 6
+    if plan.ar_bytes <= symm.lam_bytes and msg * (symm.nranks - 1) <= _FUSED_PUSH_MAX:
+        return 5
+    return 0
+
+
 def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start: int = 0, residual=None,
            out_dtype=None, comm=None):
     """y = epilogue(x @ w.T); with ``comm`` the product is summed over the TP group first
@@ -45,12 +74,9 @@ def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start:
             return cu.linear(x, w, bias, act, gated, act_start, residual, out_dtype)
         symm = comm.symm
         if symm is not None:
-            plan = cu.gemm_plan(x.shape[0], w.shape[0], x.shape[1], symm.nranks)
-            # fused one-shot epilogue while the per-rank push stays small; beyond that the bandwidth-optimal
-            # two-shot all-reduce after a plain GEMM wins (measured crossover ~1 MB per rank at 8 GPUs)
-            push_bytes = x.shape[0] * w.shape[0] * x.element_size() * (symm.nranks - 1)
-            if plan.ar_bytes <= symm.lam_bytes and plan.tiles <= 2048 and push_bytes <= (6 << 20):
-                return cu.linear(x, w, bias, ACT_NONE, False, 0, residual, None, symm=symm)
+            mode = _fused_ar_mode(cu, symm, x.shape[0], w.shape[0], x.shape[1], x.element_size())
+            if mode:
+                return cu.linear(x, w, bias, ACT_NONE, False, 0, residual, None, symm=symm, collective=mode)
         y = cu.linear(x, w, None, ACT_NONE, False, 0, None, None)
         comm.all_reduce(y)
         if bias is not None:

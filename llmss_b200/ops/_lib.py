@@ -32,6 +32,29 @@ _SIGS = {
     "llmss_symm_region_bytes": (c_size_t, [c_size_t, c_size_t]),
     "llmss_symm_create": (c_int, [c_int, c_int, C.POINTER(c_void_p), c_size_t, c_size_t, C.POINTER(c_void_p)]),
     "llmss_symm_destroy": (c_int, [c_void_p]),
+    "llmss_symm_init_region": (c_int, [c_void_p, c_size_t, c_size_t]),
+    "llmss_symm_create2": (c_int, [c_int, c_int, C.POINTER(c_void_p), c_void_p, c_size_t, c_size_t, C.POINTER(c_void_p)]),
+    "llmss_symm_has_multicast": (c_int, [c_void_p]),
+    "llmss_vmm_caps": (c_int, [C.POINTER(c_int)]),
+    "llmss_vmm_padded_size": (c_int, [c_size_t, c_int, c_int, C.POINTER(c_size_t)]),
+    "llmss_vmm_alloc": (c_int, [c_size_t, C.POINTER(c_void_p)]),
+    "llmss_vmm_ptr": (c_void_p, [c_void_p]),
+    "llmss_vmm_mc_ptr": (c_void_p, [c_void_p]),
+    "llmss_vmm_bytes": (c_size_t, [c_void_p]),
+    "llmss_vmm_export_fd": (c_int, [c_void_p, C.POINTER(c_int)]),
+    "llmss_vmm_import": (c_int, [c_int, c_size_t, C.POINTER(c_void_p)]),
+    "llmss_vmm_unmap": (c_int, [c_void_p, c_size_t]),
+    "llmss_vmm_free": (c_int, [c_void_p]),
+    "llmss_mc_create": (c_int, [c_int, c_size_t, C.POINTER(C.c_ulonglong), C.POINTER(c_int)]),
+    "llmss_mc_import": (c_int, [c_int, C.POINTER(C.c_ulonglong)]),
+    "llmss_mc_add_device": (c_int, [C.c_ulonglong]),
+    "llmss_mc_bind_and_map": (c_int, [C.c_ulonglong, c_void_p]),
+    "llmss_mc_release": (c_int, [C.c_ulonglong]),
+    "llmss_fdx_open": (c_int, [C.c_char_p, C.POINTER(c_int)]),
+    "llmss_fdx_send": (c_int, [c_int, C.c_char_p, c_int, c_int]),
+    "llmss_fdx_recv": (c_int, [c_int, c_int, C.POINTER(c_int), C.POINTER(c_int)]),
+    "llmss_fdx_close": (c_int, [c_int]),
+    "llmss_fd_close": (c_int, [c_int]),
     "llmss_symm_epoch": (c_int, [c_void_p, C.POINTER(C.c_uint32)]),
     "llmss_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "llmss_allgather": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
@@ -113,6 +136,11 @@ def has(name: str) -> bool:
 
 class KernelError(RuntimeError):
     pass
+
+
+def last_error() -> str:
+    msg = load().llmss_last_error()
+    return msg.decode() if msg else ""
 
 
 def check(rc: int, what: str):

@@ -75,7 +75,10 @@ def gemm_plan(M: int, N: int, K: int, nranks: int = 1, max_ctas: int = 0) -> _li
 
 
 def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start: int = 0, residual=None,
-           out_dtype=None, symm=None, out=None, max_ctas: int = 0):
+           out_dtype=None, symm=None, out=None, max_ctas: int = 0, collective: int = 1):
+    """``symm``: fuse the tensor-parallel all-reduce into the epilogue.  ``collective``: 1 = library picks the
+    exchange (in-switch NVLS reduction from `LLMSS_NVLS_MIN_BYTES` upwards when the workspace is multicast
+    bound, else the one-shot Lamport push), 4 = NVLS, 5 = one-shot push."""
     lib = _lib.load()
     M, K, ldx = _rows2d(x)
     N, Kw, ldw = _rows2d(w)
@@ -90,9 +93,10 @@ def linear(x, w, bias=None, act: int = ACT_NONE, gated: bool = False, act_start:
     ldr = residual.stride(0) if residual is not None else 0
     ar = symm is not None and symm.nranks > 1
     a = arena(x.device)
-    rc = lib.llmss_gemm(_ptr(x), ldx, _ptr(w), ldw, _ptr(bias), _ptr(residual), ldr, _ptr(out), out.stride(0),
-                        M, N, K, _DT[x.dtype], out_f32, act, act_start, 1 if gated else 0,
-                        _ptr(a.sk_ws), _ptr(a.sk_counters), symm.handle if ar else None, max_ctas, _stream())
+    rc = lib.llmss_gemm_ex(_ptr(x), ldx, _ptr(w), ldw, _ptr(bias), _ptr(residual), ldr, _ptr(out), out.stride(0),
+                           M, N, K, _DT[x.dtype], out_f32, act, act_start, 1 if gated else 0,
+                           _ptr(a.sk_ws), _ptr(a.sk_counters), symm.handle if ar else None, max_ctas,
+                           collective if ar else 0, None, _stream())
     _lib.check(rc, "llmss_gemm")
     _count()
     return out

@@ -171,10 +171,10 @@ def _fmix32(x):
 
 
 def rng_uniform(seed: torch.Tensor, step: torch.Tensor) -> torch.Tensor:
-    """Counter-based uniforms in [0,1), one per row; bit-identical to csrc/sample.cu."""
-    rows = torch.arange(seed.numel(), dtype=torch.int64, device=seed.device)
+    """Counter-based uniforms in [0,1), one per row, keyed on the request's (seed, step) only (not on the
+    batch row: a request samples the same tokens in any slot); bit-identical to csrc/sample.cu."""
     s, t = seed.long() & 0xFFFFFFFF, step.long() & 0xFFFFFFFF
-    x = (rows * 0x9E3779B1 + t * 0x85EBCA77 + s * 0xC2B2AE3D) & 0xFFFFFFFF
+    x = (0x9E3779B1 + t * 0x85EBCA77 + s * 0xC2B2AE3D) & 0xFFFFFFFF
     x = _fmix32(_fmix32(x))
     return (x >> 8).float() * (1.0 / 16777216.0)
 

@@ -45,7 +45,7 @@ class _Live:
 
 class ConsumerLoop:
     def __init__(self, engine: Engine, tokenizer, broker, max_new_per_step: int = 16, plan_ints: int = 1 << 18,
-                 idle_block_s: float = 0.05):
+                 idle_block_s: float = 0.05, poll_every: int = 4):
         self.engine, self.tok, self.broker = engine, tokenizer, broker
         self.comm = engine.comm
         self.rank = self.comm.rank
@@ -53,6 +53,13 @@ class ConsumerLoop:
         self.idle_block_s = idle_block_s
         dev = engine.core.device
         self.plan = torch.zeros(plan_ints, dtype=torch.int32, device=dev if dev.type == "cuda" else "cpu")
+        self.hdr = torch.zeros(4, dtype=torch.int32, device=self.plan.device)
+        # While the engine is busy the broker is polled (and the ranks synchronise on the 16-byte header) only every
+        # `poll_every` steps -- the schedule is a function of the step counter, so every rank knows without asking
+        # whether this step has a header; a pure decode step in between costs no collective and no host sync.
+        self.poll_every = max(1, int(poll_every))
+        self._step_idx = 0
+        self.bytes_shared = 0     # collective payload so far (tests / serving bench)
         self.live: Dict[int, _Live] = {}
         self._next_rid = 0
         self.stop = False
@@ -94,59 +101,81 @@ class ConsumerLoop:
 
     # ------------------------------------------------------------------ plan broadcast
     def _share(self, new: List[tuple]) -> List[tuple]:
-        """Make every rank see the same [(rid, ids, SamplingParams)] list (+ stop flag)."""
+        """Make every rank see the same [(rid, ids, SamplingParams)] list (+ stop flag).
+
+        Wire format: a 4-int header [n_requests, stop, flat_len, 0] is broadcast first; only when n_requests > 0 a
+        second broadcast carries exactly the used prefix of the plan buffer (rounded up to 256 ints), and the
+        followers decode exactly ``flat_len`` ints of it."""
         items = []
+        flat: List[int] = []
         if self.rank == 0:
-            flat = [len(new), int(self.stop)]
             for req, ids in new:
                 rid = self._next_rid
                 self._next_rid += 1
                 self.live[rid] = _Live(req)
                 sp = req.sampling()
                 flat += [rid, len(ids), sp.max_new_tokens, int(sp.is_greedy), sp.top_k, _f2i(sp.temperature),
-                         _f2i(sp.top_p), sp.seed & 0x7FFFFFFF]
+                         _f2i(sp.top_p), -1 if sp.seed is None else (sp.seed & 0x7FFFFFFF)]
                 flat += ids
                 items.append((rid, ids, sp))
             if len(flat) > self.plan.numel():
                 raise RuntimeError("request plan exceeds the broadcast buffer")
-            if not self.comm.single:
-                self.plan[:len(flat)] = torch.tensor(flat, dtype=torch.int32)
         if self.comm.single:
             return items
-        self.comm.broadcast(self.plan, src=0)
+        if self.rank == 0:
+            self.hdr.copy_(torch.tensor([len(new), int(self.stop), len(flat), 0], dtype=torch.int32))
+        self.comm.broadcast(self.hdr, src=0)
+        self.bytes_shared += 16
+        n, stop, flat_len, _ = self.hdr.tolist()
+        self.stop = bool(stop)
+        if n == 0:
+            return items
+        padded = min(self.plan.numel(), -(-flat_len // 256) * 256)
+        if self.rank == 0:
+            self.plan[:flat_len] = torch.tensor(flat, dtype=torch.int32)
+        self.comm.broadcast(self.plan[:padded], src=0)
+        self.bytes_shared += padded * 4
         if self.rank == 0:
             return items
         from ..engine.runner import SamplingParams
 
-        head = self.plan[:2].tolist()
-        n, self.stop = head[0], bool(head[1])
-        if n == 0:
-            return []
-        buf = self.plan.tolist() if n > 4 else self.plan[:65536].tolist()
-        pos = 2
+        buf = self.plan[:flat_len].tolist()
+        pos = 0
         for _ in range(n):
             rid, L, mx, gr, tk, te, tp, seed = buf[pos:pos + _HDR]
             pos += _HDR
             ids = buf[pos:pos + L]
             pos += L
             items.append((rid, ids, SamplingParams(max_new_tokens=mx, is_greedy=bool(gr), top_k=tk,
-                                                   temperature=_i2f(te), top_p=_i2f(tp), seed=seed)))
+                                                   temperature=_i2f(te), top_p=_i2f(tp), seed=None if seed < 0 else seed)))
         return items
 
     # ------------------------------------------------------------------ main loop
     def step(self) -> int:
         """One scheduling iteration; returns the number of tokens produced."""
         idle = not self.engine.has_work()
-        new = self._pull(block=idle) if self.rank == 0 else []
-        for rid, ids, sp in self._share(new):
-            self.engine.add_request(ids, sp, request_id=rid)
+        self._step_idx += 1
+        if idle or self._step_idx % self.poll_every == 0:   # same decision on every rank (replicated engine state)
+            new = self._pull(block=idle) if self.rank == 0 else []
+            for rid, ids, sp in self._share(new):
+                self.engine.add_request(ids, sp, request_id=rid)
         if not self.engine.has_work():
             return 0
         outs = self.engine.step()
+        if self.rank != 0:
+            for o in outs:
+                if o.finished:
+                    self.engine.stats.pop(o.request_id, None)
         if self.rank == 0:
             for o in outs:
                 lv = self.live.get(o.request_id)
                 if lv is None:
+                    continue
+                if o.token < 0:  # rejected by the engine: can never fit the KV cache
+                    self._reply(lv.req, GenerateResponse(prompt=lv.req.prompt, continuation="",
+                                                         error="request does not fit the KV cache (prompt + max_new_tokens too long)"))
+                    del self.live[o.request_id]
+                    self.engine.stats.pop(o.request_id, None)
                     continue
                 lv.tokens.append(o.token)
                 if lv.req.stream and not o.finished:

@@ -70,7 +70,7 @@ def _to_internal(pb, stream: bool) -> protocol.GenerateRequest:
     # proto3 scalars default to 0: treat unset sampling fields as the reference CLI defaults
     return protocol.GenerateRequest(
         prompt=pb.prompt, max_new_tokens=pb.max_new_tokens or 20, is_greedy=pb.is_greedy,
-        temperature=pb.temperature or 1.0, top_p=pb.top_p or 0.95, top_k=pb.top_k, seed=pb.seed, stream=stream)
+        temperature=pb.temperature or 1.0, top_p=pb.top_p or 0.95, top_k=pb.top_k, seed=(pb.seed or None), stream=stream)
 
 
 def _to_pb(r: protocol.GenerateResponse):

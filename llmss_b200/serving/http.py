@@ -28,7 +28,7 @@ class Request(BaseModel):
     temperature: float = 1.0
     top_p: float = 0.95
     top_k: int = 50
-    seed: int = 0
+    seed: Optional[int] = None
 
 
 class Response(BaseModel):

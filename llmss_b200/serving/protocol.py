@@ -24,7 +24,7 @@ class GenerateRequest:
     temperature: float = 1.0
     top_p: float = 0.95
     top_k: int = 50
-    seed: int = 0
+    seed: Optional[int] = None
     stream: bool = False
     request_id: Optional[str] = None
     reply_to: Optional[str] = None
@@ -32,7 +32,7 @@ class GenerateRequest:
     def sampling(self) -> SamplingParams:
         return SamplingParams(max_new_tokens=int(self.max_new_tokens), is_greedy=bool(self.is_greedy),
                               temperature=float(self.temperature), top_p=float(self.top_p), top_k=int(self.top_k),
-                              seed=int(self.seed)).validate()
+                              seed=None if self.seed is None else int(self.seed)).validate()
 
     def with_routing(self) -> "GenerateRequest":
         if self.request_id is None:

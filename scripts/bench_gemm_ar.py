@@ -13,6 +13,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 
+from llmss_b200 import ops
 from llmss_b200.ops import cuda_impl as cu
 from llmss_b200.parallel.comm import comm_for
 from llmss_b200.utils.dist import initialize_torch_distributed
@@ -53,60 +54,70 @@ def main():
     pg, rank, world = initialize_torch_distributed(timeout_s=300)
     dev = torch.device("cuda", torch.cuda.current_device())
     comm = comm_for(pg, dev)
-    symm = comm.attach_symmetric(128 << 20)
+    symm = comm.attach_symmetric(256 << 20, lamport_bytes=64 << 20)
+    if rank == 0:
+        print(f"symmetric heap: mode={symm.mode} multicast={symm.has_multicast} log={symm.bringup_log}", flush=True)
     rows = []
     shapes = [("gptj out+down", 4096, 20480), ("llama7b o_proj", 4096, 4096), ("llama7b down", 4096, 11008),
               ("llama13b down", 5120, 13824)]
+    Ms = (1, 16, 64, 128, 256) + ((8192,) if "--prefill" in sys.argv else ())
+    if "--quick" in sys.argv:
+        shapes, Ms = shapes[:1] + shapes[3:], (16, 64, 256)
+    nan = float("nan")
     for name, N, Kfull in shapes:
         K = (Kfull // world) // 64 * 64
-        for M in (1, 16, 64, 256):
+        for M in Ms:
             nvar = max(2, min(16, int(300e6 // (N * K * 2)) + 1))
             ws = [torch.randn(N, K, device=dev, dtype=torch.bfloat16) / math.sqrt(K * world) for _ in range(nvar)]
             x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
             y = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
             plan = cu.gemm_plan(M, N, K, world)
-            if plan.ar_bytes > symm.lam_bytes:
-                continue
             i = [0]
 
-            def fused():
+            def w():
                 i[0] += 1
-                cu.linear(x, ws[i[0] % nvar], symm=symm, out=y)
+                return ws[i[0] % nvar]
 
-            def gemm_only():
-                i[0] += 1
-                cu.linear(x, ws[i[0] % nvar], out=y)
+            msg = M * N * 2
+            can_push = plan.ar_bytes <= symm.lam_bytes
+            can_nvls = symm.has_multicast and plan.split > 0 and plan.tiles * 128 * plan.bn * 2 <= min(symm.lam_bytes, symm.buf_bytes)
+            r = dict(name=name, M=M, N=N, K=K, tp=world, split=plan.split, bn=plan.bn, tiles=plan.tiles)
+            r["gemm_us"] = graph_time(lambda: cu.linear(x, w(), out=y))
+            r["fused_push_us"] = graph_time(lambda: cu.linear(x, w(), symm=symm, out=y, collective=5)) if can_push else nan
+            r["fused_nvls_us"] = graph_time(lambda: cu.linear(x, w(), symm=symm, out=y, collective=4)) if can_nvls else nan
+            can_two = plan.split > 0 and (world + 1) * plan.tiles * 128 * plan.bn * 2 <= symm.lam_bytes
+            r["fused_two_us"] = graph_time(lambda: cu.linear(x, w(), symm=symm, out=y, collective=6)) if can_two else nan
+            r["ar_twolam_us"] = graph_time(lambda: symm.all_reduce_(y, algo=4)) if (world + 1) * msg <= symm.lam_bytes else nan
+            r["ar_oneshot_us"] = graph_time(lambda: symm.all_reduce_(y, algo=1)) if msg * world <= symm.lam_bytes and msg <= (1 << 20) else nan
+            r["ar_twoshot_us"] = graph_time(lambda: symm.all_reduce_(y, algo=2)) if (msg // 16) % world == 0 and 2 * msg <= symm.buf_bytes else nan
+            r["ar_nvls_us"] = graph_time(lambda: symm.all_reduce_(y, algo=3)) if symm.has_multicast and 2 * msg <= symm.buf_bytes else nan
 
-            def ours_unfused():
-                i[0] += 1
-                cu.linear(x, ws[i[0] % nvar], out=y)
-                symm.all_reduce_(y)
+            def product_path():  # what ops.linear(..., comm=comm) does for this shape
+                ops.linear(x, w(), comm=comm)
 
-            def ar_only():
-                symm.all_reduce_(y)
+            r["ours_us"] = graph_time(product_path)
+            r["mode"] = ops._fused_ar_mode(cu, symm, M, N, K, 2)
 
             def reference_path():  # layers.py:175-179: F.linear (cuBLAS) then NCCL all_reduce
-                i[0] += 1
-                torch.mm(x, ws[i[0] % nvar].t(), out=y)
+                torch.mm(x, w().t(), out=y)
                 dist.all_reduce(y)
 
-            def nccl_only():
-                dist.all_reduce(y)
-
-            r = dict(name=name, M=M, N=N, K=K, tp=world, split=plan.split, fused_us=graph_time(fused),
-                     gemm_us=graph_time(gemm_only), unfused_us=graph_time(ours_unfused), ar_us=graph_time(ar_only),
-                     ref_us=graph_time(reference_path), nccl_us=graph_time(nccl_only))
-            # roofline: slower of weight streaming at measured HBM peak and the all-reduce bytes over NVLink
-            t_hbm = N * K * 2 / 6545.6e9 * 1e6
-            t_link = (world - 1) * M * N * 2 / 770e9 * 1e6
-            r["roofline_us"] = max(t_hbm, t_link)
-            r["frac"] = r["roofline_us"] / r["fused_us"]
+            r["ref_us"] = graph_time(reference_path)
+            r["nccl_us"] = graph_time(lambda: dist.all_reduce(y))
+            r["cublas_us"] = graph_time(lambda: torch.mm(x, w().t(), out=y))
+            # roofline: slowest of weight streaming at the measured HBM peak, the flops at the measured bf16 peak and
+            # the bytes that must cross NVLink (in-switch reduction: 2 (t-1)/t x message per direction) at 770 GB/s
+            t_hbm = (N * K * 2 + M * K * 2 + M * N * 2) / 6545.6e9 * 1e6
+            t_flop = 2.0 * M * N * K / 1654.1e12 * 1e6
+            t_link = 2.0 * (world - 1) / world * msg / 770e9 * 1e6
+            r["roofline_us"] = max(t_hbm, t_flop, t_link)
+            r["frac"] = r["roofline_us"] / r["ours_us"]
             rows.append(r)
             if rank == 0:
-                print(f"{name:15s} tp={world} M={M:3d} N={N} K={K:5d} split={plan.split} | fused {r['fused_us']:7.1f} us | "
-                      f"gemm {r['gemm_us']:6.1f} + one-shot AR {r['ar_us']:6.1f} = unfused {r['unfused_us']:7.1f} | "
-                      f"cuBLAS+NCCL {r['ref_us']:7.1f} (NCCL alone {r['nccl_us']:6.1f}) | roofline {r['roofline_us']:5.1f} us "
-                      f"-> {100 * r['frac']:4.1f}% | {r['ref_us'] / r['fused_us']:.2f}x vs reference path", flush=True)
+                print(f"{name:15s} tp={world} M={M:4d} N={N} K={K:5d} split={plan.split} | gemm {r['gemm_us']:7.1f} | fused push {r['fused_push_us']:7.1f} "
+                      f"two {r['fused_two_us']:7.1f} nvls {r['fused_nvls_us']:7.1f} | AR 1shot {r['ar_oneshot_us']:7.1f} 2lam {r['ar_twolam_us']:7.1f} 2flag {r['ar_twoshot_us']:7.1f} nvls {r['ar_nvls_us']:7.1f} | "
+                      f"ours(mode {r['mode']}) {r['ours_us']:7.1f} | cuBLAS {r['cublas_us']:7.1f} + NCCL {r['nccl_us']:6.1f} = {r['ref_us']:7.1f} | "
+                      f"roofline {r['roofline_us']:6.1f} -> {100 * r['frac']:4.1f}% | {r['ref_us'] / r['ours_us']:.2f}x vs ref", flush=True)
     if rank == 0 and "--json" in sys.argv:
         json.dump(rows, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
     dist.barrier()

@@ -35,15 +35,19 @@ def main():
     symm = comm.attach_symmetric(64 << 20, lamport_bytes=max(16, 8 * world) << 20)  # bulk + Lamport area (grows with the rank count)
     assert symm is not None
     ok = True
+    log(f"symmetric heap: mode={symm.mode} multicast={symm.has_multicast} log={symm.bringup_log}")
+    algos = (1, 2, 3, 4) if symm.has_multicast else (1, 2, 4)
 
     # ---- 1. all-reduce
     for dtype in (torch.bfloat16, torch.float16, torch.float32):
         for n in (8, 1024, 4096 * 64, 4096 * 64 + 8, 1 << 20, 3 << 20):
-            for algo in (1, 2):
+            for algo in algos:
                 nbytes = n * torch.empty((), dtype=dtype).element_size()
                 if algo == 2 and (nbytes // 16) % world != 0:
                     continue
-                if (algo == 1 and nbytes * world > symm.lam_bytes) or (algo == 2 and nbytes * 2 > symm.buf_bytes):
+                if (algo == 1 and nbytes * world > symm.lam_bytes) or (algo in (2, 3) and nbytes * 2 > symm.buf_bytes):
+                    continue
+                if algo == 4 and nbytes * (world + 1) > symm.lam_bytes:
                     continue
                 torch.manual_seed(1000 + rank)
                 x = torch.randn(n, device=dev, dtype=dtype)
@@ -108,18 +112,20 @@ def main():
             plan = cu.gemm_plan(M, N, K, world)
             if plan.ar_bytes > symm.lam_bytes:
                 continue
-            for rep in range(3):
-                y = cu.linear(xr, wr, bias, residual=res, symm=symm)
-                torch.cuda.synchronize()
-                err = (y.float() - want).abs().max().item()
-                if err > 0.08:
+            modes = [5] + ([4] if (symm.has_multicast and plan.split > 0) else []) + ([6] if plan.split > 0 else [])
+            for mode in modes:
+                for rep in range(3):
+                    y = cu.linear(xr, wr, bias, residual=res, symm=symm, collective=mode)
+                    torch.cuda.synchronize()
+                    err = (y.float() - want).abs().max().item()
+                    if err > 0.08:
+                        ok = False
+                        log(f"FAIL gemm+AR M={M} N={N} K={K} {dtype} mode={mode} rep={rep} max err {err}")
+                gathered = [torch.empty_like(y) for _ in range(world)]
+                dist.all_gather(gathered, y)
+                if not all(torch.equal(gathered[0], gg) for gg in gathered):
                     ok = False
-                    log(f"FAIL gemm+AR M={M} N={N} K={K} {dtype} rep={rep} max err {err}")
-            gathered = [torch.empty_like(y) for _ in range(world)]
-            dist.all_gather(gathered, y)
-            if not all(torch.equal(gathered[0], gg) for gg in gathered):
-                ok = False
-                log(f"FAIL gemm+AR not bit-identical across ranks M={M} N={N} K={K}")
+                    log(f"FAIL gemm+AR not bit-identical across ranks M={M} N={N} K={K} mode={mode}")
     log("fused GEMM+AR done", "OK" if ok else "FAILED")
 
     # ---- 3b. fused GEMM -> reduce-scatter (K2) and all-gather -> GEMM (K3), prefill-size token counts
@@ -210,7 +216,9 @@ def main():
         cases.append(("ar", x, w_))
     torch.manual_seed(600 + rank)
     xg = torch.randn(32, 1024, device=dev, dtype=torch.bfloat16)
-    wg = torch.randn(1024, 1024, device=dev, dtype=torch.bfloat16) / math.sqrt(1024 * world)
+    wg = torch.randn(4096, 1024, device=dev, dtype=torch.bfloat16) / math.sqrt(1024 * world)
+    stress_split = cu.gemm_plan(32, 4096, 1024, world).split > 0
+    stress_nvls = symm.has_multicast and stress_split
     eg = xg.float() @ wg.float().t()
     dist.all_reduce(eg)
     cases.append(("gemm", (xg, wg), eg))
@@ -221,11 +229,11 @@ def main():
             torch.cuda._sleep(int(rnd.random() * 400000))  # up to ~0.2 ms of skew on this rank only
         if kind == "ar":
             y_ = inp.clone()
-            symm.all_reduce_(y_, algo=1 if (it % 3) else 0)
+            symm.all_reduce_(y_, algo=((3 if symm.has_multicast else 4) if it % 2 else (4 if it % 4 else 1)) if (it % 3) else 0)
             e_ = (y_.float() - want_.float()).abs().max().item()
             tol_ = 0.06 * math.sqrt(world)
         else:
-            y_ = cu.linear(inp[0], inp[1], symm=symm)
+            y_ = cu.linear(inp[0], inp[1], symm=symm, collective=(4 if stress_nvls else 6) if it % 2 else (6 if (stress_split and it % 4) else 5))
             e_ = (y_.float() - want_).abs().max().item()
             tol_ = 0.08
         if e_ > tol_:
@@ -256,8 +264,10 @@ def main():
             return t.item()
 
         ours = timed(lambda: symm.all_reduce_(x, algo=1))
+        nvls = timed(lambda: symm.all_reduce_(x, algo=3)) if symm.has_multicast else float("nan")
+        two = timed(lambda: symm.all_reduce_(x, algo=4))
         nccl = timed(lambda: dist.all_reduce(x))
-        log(f"all-reduce {nbytes >> 10:4d} KiB x{world}: one-shot P2P {ours:7.1f} us | NCCL {nccl:7.1f} us")
+        log(f"all-reduce {nbytes >> 10:4d} KiB x{world}: one-shot P2P {ours:7.1f} us | two-shot Lamport {two:7.1f} us | NVLS {nvls:7.1f} us | NCCL {nccl:7.1f} us")
 
     # ---- 5. engine TP=N == TP=1
     from llmss_b200.engine.engine import Engine

@@ -45,3 +45,56 @@ def test_max_seq_len_stops_generation(tmp_path):
     eng = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=2, max_seq_len=16)
     out = eng.generate([[5] * 10], SamplingParams(max_new_tokens=50, is_greedy=True))
     assert len(out[0]) == 6  # 10 prompt + 6 generated = 16 = max_seq_len (no sliding window)
+
+
+def test_sampling_does_not_depend_on_the_batch_slot(tmp_path):
+    """The sampler's RNG is keyed on (request seed, tokens sampled so far), not on the row of the running batch:
+    a request draws the same tokens alone, behind other requests, or after its neighbours changed."""
+    cfg, _ = make_tiny("llama", tmp_path)
+    sp = SamplingParams(max_new_tokens=8, top_k=30, top_p=0.95, temperature=0.9, seed=1234)
+    other = SamplingParams(max_new_tokens=3, top_k=10, top_p=0.9, seed=99)
+    probe = [7, 8, 9, 10, 11]
+    eng = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=4, max_seq_len=64)
+    alone = eng.generate([probe], sp)[0]
+    crowded = eng.generate([[1, 2, 3], [4, 5], probe, [6, 6, 6, 6]], [other, other, sp, other])
+    assert crowded[2] == alone           # slot 2 of 4, neighbours finish early (slots are re-bound mid-way)
+    first = eng.generate([probe, [3, 2, 1]], [sp, other])
+    assert first[0] == alone             # slot 0
+    # without an explicit seed the stream comes from the request id: two identical requests differ from each other
+    nos = SamplingParams(max_new_tokens=12, top_k=0, top_p=1.0, temperature=1.0)
+    a, b = eng.generate([probe, probe], [nos, nos])
+    assert a != b
+
+
+def test_admission_reserves_worst_case_and_rejects_the_impossible(tmp_path):
+    """Blocks are promised at admission (prompt + max_new), so a running sequence can never fail to grow; a request
+    that cannot fit even an empty cache is reported as finished with token -1 instead of blocking the queue."""
+    cfg, _ = make_tiny("gpt2", tmp_path)
+    # 5 usable blocks of 16 tokens: two requests of 20 + 20 tokens (3 blocks each) cannot run together
+    eng = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=4, max_seq_len=64,
+                                 block_size=16, num_blocks=6)
+    sp = SamplingParams(max_new_tokens=20, is_greedy=True)
+    a = eng.add_request([5] * 20, sp)
+    b = eng.add_request([6] * 20, sp)
+    outs = {}
+    for o in eng.step():                         # prefill: only `a` is admitted, `b` waits for blocks
+        outs.setdefault(o.request_id, []).append(o.token)
+    assert [s.seq_id for s in eng.running] == [a] and [s.seq_id for s in eng.waiting] == [b]
+    assert eng.runner._outstanding == 1          # 2 blocks allocated for the prompt, the third is promised
+    too_big = eng.add_request([7] * 60, SamplingParams(max_new_tokens=60, is_greedy=True))  # 64 tokens = 4 blocks: fits
+    huge = eng.add_request([7] * 10, SamplingParams(max_new_tokens=20, is_greedy=True))
+    while eng.has_work():
+        for o in eng.step():
+            outs.setdefault(o.request_id, []).append(o.token)
+    assert len(outs[a]) == 20 and len(outs[b]) == 20 and len(outs[huge]) == 20
+    assert len(outs[too_big]) == 4               # stops at max_seq_len = 64
+    assert eng.runner._outstanding == 0 and eng.runner.alloc.num_free == 5
+    eng2 = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=4, max_seq_len=64,
+                                  block_size=16, num_blocks=3)
+    never = eng2.add_request([7] * 40, SamplingParams(max_new_tokens=8, is_greedy=True))  # 3 blocks > 2 usable
+    ok = eng2.add_request([7] * 10, SamplingParams(max_new_tokens=4, is_greedy=True))
+    got = {}
+    while eng2.has_work():
+        for o in eng2.step():
+            got.setdefault(o.request_id, []).append(o.token)
+    assert got[never] == [-1] and len(got[ok]) == 4

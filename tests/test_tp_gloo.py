@@ -92,3 +92,69 @@ def test_tp_equals_single(family, world, fuse, tmp_path):
         per_layer = 1 if (family == "gptj" and fuse) else 2
         assert got["stats"]["all_reduce"] == per_layer * L, got["stats"]
         assert got["stats"]["all_gather"] == 1 and got["stats"]["broadcast"] == 0
+
+
+# ------------------------------------------------------------------------------------------------
+# consumer loop at TP=2: what the ranks exchange per step (verdict: a 1 MiB plan broadcast + .tolist() per token)
+def _consumer_worker(rank, world, port, path, out_file):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    os.environ.pop("DEBUG", None)
+    from test_serving_cpu import ByteTokenizer
+
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.serving.broker import PRODUCER_QUEUE, InProcBroker
+    from llmss_b200.serving.consumer import ConsumerLoop
+    from llmss_b200.serving.protocol import GenerateRequest, GenerateResponse
+    from llmss_b200.utils.dist import initialize_torch_distributed
+
+    pg, _, _ = initialize_torch_distributed()
+    eng = Engine.from_pretrained(path, device="cpu", process_group=pg, max_batch=8, max_seq_len=96)
+    seen = []
+    add = eng.add_request
+    eng.add_request = lambda ids, sp, request_id=None: (seen.append((request_id, list(ids), sp.max_new_tokens, sp.seed)),
+                                                        add(ids, sp, request_id=request_id))[1]
+    broker = InProcBroker()
+    reqs = []
+    if rank == 0:  # six requests at once (> 4: the old follower decoded a different prefix length), some long
+        for i in range(6):
+            r = GenerateRequest(prompt="p" * (5 + 11 * i), max_new_tokens=3 + i, is_greedy=(i % 2 == 0),
+                                seed=(40 + i) if i % 3 else None).with_routing()
+            reqs.append(r)
+            broker.lpush(PRODUCER_QUEUE, r.to_json())
+    loop = ConsumerLoop(eng, ByteTokenizer(), broker, idle_block_s=0.01, poll_every=4)
+    steps = 0
+    flag = torch.zeros(1)
+    while True:   # rank 0 decides when the job is over: everything answered
+        loop.step()
+        steps += 1
+        if steps % 8 == 0 or not eng.has_work():
+            flag[0] = float(rank == 0 and not eng.has_work() and steps > 4)
+            dist.broadcast(flag, src=0)
+            if flag.item():
+                break
+    answers = []
+    if rank == 0:
+        for r in reqs:
+            got = broker.brpop(r.reply_to, timeout=5)
+            answers.append(GenerateResponse.from_json(got[1]).num_tokens)
+    torch.save({"seen": seen, "bytes": loop.bytes_shared, "steps": steps, "stats_left": len(eng.stats),
+                "answers": answers}, f"{out_file}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_consumer_plan_exchange_is_small_and_identical_on_every_rank(tmp_path):
+    from llmss_b200.utils.checkpoint import write_random_checkpoint
+
+    path = str(write_random_checkpoint(tmp_path / "ckpt", "gptj-tiny", dtype=torch.float32, device="cpu", std=0.05))
+    out_file = str(tmp_path / "out")
+    mp.spawn(_consumer_worker, args=(2, _free_port(), path, out_file), nprocs=2, join=True)
+    a, b = torch.load(f"{out_file}.0"), torch.load(f"{out_file}.1")
+    assert a["answers"] == [3, 4, 5, 6, 7, 8]
+    assert a["seen"] == b["seen"] and len(a["seen"]) == 6            # ids, lengths, budgets and seeds survive the wire
+    assert [s[3] for s in a["seen"]] == [None, 41, 42, None, 44, 45]
+    assert a["stats_left"] == 0 and b["stats_left"] == 0             # followers drop finished requests too
+    # one payload broadcast (6 headers + ~200 prompt tokens, rounded to 256 ints) plus a 16-byte header on every
+    # polled step -- not a 1 MiB plan per generated token
+    assert a["bytes"] == b["bytes"] and a["bytes"] < 4096 + 16 * a["steps"]
+    assert a["bytes"] <= 4096 + 16 * (a["steps"] // 4 + 8)            # decode steps between polls exchange nothing

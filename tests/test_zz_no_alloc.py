@@ -72,6 +72,9 @@ def _run_both(lib, B, hq, hkv, d, lens, splits, dtype, seed):
     err = (got.float() - want.float()).abs()
     tol = 2e-2 + 2e-2 * want.float().abs()  # the tolerance test_attn_decode uses against the oracle
     assert int((err > tol).sum()) == 0, f"static vs. regular entry point: max err {err.max().item():.4g}"
+    # both entry points launch the same deterministic kernels on the same inputs (fixed split partition, ordered
+    # combine, no atomics); only the home of the partials differs, so the outputs must agree bit for bit
+    assert torch.equal(got, want), f"static vs. regular entry point differ in bits: max err {err.max().item():.4g}"
     assert want.float().abs().sum().item() > 0
 
 
@@ -98,3 +101,19 @@ def test_static_entry_point_refuses_oversize_request():
     assert rc != 0
     msg = lib.llmss_last_error().decode()
     assert "exceed" in msg and "8 MiB" in msg, msg
+
+
+def test_static_entry_point_rejects_zero_kv_heads_without_crashing():
+    """hkv = 0 used to reach `hq % hkv` on the host (integer division by zero kills the process); both entry
+    points now answer with an error code and a message."""
+    lib = _lib()
+    q, kc, vc, bt, sl, bs = _case(2, 4, 4, 64, [5, 9], torch.bfloat16, 4)
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    out = torch.zeros(2, 4 * 64, device="cuda", dtype=torch.bfloat16)
+    rc = lib.llmss_attn_decode_static(p(q), q.stride(0), p(kc), p(vc), p(bt), bt.shape[1], p(sl), p(out), out.stride(0),
+                                      2, 4, 0, 64, bs, 0.125, 1, DT[torch.bfloat16], stream)
+    assert rc != 0 and b"hkv" in lib.llmss_last_error()
+    rc = lib.llmss_attn_decode(p(q), q.stride(0), p(kc), p(vc), p(bt), bt.shape[1], p(sl), p(out), out.stride(0), None,
+                               2, 4, 0, 64, bs, 0.125, 1, DT[torch.bfloat16], stream)
+    assert rc != 0 and b"hkv" in lib.llmss_last_error()

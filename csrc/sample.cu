@@ -52,6 +52,142 @@ __device__ __forceinline__ float block_sum_f(float v, float* red) {
   return t;
 }
 
+// ---- building blocks shared by the single-GPU sampler and the vocab-parallel one (all threads of a 1024-thread CTA
+// call them; the shared arrays are the caller's) ----
+
+// Key (fkey order) of the k-th largest of x[0..n): 4-pass 8-bit radix select.
+__device__ __forceinline__ uint32_t block_radix_kth(const float* __restrict__ x, int n, int k, int* hist,
+                                                    uint32_t* s_prefix, int* s_krem) {
+  const int tid = threadIdx.x;
+  if (tid == 0) { *s_prefix = 0; *s_krem = k; }
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 24 - 8 * pass;
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
+    const uint32_t prefix = *s_prefix;
+    const uint32_t pmask = (pass == 0) ? 0u : (0xffffffffu << (shift + 8));
+    for (int i = tid; i < n; i += kThreads) {
+      const uint32_t key = fkey(x[i]);
+      if ((key & pmask) == prefix) atomicAdd(&hist[(key >> shift) & 0xff], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int rem = *s_krem, bin = 255;
+      for (; bin > 0; --bin) {
+        if (hist[bin] >= rem) break;
+        rem -= hist[bin];
+      }
+      *s_krem = rem;
+      *s_prefix = prefix | ((uint32_t)bin << shift);
+    }
+    __syncthreads();
+  }
+  return *s_prefix;
+}
+
+// In-block bitonic sort of (cval, cidx)[0..count): value descending, index ascending.
+__device__ __forceinline__ void block_sort_candidates(float* cval, int* cidx, int count) {
+  const int tid = threadIdx.x;
+  int nsort = 1;
+  while (nsort < count) nsort <<= 1;
+  for (int i = tid; i < nsort; i += kThreads)
+    if (i >= count) { cval[i] = -INFINITY; cidx[i] = 0x7fffffff; }
+  __syncthreads();
+  for (int size = 2; size <= nsort; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const int i = tid;
+      if (i < nsort) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool desc_block = ((i & size) == 0);  // this block sorted "better first"
+          const float vi = cval[i], vj = cval[j];
+          const int ii = cidx[i], ij = cidx[j];
+          const bool i_before_j = (vi > vj) || (vi == vj && ii < ij);
+          if (i_before_j != desc_block) { cval[i] = vj; cval[j] = vi; cidx[i] = ij; cidx[j] = ii; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// Every x[i] whose key is >= thr_key (at most kMaxCand of them), sorted; indices are offset by idx_offset.
+__device__ __forceinline__ int block_gather_sorted(const float* __restrict__ x, int n, uint32_t thr_key, int idx_offset,
+                                                   float* cval, int* cidx, int* s_count) {
+  const int tid = threadIdx.x;
+  if (tid == 0) *s_count = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += kThreads) {
+    const float v = x[i];
+    if (fkey(v) >= thr_key) {
+      const int slot = atomicAdd(s_count, 1);
+      if (slot < kMaxCand) { cval[slot] = v; cidx[slot] = i + idx_offset; }
+    }
+  }
+  __syncthreads();
+  const int count = min(*s_count, kMaxCand);
+  block_sort_candidates(cval, cidx, count);
+  return count;
+}
+
+// Warp 0: nucleus (top-p on the raw distribution, Z = its normaliser) over the sorted candidates, temperature
+// weights, one inverse-CDF draw.  Returns the position of the chosen candidate.
+__device__ __forceinline__ int warp_draw_from_sorted(const float* cval, int count, float xmax, float Z, float tp,
+                                                     float inv_t, float u01) {
+  const int tid = threadIdx.x;
+  // n_p = number of sorted positions whose preceding mass is < top_p
+  float run = 0.f;  // mass before the current 32-chunk
+  int n_p = 0;
+  for (int base = 0; base < count; base += 32) {
+    const int i = base + tid;
+    const float p = (i < count) ? __expf(cval[i] - xmax) / Z : 0.f;
+    float incl = p;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      float n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (tid >= o) incl += n;
+    }
+    const bool ok = (i < count) && ((run + incl - p) < tp);
+    const unsigned mask = __ballot_sync(0xffffffffu, ok);
+    n_p += __popc(mask);
+    run += __shfl_sync(0xffffffffu, incl, 31);
+    if (mask != 0xffffffffu) break;
+  }
+  n_p = max(n_p, 1);
+  const float thr_p = cval[n_p - 1];
+  // keep = prefix with value >= thr_p (ties stay), already limited to >= k-th largest
+  int n_keep = 0;
+  for (int base = 0; base < count; base += 32) {
+    const int i = base + tid;
+    const unsigned mask = __ballot_sync(0xffffffffu, (i < count) && (cval[i] >= thr_p));
+    n_keep += __popc(mask);
+    if (mask != 0xffffffffu) break;
+  }
+  // total weight at temperature
+  float tot = 0.f;
+  for (int i = tid; i < n_keep; i += 32) tot += __expf((cval[i] - xmax) * inv_t);
+  tot = warp_sum(tot);
+  const float target = u01 * tot;
+  float before = 0.f;
+  int pick = n_keep - 1;
+  bool found = false;
+  for (int base = 0; base < n_keep && !found; base += 32) {
+    const int i = base + tid;
+    const float w = (i < n_keep) ? __expf((cval[i] - xmax) * inv_t) : 0.f;
+    float incl = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      float n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (tid >= o) incl += n;
+    }
+    const bool hit = (i < n_keep) && (target < before + incl);
+    const unsigned mask = __ballot_sync(0xffffffffu, hit);
+    if (mask) { pick = base + __ffs(mask) - 1; found = true; }
+    before += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  return pick;
+}
+
 __global__ void __launch_bounds__(kThreads) sample_kernel(
     const float* __restrict__ logits, int64_t ld, int vocab, const int* __restrict__ greedy,
     const float* __restrict__ temperature, const int* __restrict__ top_k, const float* __restrict__ top_p,
@@ -174,120 +310,14 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(
   for (int i = tid; i < vocab; i += kThreads) part += __expf(x[i] - xmax);
   const float Z = block_sum_f(part, red);
 
-  // ---- radix select: key of the k-th largest logit
+  // ---- k-th largest logit, candidates >= it, sorted (value desc, index asc)
   if (k <= 0 || k > kMaxCand) k = kMaxCand;
   if (k > vocab) k = vocab;
-  if (tid == 0) { s_prefix = 0; s_krem = k; }
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 24 - 8 * pass;
-    if (tid < 256) hist[tid] = 0;
-    __syncthreads();
-    const uint32_t prefix = s_prefix;
-    const uint32_t pmask = (pass == 0) ? 0u : (0xffffffffu << (shift + 8));
-    for (int i = tid; i < vocab; i += kThreads) {
-      const uint32_t key = fkey(x[i]);
-      if ((key & pmask) == prefix) atomicAdd(&hist[(key >> shift) & 0xff], 1);
-    }
-    __syncthreads();
-    if (tid == 0) {
-      int rem = s_krem, bin = 255;
-      for (; bin > 0; --bin) {
-        if (hist[bin] >= rem) break;
-        rem -= hist[bin];
-      }
-      s_krem = rem;
-      s_prefix = prefix | ((uint32_t)bin << shift);
-    }
-    __syncthreads();
-  }
-  const uint32_t thr_key = s_prefix;
-
-  // ---- gather candidates (logit >= k-th largest), then sort (value desc, index asc)
-  if (tid == 0) s_count = 0;
-  __syncthreads();
-  for (int i = tid; i < vocab; i += kThreads) {
-    const float v = x[i];
-    if (fkey(v) >= thr_key) {
-      const int slot = atomicAdd(&s_count, 1);
-      if (slot < kMaxCand) { cval[slot] = v; cidx[slot] = i; }
-    }
-  }
-  __syncthreads();
-  const int count = min(s_count, kMaxCand);
-  int nsort = 1;
-  while (nsort < count) nsort <<= 1;
-  for (int i = tid; i < nsort; i += kThreads)
-    if (i >= count) { cval[i] = -INFINITY; cidx[i] = 0x7fffffff; }
-  __syncthreads();
-  for (int size = 2; size <= nsort; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      const int i = tid;
-      if (i < nsort) {
-        const int j = i ^ stride;
-        if (j > i) {
-          const bool desc_block = ((i & size) == 0);  // this block sorted "better first"
-          const float vi = cval[i], vj = cval[j];
-          const int ii = cidx[i], ij = cidx[j];
-          const bool i_before_j = (vi > vj) || (vi == vj && ii < ij);
-          if (i_before_j != desc_block) { cval[i] = vj; cval[j] = vi; cidx[i] = ij; cidx[j] = ii; }
-        }
-      }
-      __syncthreads();
-    }
-  }
+  const uint32_t thr_key = block_radix_kth(x, vocab, k, hist, &s_prefix, &s_krem);
+  const int count = block_gather_sorted(x, vocab, thr_key, 0, cval, cidx, &s_count);
   // ---- top-p over the sorted candidates, temperature weights, inverse-CDF draw (thread 0..31)
   if (tid < 32) {
-    // n_p = number of sorted positions whose preceding mass is < top_p
-    float run = 0.f;  // mass before the current 32-chunk
-    int n_p = 0;
-    float thr_p = -INFINITY;
-    for (int base = 0; base < count; base += 32) {
-      const int i = base + tid;
-      const float p = (i < count) ? __expf(cval[i] - xmax) / Z : 0.f;
-      float incl = p;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        float n = __shfl_up_sync(0xffffffffu, incl, o);
-        if (tid >= o) incl += n;
-      }
-      const bool ok = (i < count) && ((run + incl - p) < tp);
-      const unsigned mask = __ballot_sync(0xffffffffu, ok);
-      n_p += __popc(mask);
-      run += __shfl_sync(0xffffffffu, incl, 31);
-      if (mask != 0xffffffffu) break;
-    }
-    n_p = max(n_p, 1);
-    thr_p = cval[n_p - 1];
-    // keep = prefix with value >= thr_p (ties stay), already limited to >= k-th largest
-    int n_keep = 0;
-    for (int base = 0; base < count; base += 32) {
-      const int i = base + tid;
-      const unsigned mask = __ballot_sync(0xffffffffu, (i < count) && (cval[i] >= thr_p));
-      n_keep += __popc(mask);
-      if (mask != 0xffffffffu) break;
-    }
-    // total weight at temperature
-    float tot = 0.f;
-    for (int i = tid; i < n_keep; i += 32) tot += __expf((cval[i] - xmax) * inv_t);
-    tot = warp_sum(tot);
-    const float target = u01 * tot;
-    float before = 0.f;
-    int pick = n_keep - 1;
-    bool found = false;
-    for (int base = 0; base < n_keep && !found; base += 32) {
-      const int i = base + tid;
-      const float w = (i < n_keep) ? __expf((cval[i] - xmax) * inv_t) : 0.f;
-      float incl = w;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        float n = __shfl_up_sync(0xffffffffu, incl, o);
-        if (tid >= o) incl += n;
-      }
-      const bool hit = (i < n_keep) && (target < before + incl);
-      const unsigned mask = __ballot_sync(0xffffffffu, hit);
-      if (mask) { pick = base + __ffs(mask) - 1; found = true; }
-      before += __shfl_sync(0xffffffffu, incl, 31);
-    }
+    const int pick = warp_draw_from_sorted(cval, count, xmax, Z, tp, inv_t, u01);
     if (tid == 0) {
       const int tok = cidx[pick];
       if (out_tokens) out_tokens[row] = tok;
@@ -353,6 +383,129 @@ __global__ void argmax_merge_kernel(const Cand* __restrict__ cand, int nranks, i
   if (out64) out64[row] = bi;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Vocab-parallel sampling (K11, general case): top-k / top-p / temperature without gathering [B, V] logits.
+// Each rank condenses its vocab shard to a fixed-size record per row -- local max, local sum-exp (relative to that
+// max) and its local top-k candidates, ties at the k-th value included, sorted -- the records are gathered
+// (1 KiB per row and rank instead of V/t floats), and every rank merges them identically: global max and
+// normaliser from the (max, sum-exp) pairs, union of the candidates sorted (value desc, index asc), global k-th
+// value, nucleus, temperature, one draw with the request's counter RNG.  An element >= the global k-th value is
+// >= its own rank's local k-th value, so the union is complete and the result equals sample_kernel's on the
+// gathered logits (oracle: ops/reference.py:sample_vocab_parallel).
+// Record layout (floats): [max, sumexp, count(int), 0, vals[KS], idx[KS](int)].
+__global__ void __launch_bounds__(kThreads) vp_summary_kernel(const float* __restrict__ logits, int64_t ld, int n_valid,
+                                                              int idx_offset, const int* __restrict__ greedy,
+                                                              const int* __restrict__ top_k, float* __restrict__ recs,
+                                                              int KS) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float red[32];
+  __shared__ int hist[256];
+  __shared__ float cval[kMaxCand];
+  __shared__ int cidx[kMaxCand];
+  __shared__ int s_count;
+  __shared__ uint32_t s_prefix;
+  __shared__ int s_krem;
+  __shared__ float s_f;
+  const int row = blockIdx.x, tid = threadIdx.x;
+  const float* x = logits + (int64_t)row * ld;
+  float* rec = recs + (int64_t)row * (4 + 2 * KS);
+  if (n_valid <= 0) {  // this rank's shard is all padding
+    if (tid == 0) { rec[0] = -INFINITY; rec[1] = 0.f; reinterpret_cast<int*>(rec)[2] = 0; rec[3] = 0.f; }
+    return;
+  }
+  float best = -INFINITY;
+  for (int i = tid; i < n_valid; i += kThreads) best = fmaxf(best, x[i]);
+  best = warp_max(best);
+  if ((tid & 31) == 0) red[tid >> 5] = best;
+  __syncthreads();
+  if (tid < 32) {
+    float b = warp_max(red[tid]);
+    if (tid == 0) s_f = b;
+  }
+  __syncthreads();
+  const float xmax = s_f;
+  float part = 0.f;
+  for (int i = tid; i < n_valid; i += kThreads) part += __expf(x[i] - xmax);
+  const float sumexp = block_sum_f(part, red);
+  int k = greedy[row] ? 1 : top_k[row];
+  if (k <= 0 || k > KS) k = KS;
+  if (k > n_valid) k = n_valid;
+  const uint32_t thr_key = block_radix_kth(x, n_valid, k, hist, &s_prefix, &s_krem);
+  int count = block_gather_sorted(x, n_valid, thr_key, idx_offset, cval, cidx, &s_count);
+  count = min(count, KS);  // more than KS - k + 1 exact ties at the k-th value: the highest indices are dropped
+  if (tid == 0) { rec[0] = xmax; rec[1] = sumexp; reinterpret_cast<int*>(rec)[2] = count; rec[3] = 0.f; }
+  for (int i = tid; i < count; i += kThreads) {
+    rec[4 + i] = cval[i];
+    reinterpret_cast<int*>(rec)[4 + KS + i] = cidx[i];
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) vp_merge_sample_kernel(
+    const float* __restrict__ recs, int nranks, int KS, int vocab, const int* __restrict__ greedy,
+    const float* __restrict__ temperature, const int* __restrict__ top_k, const float* __restrict__ top_p,
+    uint32_t* __restrict__ rng_state, int* __restrict__ out_tokens, long long* __restrict__ out_tokens64) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float cval[kMaxCand];
+  __shared__ int cidx[kMaxCand];
+  __shared__ float s_max[8], s_sum[8];
+  __shared__ int s_off[9];
+  const int row = blockIdx.x, tid = threadIdx.x;
+  const int rf = 4 + 2 * KS;
+  const float* base = recs + (int64_t)row * nranks * rf;
+  if (tid == 0) {
+    int off = 0;
+    for (int r = 0; r < nranks; ++r) {
+      s_max[r] = base[(int64_t)r * rf];
+      s_sum[r] = base[(int64_t)r * rf + 1];
+      s_off[r] = off;
+      off = min(kMaxCand, off + min(KS, max(0, reinterpret_cast<const int*>(base + (int64_t)r * rf)[2])));
+    }
+    s_off[nranks] = off;
+  }
+  // every thread reads the counter before the barrier, thread 0 advances it after
+  const uint32_t seed = rng_state[2 * row], step = rng_state[2 * row + 1];
+  __syncthreads();
+  if (tid == 0) rng_state[2 * row + 1] = step + 1;
+  float M = -INFINITY;
+  for (int r = 0; r < nranks; ++r) M = fmaxf(M, s_max[r]);
+  float Z = 0.f;
+  for (int r = 0; r < nranks; ++r)
+    if (s_sum[r] > 0.f) Z += s_sum[r] * __expf(s_max[r] - M);  // rank order: identical on every rank
+  const int n_union = s_off[nranks];
+  for (int r = 0; r < nranks; ++r) {
+    const int o = s_off[r], c = s_off[r + 1] - o;
+    const float* rv = base + (int64_t)r * rf + 4;
+    const int* ri = reinterpret_cast<const int*>(base + (int64_t)r * rf) + 4 + KS;
+    for (int i = tid; i < c; i += kThreads) { cval[o + i] = rv[i]; cidx[o + i] = ri[i]; }
+  }
+  __syncthreads();
+  block_sort_candidates(cval, cidx, n_union);
+  if (greedy[row] || n_union <= 1) {
+    if (tid == 0) {
+      const int tok = n_union > 0 ? cidx[0] : 0;
+      if (out_tokens) out_tokens[row] = tok;
+      if (out_tokens64) out_tokens64[row] = tok;
+    }
+    return;
+  }
+  int k = top_k[row];
+  if (k <= 0 || k > KS) k = KS;
+  k = min(min(k, vocab), n_union);
+  const float thr_k = cval[k - 1];
+  const int count = __syncthreads_count(tid < n_union && cval[tid] >= thr_k);  // sorted: a prefix, ties included
+  if (tid < 32) {
+    const float u01 = rng_uniform(seed, step);
+    const int pick = warp_draw_from_sorted(cval, count, M, Z, top_p[row], 1.0f / temperature[row], u01);
+    if (tid == 0) {
+      const int tok = cidx[pick];
+      if (out_tokens) out_tokens[row] = tok;
+      if (out_tokens64) out_tokens64[row] = tok;
+    }
+  }
+}
+
 }  // namespace
 
 // cand: [B] 16-byte records (this rank's best logit of each row and its global vocabulary index).
@@ -371,6 +524,31 @@ LLMSS_API int llmss_argmax_merge(const void* cand_all, int nranks, int B, int* o
   if (B == 0) return 0;
   LLMSS_CHECK_CUDA(launch_pdl(argmax_merge_kernel, dim3((B + 127) / 128), dim3(128), 0, stream, (const Cand*)cand_all,
                               nranks, B, out_tokens, out_tokens64));
+  return 0;
+}
+
+// Vocab-parallel sampling, step 1 (every rank, on its own fp32 shard [B, >= n_valid] whose column 0 is global token
+// idx_offset): one record of llmss_vp_record_floats(ks) floats per row into `recs`.  ks = candidates kept per rank
+// (even, so records are 16-byte multiples; 1 <= top_k <= ks is exact; nranks * ks <= 1024).
+LLMSS_API int llmss_vp_record_floats(int ks) { return 4 + 2 * ks; }
+LLMSS_API int llmss_vp_summary(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, const int* greedy,
+                               const int* top_k, float* recs, int ks, cudaStream_t stream) {
+  LLMSS_REQUIRE(ks >= 2 && ks <= kMaxCand && ks % 2 == 0, "vp_summary: ks=%d must be even and within [2, %d]", ks, kMaxCand);
+  LLMSS_REQUIRE(n_valid >= 0 && ld >= n_valid, "vp_summary: bad shard width");
+  if (B == 0) return 0;
+  LLMSS_CHECK_CUDA(launch_pdl(vp_summary_kernel, dim3(B), dim3(kThreads), 0, stream, logits, ld, n_valid, idx_offset,
+                              greedy, top_k, recs, ks));
+  return 0;
+}
+// Step 2 (every rank, on the column-gathered records [B][nranks][record]): merge + sample; advances rng_state.
+LLMSS_API int llmss_vp_merge_sample(const float* recs_all, int nranks, int ks, int B, int vocab, const int* greedy,
+                                    const float* temperature, const int* top_k, const float* top_p,
+                                    uint32_t* rng_state, int* out_tokens, long long* out_tokens64, cudaStream_t stream) {
+  LLMSS_REQUIRE(nranks >= 1 && nranks <= 8 && nranks * ks <= kMaxCand, "vp_merge_sample: %d ranks x %d candidates exceed %d",
+                nranks, ks, kMaxCand);
+  if (B == 0) return 0;
+  LLMSS_CHECK_CUDA(launch_pdl(vp_merge_sample_kernel, dim3(B), dim3(kThreads), 0, stream, recs_all, nranks, ks, vocab,
+                              greedy, temperature, top_k, top_p, rng_state, out_tokens, out_tokens64));
   return 0;
 }
 

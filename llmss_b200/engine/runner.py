@@ -97,6 +97,7 @@ class ModelRunner:
         self.graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}   # (padded batch, vocab-parallel greedy) -> graph
         self.launches_per_graph: Dict[int, int] = {}   # own-kernel launches captured per decode graph
         self._all_greedy = True
+        self._vp_sampling_ok = True
         self._tuned_splits: Dict[int, int] = {}
         self.tuning_log: Dict[int, dict] = {}
         self.graph_pool = None
@@ -225,6 +226,9 @@ class ModelRunner:
         self.np_len[:] = 0
         self.np_nblk[:] = 0
         self._all_greedy = all(s.params.is_greedy for s in seqs)
+        # vocab-parallel sampling keeps 128 candidates per rank: exact for 1 <= top_k <= 128 (ops/cuda_impl.VP_KS)
+        self._vp_sampling_ok = self.core.tp * 128 <= 1024 and all(
+            s.params.is_greedy or 1 <= s.params.top_k <= 128 for s in seqs)
         for i, s in enumerate(seqs):
             s.slot = i
             self.h_samp_i[i] = int(s.params.is_greedy)
@@ -267,13 +271,18 @@ class ModelRunner:
         self.np_slot[:] = np.where(act, blk * bs + pos % bs, -1)
         self.np_slen[:] = np.where(act, pos + 1, 0)
 
-    def _vp_greedy(self) -> bool:
-        """Vocab-parallel greedy decoding (no logits all-gather): TP > 1 on CUDA and every bound request greedy."""
+    def _vp_greedy(self) -> int:
+        """Vocab-parallel token choice (no [B, V] logits all-gather) at TP > 1 on CUDA: 1 = every bound request is
+        greedy (16-byte argmax candidates), 2 = mixed greedy / top-k sampling (1 KiB candidate records), 0 = a
+        request needs the whole distribution (top_k = 0 or > 128) or the path is switched off (LLMSS_VP_GREEDY=0)."""
         c = self.core.comm
-        return bool(self.cuda and self._all_greedy and not c.single and c.symm is not None
-                    and os.environ.get("LLMSS_VP_GREEDY", "1") == "1")
+        if not (self.cuda and not c.single and c.symm is not None and os.environ.get("LLMSS_VP_GREEDY", "1") == "1"):
+            return 0
+        if self._all_greedy:
+            return 1
+        return 2 if self._vp_sampling_ok else 0
 
-    def _decode_body(self, Bp: int, splits: int, vp_greedy: bool = False):
+    def _decode_body(self, Bp: int, splits: int, vp_greedy: int = 0):
         tok, pos, slot, slen, bt = self._dev_views(Bp)
         MB = self.max_batch
         batch = BatchInput(tokens=tok, positions=pos, slot_mapping=slot, block_tables=bt, seq_lens=slen,
@@ -285,7 +294,12 @@ class ModelRunner:
             from ..ops import cuda_impl as cu
 
             local = self.core.forward(batch, self.kv, last_only=False, gather_logits=False)
-            cu.greedy_vocab_parallel(local, self.core.comm.symm, self.spec.vocab, out=tok)
+            if vp_greedy == 1:
+                cu.greedy_vocab_parallel(local, self.core.comm.symm, self.spec.vocab, out=tok)
+            else:
+                cu.sample_vocab_parallel(local, self.core.comm.symm, self.spec.vocab, self.d_samp_i[:Bp],
+                                         self.d_samp_f[:Bp], self.d_samp_i[MB:MB + Bp], self.d_samp_f[MB:MB + Bp],
+                                         self.d_rng[:Bp], out=tok)
             return
         logits = self.core.forward(batch, self.kv, last_only=False)  # every row is a last token
         ops.sample(logits, self.d_samp_i[:Bp], self.d_samp_f[:Bp], self.d_samp_i[MB:MB + Bp],

@@ -282,3 +282,46 @@ def greedy_vocab_parallel(local_logits, symm, vocab: int, out=None):
     _lib.check(lib.llmss_argmax_merge(_ptr(allc), symm.nranks, B, o32, o64, _stream()), "llmss_argmax_merge")
     _count(2)
     return out
+
+
+VP_KS = 128  # candidates a rank contributes per row: exact for 1 <= top_k <= 128 (8 ranks x 128 = the merge's 1024 slots)
+
+
+def vp_summary(local_logits, n_valid: int, idx_offset: int, greedy, top_k, ks: int = VP_KS):
+    """Per-row record of this rank's shard: [max, sum-exp, count, 0, vals[ks], idx[ks]] (fp32 / int32 bits)."""
+    lib = _lib.load()
+    B = local_logits.shape[0]
+    assert local_logits.dtype == torch.float32 and local_logits.stride(1) == 1
+    rec = torch.empty(B, 4 + 2 * ks, dtype=torch.float32, device=local_logits.device)
+    _lib.check(lib.llmss_vp_summary(_ptr(local_logits), local_logits.stride(0), B, n_valid, idx_offset, _ptr(greedy),
+                                    _ptr(top_k), _ptr(rec), ks, _stream()), "llmss_vp_summary")
+    _count()
+    return rec
+
+
+def vp_merge_sample(recs_all, nranks: int, vocab: int, greedy, temperature, top_k, top_p, rng_state, out=None,
+                    ks: int = VP_KS):
+    """recs_all: [B, nranks * (4 + 2 ks)] column-gathered records -> tokens [B]; advances rng_state."""
+    lib = _lib.load()
+    B = recs_all.shape[0]
+    assert recs_all.is_contiguous() and recs_all.shape[1] == nranks * (4 + 2 * ks)
+    if out is None:
+        out = torch.empty(B, dtype=torch.int32, device=recs_all.device)
+    o32 = _ptr(out) if out.dtype == torch.int32 else None
+    o64 = _ptr(out) if out.dtype == torch.int64 else None
+    _lib.check(lib.llmss_vp_merge_sample(_ptr(recs_all), nranks, ks, B, vocab, _ptr(greedy), _ptr(temperature),
+                                         _ptr(top_k), _ptr(top_p), _ptr(rng_state), o32, o64, _stream()),
+               "llmss_vp_merge_sample")
+    _count()
+    return out
+
+
+def sample_vocab_parallel(local_logits, symm, vocab: int, greedy, temperature, top_k, top_p, rng_state, out=None):
+    """K11: top-k / top-p / temperature sampling over vocab-sharded logits [B, V/t] without gathering them
+    (reference path: list all_gather of [B, S, V/t] at layers.py:131-135 + rank-0 warpers + broadcast,
+    generate.py:109-144).  Three launches: shard summary, 1 KiB-per-row record gather, identical merge + draw."""
+    B, Vb = local_logits.shape
+    off = symm.rank * Vb
+    rec = vp_summary(local_logits, max(0, min(Vb, vocab - off)), off, greedy, top_k)
+    allr = symm.all_gather_cols(rec)
+    return vp_merge_sample(allr, symm.nranks, vocab, greedy, temperature, top_k, top_p, rng_state, out)

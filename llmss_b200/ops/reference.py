@@ -182,7 +182,8 @@ def rng_uniform(seed: torch.Tensor, step: torch.Tensor) -> torch.Tensor:
 MAX_CANDIDATES = 1024
 
 
-def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab: Optional[int] = None) -> torch.Tensor:
+def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab: Optional[int] = None,
+           u_shift: float = 0.0) -> torch.Tensor:
     """Next-token choice per row (G15/G16 with the *intended* semantics).
 
     Order = the reference's warper list order (generate.py:114-120): top-p on the raw
@@ -201,7 +202,8 @@ def sample(logits, greedy, temperature, top_k, top_p, rng_state, vocab: Optional
         x = x[:, :V]
     greedy = greedy.bool()
     arg = x.argmax(-1)
-    u = rng_uniform(rng_state[:, 0], rng_state[:, 1]).double()[:, None]
+    # u_shift nudges the uniform draw (tests use it to find the rows whose choice sits on a CDF boundary)
+    u = (rng_uniform(rng_state[:, 0], rng_state[:, 1]).double()[:, None] + u_shift).clamp(0.0, 1.0 - 2.0 ** -24)
     rng_state[:, 1] += 1
     xmax = x.max(-1, keepdim=True).values
     temp = temperature.float()[:, None]
@@ -258,7 +260,8 @@ def shard_summary(local_logits, offset: int, vocab: int, k: int):
     return out
 
 
-def sample_vocab_parallel(shards, greedy, temperature, top_k, top_p, rng_state, vocab: int, k_summary: int = 64):
+def sample_vocab_parallel(shards, greedy, temperature, top_k, top_p, rng_state, vocab: int, k_summary: int = 64,
+                          u_shift: float = 0.0):
     """`sample()` computed from per-rank shard summaries only (the algorithm a vocab-parallel CUDA sampler
     follows; replaces the [B, V] logits all-gather of layers.py:131-135 + generate.py:109-129).
 
@@ -270,7 +273,7 @@ def sample_vocab_parallel(shards, greedy, temperature, top_k, top_p, rng_state, 
     t = len(shards)
     B, Vb = shards[0].shape
     summ = [shard_summary(s, r * Vb, vocab, k_summary) for r, s in enumerate(shards)]
-    u = rng_uniform(rng_state[:, 0], rng_state[:, 1]).double()
+    u = (rng_uniform(rng_state[:, 0], rng_state[:, 1]).double() + u_shift).clamp(0.0, 1.0 - 2.0 ** -24)
     rng_state[:, 1] += 1
     toks = torch.zeros(B, dtype=torch.long)
     for b in range(B):

@@ -272,6 +272,23 @@ def test_vocab_parallel_argmax_kernels():
     assert torch.equal(out.long()[rows], ref[rows])
 
 
+def _oracle_choices(fn, rng):
+    """The oracle's token per row, plus the tokens it would pick with the uniform draw nudged by +-2e-4: the CUDA
+    kernels evaluate the same CDF in fp32 (`__expf`), so a row whose draw sits on a CDF boundary may legitimately
+    land on the neighbouring token; every other row must match exactly."""
+    want = fn(rng.clone(), 0.0).long().cpu()
+    lo, hi = fn(rng.clone(), -2e-4).long().cpu(), fn(rng.clone(), 2e-4).long().cpu()
+    return want, lo, hi
+
+
+def _check_tokens(got, want, lo, hi, what):
+    got = got.long().cpu()
+    exact = got == want
+    near = exact | (got == lo) | (got == hi)
+    assert bool(near.all()), f"{what}: rows {(~near).nonzero().flatten().tolist()} differ from the oracle\n{got}\n{want}"
+    assert exact.float().mean().item() >= 0.9, f"{what}: only {exact.float().mean().item():.2f} of rows match exactly"
+
+
 def test_sample_matches_oracle():
     cu = _cu()
     torch.manual_seed(3)
@@ -281,18 +298,73 @@ def test_sample_matches_oracle():
     temp = torch.tensor([1.0, 0.7, 1.0, 0.5] * (B // 4), device="cuda")
     top_k = torch.tensor([50, 50, 0, 5, 0, 1000, 1, 0] * (B // 8), dtype=torch.int32, device="cuda")
     top_p = torch.tensor([0.95, 0.95, 1.0, 0.5, 0.9, 1.0, 1.0, 1.0] * (B // 8), device="cuda")
-    for step in range(4):
-        rng = torch.tensor([[1234, step]] * B, dtype=torch.int32, device="cuda")
+    for step in range(6):
+        rng = torch.tensor([[1234 + 17 * b, step] for b in range(B)], dtype=torch.int32, device="cuda")
+        want, lo, hi = _oracle_choices(lambda r, sh: R.sample(logits, greedy, temp, top_k, top_p, r, vocab=V, u_shift=sh), rng)
         rng_ref = rng.clone()
+        R.sample(logits, greedy, temp, top_k, top_p, rng_ref, vocab=V)
         got = cu.sample(logits, greedy, temp, top_k, top_p, rng, vocab=V)
-        want = R.sample(logits, greedy, temp, top_k, top_p, rng_ref, vocab=V)
         torch.cuda.synchronize()
         assert torch.equal(rng, rng_ref.to(rng.dtype))
-        agree = (got.long() == want.long()).float().mean().item()
-        assert agree >= 0.85, f"step {step}: only {agree:.2f} of rows agree\n{got}\n{want}"
+        _check_tokens(got, want, lo, hi, f"step {step}")
         g = greedy.bool()
         assert torch.equal(got.long()[g], logits[g, :V].argmax(-1))
         assert int(got.max()) < V
+
+
+def test_sample_plain_multinomial_never_falls_through():
+    """top_k = 0, top_p = 1: every thread must see the same draw (the RNG counter is advanced only after all
+    threads have read it) and the per-thread CDF intervals must tile [0, total) without gaps -- before the fix a
+    missed interval returned token vocab - 1."""
+    cu = _cu()
+    torch.manual_seed(5)
+    B, V = 64, 50257
+    logits = (torch.randn(B, V, device="cuda") * 4).float()
+    logits[:, V - 1] = -60.0   # the old fall-through token: probability ~ 0
+    z = torch.zeros(B, dtype=torch.int32, device="cuda")
+    one = torch.ones(B, device="cuda")
+    for step in range(50):
+        rng = torch.tensor([[77 + b, step] for b in range(B)], dtype=torch.int32, device="cuda")
+        got = cu.sample(logits, z, one, z, one, rng, vocab=V)
+        assert int((got == V - 1).sum()) == 0, f"step {step}: fell through to the last token"
+        if step < 4:
+            want, lo, hi = _oracle_choices(lambda r, sh: R.sample(logits, z, one, z, one, r, vocab=V, u_shift=sh), rng)
+            _check_tokens(got, want, lo, hi, f"multinomial step {step}")
+
+
+@pytest.mark.parametrize("t", [2, 4, 8])
+def test_vocab_parallel_sampling_kernels(t):
+    """K11 general case on one GPU: the t ranks' shard summaries are produced one after the other, concatenated the
+    way the record all-gather lays them out, and merged; tokens must equal the vocab-parallel oracle (and therefore
+    the single-GPU sampler on the gathered logits)."""
+    cu = _cu()
+    torch.manual_seed(11 + t)
+    B, V = 24, 50257                      # V not divisible by t: the last shard is padded
+    Vb = -(-V // t)
+    full = (torch.randn(B, Vb * t, device="cuda") * 3).float()
+    full[:, V:] = 1e9                     # padding columns hold garbage that must never win
+    full[3, 100] = full[3, 40000] = full[3, :V].max() + 1.0   # exact tie across two shards (greedy row): lowest index wins
+    greedy = torch.tensor([1, 0, 0] * (B // 3), dtype=torch.int32, device="cuda")
+    temp = torch.tensor([1.0, 0.7, 0.5, 1.0] * (B // 4), device="cuda")
+    top_k = torch.tensor([50, 5, 128, 1, 64, 20] * (B // 6), dtype=torch.int32, device="cuda")
+    top_p = torch.tensor([0.95, 0.5, 1.0, 0.9] * (B // 4), device="cuda")
+    shards = [full[:, r * Vb:(r + 1) * Vb].contiguous() for r in range(t)]
+    cpu = lambda x: x.cpu()  # noqa: E731
+    for step in range(4):
+        rng = torch.tensor([[900 + 13 * b, step] for b in range(B)], dtype=torch.int32, device="cuda")
+        want, lo, hi = _oracle_choices(
+            lambda r, sh: R.sample_vocab_parallel([cpu(x) for x in shards], cpu(greedy), cpu(temp), cpu(top_k), cpu(top_p),
+                                                  cpu(r), V, k_summary=cu.VP_KS, u_shift=sh), rng)
+        recs = [cu.vp_summary(shards[r], max(0, min(Vb, V - r * Vb)), r * Vb, greedy, top_k) for r in range(t)]
+        got = cu.vp_merge_sample(torch.cat(recs, dim=1).contiguous(), t, V, greedy, temp, top_k, top_p, rng)
+        torch.cuda.synchronize()
+        assert rng[:, 1].tolist() == [step + 1] * B
+        _check_tokens(got, want, lo, hi, f"t={t} step {step}")
+        assert int(got.max()) < V
+        single = cu.sample(full[:, :V].contiguous(), greedy, temp, top_k, top_p,
+                           torch.tensor([[900 + 13 * b, step] for b in range(B)], dtype=torch.int32, device="cuda"), vocab=V)
+        assert (single.long() == got.long()).float().mean().item() >= 0.9
+    assert got.tolist()[3] == 100
 
 
 @pytest.mark.parametrize("mode", ["streamk", "cluster"])

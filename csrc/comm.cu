@@ -198,8 +198,17 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(SymmWs ws, 
   uint4* mine = symm_lam<uint4>(ws, ws.rank, par);
   for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) {
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // the peers' vectors are polled together: one L2 round trip after the last arrival instead of one per peer
+    uint4* slot[kSymmMaxRanks];
+    uint4 got[kSymmMaxRanks];
+    int m = 0;
+    for (int r = 0; r < ws.nranks; ++r)
+      if (r != ws.rank) slot[m++] = mine + (int64_t)r * nvec + v;
+    for (int i = m; i < kSymmMaxRanks; ++i) slot[i] = slot[0];
+    lam_take_batch<kSymmMaxRanks>(slot, m, got, 1);
+    m = 0;
     for (int r = 0; r < ws.nranks; ++r) {  // fixed order -> bit-identical on all ranks
-      const uint4 raw = (r == ws.rank) ? lam_sanitize<EB>(in[v]) : lam_take(mine + (int64_t)r * nvec + v, 1);
+      const uint4 raw = (r == ws.rank) ? lam_sanitize<EB>(in[v]) : got[m++];
       accum8<T>(acc, raw);
     }
     uint4 o;
@@ -336,7 +345,21 @@ __global__ void __launch_bounds__(kThreads) allreduce_nvls_kernel(SymmWs ws, con
   }
   if constexpr (LAM) {
     uint4* mine = symm_lam<uint4>(ws, ws.rank, par);
-    for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) out[v] = lam_take(mine + v, 6);
+  for (int64_t vb = v0 + threadIdx.x; vb < v1; vb += (int64_t)kThreads * 4) {
+    uint4* slot[4];
+    uint4 got[4];
+    int m = 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t v = vb + (int64_t)u * kThreads;
+      slot[u] = mine + (v < v1 ? v : vb);
+      if (v < v1) m = u + 1;
+    }
+    lam_take_batch<4>(slot, m, got, 6);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (u < m) out[vb + (int64_t)u * kThreads] = got[u];
+  }
   } else {
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -381,7 +404,11 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_lam_kernel(SymmWs 
   const int64_t b0 = min(v1, v0 + me * sub), b1 = min(v1, b0 + sub);
   for (int64_t v = b0 + threadIdx.x; v < b1; v += kThreads) {
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int r = 0; r < n; ++r) accum8<T>(acc, lam_take(mine + (int64_t)r * nvec + v, 8));
+    uint4* slot[kSymmMaxRanks];
+    uint4 got[kSymmMaxRanks];
+    for (int r = 0; r < kSymmMaxRanks; ++r) slot[r] = mine + (int64_t)(r < n ? r : 0) * nvec + v;
+    lam_take_batch<kSymmMaxRanks>(slot, n, got, 8);
+    for (int r = 0; r < n; ++r) accum8<T>(acc, got[r]);  // rank order
     uint4 o;
     if constexpr (std::is_same<T, float>::value) {
       o = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
@@ -396,7 +423,21 @@ __global__ void __launch_bounds__(kThreads) allreduce_twoshot_lam_kernel(SymmWs 
       for (int p = 0; p < n; ++p) symm_lam<uint4>(ws, (me + p) % n, par)[(int64_t)n * nvec + v] = o;
     }
   }
-  for (int64_t v = v0 + threadIdx.x; v < v1; v += kThreads) out[v] = lam_take(mine + (int64_t)n * nvec + v, 9);
+  for (int64_t vb = v0 + threadIdx.x; vb < v1; vb += (int64_t)kThreads * 4) {
+    uint4* slot[4];
+    uint4 got[4];
+    int m = 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t v = vb + (int64_t)u * kThreads;
+      slot[u] = mine + (int64_t)n * nvec + (v < v1 ? v : vb);
+      if (v < v1) m = u + 1;
+    }
+    lam_take_batch<4>(slot, m, got, 9);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (u < m) out[vb + (int64_t)u * kThreads] = got[u];
+  }
   symm_finish(ws, e);
 }
 

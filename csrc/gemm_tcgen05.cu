@@ -585,12 +585,21 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 const size_t xoff = ((size_t)xtile * NG + cg0 + u) * (BM * 16) + (size_t)f * 16;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[u][j] = 0.f;
-                for (int r = 0; r < a.ws.nranks; ++r) {  // rank order: bit-identical on every rank
-                  float t8[8];
-                  // self-validating vector: wait for it, re-arm the slot (no flags, no fences)
-                  unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)r * ar_slot_bytes + xoff), 31), t8);
+                // self-validating vectors: wait for all ranks' copies together, re-arm the slots (no flags, no fences)
+                uint4* slot[kSymmMaxRanks];
+                uint4 got[kSymmMaxRanks];
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) v[u][j] += t8[j];
+                for (int r = 0; r < kSymmMaxRanks; ++r)
+                  slot[r] = reinterpret_cast<uint4*>(mine + (size_t)(r < a.ws.nranks ? r : 0) * ar_slot_bytes + xoff);
+                lam_take_batch<kSymmMaxRanks>(slot, a.ws.nranks, got, 31);
+#pragma unroll
+                for (int r = 0; r < kSymmMaxRanks; ++r) {  // rank order: bit-identical on every rank
+                  if (r < a.ws.nranks) {
+                    float t8[8];
+                    unpack8<T>(got[r], t8);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[u][j] += t8[j];
+                  }
                 }
               }
             }
@@ -629,6 +638,42 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
 // and runs the epilogue / fused all-reduce for that slice.  No global workspace, no atomics,
 // no fences: the fix-up costs ~1 us instead of several L2 round trips.
 // ======================================================================================
+// Cluster split-K: sum of the S CTAs' fp32 partials of up to two (column group, feature) items of the tile.  All
+// DSMEM loads of both items are in flight before the first is consumed -- the reduce is bound by the DSMEM round
+// trip, not by its bandwidth -- and the sum runs in CTA order (deterministic).
+__device__ __forceinline__ void dsmem_reduce_pair(uint32_t stage_u32, int S, int item0, int item1, bool two,
+                                                  float (&v0)[8], float (&v1)[8]) {
+  const uint32_t off0 = (uint32_t)((((item0 / BM) * 2) * BM + item0 % BM) * 16);
+  const uint32_t off1 = (uint32_t)((((item1 / BM) * 2) * BM + item1 % BM) * 16);
+  float4 lo0[8], hi0[8], lo1[8], hi1[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    if (q < S) {
+      const uint32_t b0 = mapa_shared(stage_u32 + off0, (uint32_t)q);
+      lo0[q] = ld_dsmem_f4(b0);
+      hi0[q] = ld_dsmem_f4(b0 + BM * 16);
+      if (two) {
+        const uint32_t b1 = mapa_shared(stage_u32 + off1, (uint32_t)q);
+        lo1[q] = ld_dsmem_f4(b1);
+        hi1[q] = ld_dsmem_f4(b1 + BM * 16);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v0[j] = v1[j] = 0.f;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    if (q < S) {
+      v0[0] += lo0[q].x; v0[1] += lo0[q].y; v0[2] += lo0[q].z; v0[3] += lo0[q].w;
+      v0[4] += hi0[q].x; v0[5] += hi0[q].y; v0[6] += hi0[q].z; v0[7] += hi0[q].w;
+      if (two) {
+        v1[0] += lo1[q].x; v1[1] += lo1[q].y; v1[2] += lo1[q].z; v1[3] += lo1[q].w;
+        v1[4] += hi1[q].x; v1[5] += hi1[q].y; v1[6] += hi1[q].z; v1[7] += hi1[q].w;
+      }
+    }
+  }
+}
+
 template <typename T, int BN>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
@@ -760,29 +805,13 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
       uint8_t* part = symm_buf<uint8_t>(a.ws, a.ws.rank, par);
       const size_t tile_off = (size_t)tile * NG * BM * 16;
 #pragma unroll 1
-      for (int it = epi_tid; it < my_items; it += 128) {
-        const int item = r * per + it;
-        const uint32_t off = (uint32_t)((((item / BM) * 2) * BM + item % BM) * 16);
-        float v8[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v8[j] = 0.f;
-        float4 lo[8], hi[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          if (q < S) {
-            const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
-            lo[q] = ld_dsmem_f4(base);
-            hi[q] = ld_dsmem_f4(base + BM * 16);
-          }
-        }
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          if (q < S) {
-            v8[0] += lo[q].x; v8[1] += lo[q].y; v8[2] += lo[q].z; v8[3] += lo[q].w;
-            v8[4] += hi[q].x; v8[5] += hi[q].y; v8[6] += hi[q].z; v8[7] += hi[q].w;
-          }
-        }
-        *reinterpret_cast<uint4*>(part + tile_off + (size_t)item * 16) = pack8<T>(v8);
+      for (int it0 = epi_tid; it0 < my_items; it0 += 256) {
+        const bool two = it0 + 128 < my_items;
+        const int item0 = r * per + it0, item1 = two ? item0 + 128 : item0;
+        float va[8], vb[8];
+        dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
+        *reinterpret_cast<uint4*>(part + tile_off + (size_t)item0 * 16) = pack8<T>(va);
+        if (two) *reinterpret_cast<uint4*>(part + tile_off + (size_t)item1 * 16) = pack8<T>(vb);
       }
       epi_bar();
       if (epi_tid == 0) {
@@ -829,30 +858,16 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
       const int sub = (my_items + t - 1) / t;
       const size_t tile_off = (size_t)tile * NG * BM * 16;
 #pragma unroll 1
-      for (int it = epi_tid; it < my_items; it += 128) {
-        const int item = r * per + it;
-        const uint32_t off = (uint32_t)((((item / BM) * 2) * BM + item % BM) * 16);
-        float v8[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v8[j] = 0.f;
-        float4 lo[8], hi[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          if (q < S) {
-            const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
-            lo[q] = ld_dsmem_f4(base);
-            hi[q] = ld_dsmem_f4(base + BM * 16);
-          }
-        }
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          if (q < S) {
-            v8[0] += lo[q].x; v8[1] += lo[q].y; v8[2] += lo[q].z; v8[3] += lo[q].w;
-            v8[4] += hi[q].x; v8[5] += hi[q].y; v8[6] += hi[q].z; v8[7] += hi[q].w;
-          }
-        }
-        *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, it / sub, par) + (size_t)me * ar_slot_bytes + tile_off +
-                                  (size_t)item * 16) = lam_sanitize<2>(pack8<T>(v8));
+      for (int it0 = epi_tid; it0 < my_items; it0 += 256) {
+        const bool two = it0 + 128 < my_items;
+        const int item0 = r * per + it0, item1 = two ? item0 + 128 : item0;
+        float va[8], vb[8];
+        dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
+        *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, it0 / sub, par) + (size_t)me * ar_slot_bytes + tile_off +
+                                  (size_t)item0 * 16) = lam_sanitize<2>(pack8<T>(va));
+        if (two)
+          *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, (it0 + 128) / sub, par) + (size_t)me * ar_slot_bytes + tile_off +
+                                    (size_t)item1 * 16) = lam_sanitize<2>(pack8<T>(vb));
       }
       if (threadIdx.x == 64) LLMSS_STAMP(2);
       uint8_t* mine = symm_lam<uint8_t>(a.ws, me, par);
@@ -862,14 +877,23 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const int li = me * sub + i;
         if (li >= my_items) break;
         const size_t xoff = tile_off + (size_t)(r * per + li) * 16;
+        uint4* slot[kSymmMaxRanks];
+        uint4 got[kSymmMaxRanks];
+#pragma unroll
+        for (int q = 0; q < kSymmMaxRanks; ++q)
+          slot[q] = reinterpret_cast<uint4*>(mine + (size_t)(q < t ? q : 0) * ar_slot_bytes + xoff);
+        lam_take_batch<kSymmMaxRanks>(slot, t, got, 46);  // all t contributions polled together
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        for (int q = 0; q < t; ++q) {  // rank order
-          float t8[8];
-          unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)q * ar_slot_bytes + xoff), 46), t8);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] += t8[j];
+        for (int q = 0; q < kSymmMaxRanks; ++q) {  // rank order
+          if (q < t) {
+            float t8[8];
+            unpack8<T>(got[q], t8);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += t8[j];
+          }
         }
         const uint4 vec = lam_sanitize<2>(pack8<T>(acc));
         if (a.ws.mc_base != nullptr) {
@@ -880,71 +904,92 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
             *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, (me + p) % t, par) + res_off + xoff) = vec;
         }
       }
+      // results: up to four items per thread are awaited together
 #pragma unroll 1
-      for (int it = epi_tid; it < my_items; it += 128) {
-        const int item = r * per + it;
-        const int cg = item / BM, f = item % BM;
-        const int n = tn * BM + f;
-        float v[1][8], rv[1][8];
-        epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the wait
-        unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + res_off + tile_off + (size_t)item * 16), 47), v[0]);
-        const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-        store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+      for (int it0 = epi_tid; it0 < my_items; it0 += 4 * 128) {
+        uint4* slot[4];
+        uint4 got[4];
+        float rv[4][8];
+        int m = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int it = it0 + u * 128;
+          const int item = r * per + (it < my_items ? it : it0);
+          slot[u] = reinterpret_cast<uint4*>(mine + res_off + tile_off + (size_t)item * 16);
+          if (it < my_items) {
+            m = u + 1;
+            epilogue_load_res8<T>(a, rv[u], tn * BM + item % BM, tm * BN + (item / BM) * 8, lane, a.M);  // ahead of the wait
+          }
+        }
+        lam_take_batch<4>(slot, m, got, 47);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (u < m) {
+            const int item = r * per + it0 + u * 128;
+            const int cg = item / BM, f = item % BM;
+            const int n = tn * BM + f;
+            float v[1][8], rv1[1][8];
+            unpack8<T>(got[u], v[0]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) rv1[0][j] = rv[u][j];
+            const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+            store_chunk<T, 1>(a, v, rv1, n, tm * BN + cg * 8, lane, bval, a.M);
+          }
+        }
       }
     }
     const int n_pass = a.ar >= 3 ? 0 : (a.ar ? 2 : 1);
 #pragma unroll 1
     for (int pass = 0; pass < n_pass; ++pass) {
 #pragma unroll 1
-      for (int it = epi_tid; it < my_items; it += 128) {
-        const int item = r * per + it;
-        const int cg = item / BM, f = item % BM;
-        const int n = tn * BM + f;
-        const size_t xoff = ((size_t)tile * NG + cg) * (BM * 16) + (size_t)f * 16;
-        float v[1][8], rv[1][8];
-        if (pass == n_pass - 1) epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the reduction
+      for (int it0 = epi_tid; it0 < my_items; it0 += 256) {
+        const bool two = it0 + 128 < my_items;
+        float vv[2][8];
+        if (pass == 0) dsmem_reduce_pair(stage_u32, S, r * per + it0, r * per + (two ? it0 + 128 : it0), two, vv[0], vv[1]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[0][j] = 0.f;
-        if (pass == 0) {
-          const uint32_t off = (uint32_t)(((cg * 2) * BM + f) * 16);
-          // all peers' partials are requested before the first one is consumed: one DSMEM round trip per
-          // item instead of one per peer (the reduce was 2 of the ~3 us epilogue of the TP=8 decode GEMMs)
-          float4 lo[8], hi[8];
+        for (int u = 0; u < 2; ++u) {
+          if (u == 1 && !two) break;
+          const int item = r * per + it0 + u * 128;
+          const int cg = item / BM, f = item % BM;
+          const int n = tn * BM + f;
+          const size_t xoff = ((size_t)tile * NG + cg) * (BM * 16) + (size_t)f * 16;
+          float v[1][8], rv[1][8];
+          if (pass == n_pass - 1) epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the wait
+          if (pass == 0) {
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            if (q < S) {
-              const uint32_t base = mapa_shared(stage_u32 + off, (uint32_t)q);
-              lo[q] = ld_dsmem_f4(base);
-              hi[q] = ld_dsmem_f4(base + BM * 16);
-            }
-          }
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {  // CTA order: deterministic
-            if (q < S) {
-              v[0][0] += lo[q].x; v[0][1] += lo[q].y; v[0][2] += lo[q].z; v[0][3] += lo[q].w;
-              v[0][4] += hi[q].x; v[0][5] += hi[q].y; v[0][6] += hi[q].z; v[0][7] += hi[q].w;
-            }
-          }
-          if (a.ar) {
-            const uint4 vec = lam_sanitize<2>(pack8<T>(v[0]));
+            for (int j = 0; j < 8; ++j) v[0][j] = vv[u][j];
+            if (a.ar) {
+              const uint4 vec = lam_sanitize<2>(pack8<T>(v[0]));
 #pragma unroll 1
-            for (int p = 0; p < a.ws.nranks; ++p) {
-              const int peer = (a.ws.rank + p) % a.ws.nranks;
-              *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+              for (int p = 0; p < a.ws.nranks; ++p) {
+                const int peer = (a.ws.rank + p) % a.ws.nranks;
+                *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, peer, par) + (size_t)a.ws.rank * ar_slot_bytes + xoff) = vec;
+              }
+              continue;
             }
-            continue;
-          }
-        } else {
-          uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
-          for (int q = 0; q < a.ws.nranks; ++q) {  // rank order: bit-identical on every rank
-            float t8[8];
-            unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + (size_t)q * ar_slot_bytes + xoff), 43), t8);
+          } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[0][j] += t8[j];
+            for (int j = 0; j < 8; ++j) v[0][j] = 0.f;
+            uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
+            uint4* slot[kSymmMaxRanks];
+            uint4 got[kSymmMaxRanks];
+#pragma unroll
+            for (int q = 0; q < kSymmMaxRanks; ++q)
+              slot[q] = reinterpret_cast<uint4*>(mine + (size_t)(q < a.ws.nranks ? q : 0) * ar_slot_bytes + xoff);
+            lam_take_batch<kSymmMaxRanks>(slot, a.ws.nranks, got, 43);  // polled together, not one round trip per rank
+#pragma unroll
+            for (int q = 0; q < kSymmMaxRanks; ++q) {  // rank order: bit-identical on every rank
+              if (q < a.ws.nranks) {
+                float t8[8];
+                unpack8<T>(got[q], t8);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[0][j] += t8[j];
+              }
+            }
           }
+          const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+          store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
         }
-        const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-        store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
       }
     }
   }

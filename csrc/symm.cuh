@@ -113,6 +113,31 @@ __device__ __forceinline__ void mc_st_release_u32(uint32_t* mc_addr, uint32_t v)
   asm volatile("multimem.st.release.sys.global.b32 [%0], %1;" ::"l"(mc_addr), "r"(v) : "memory");
 }
 
+// The same for up to N vectors at once: all loads are issued before any is examined, and only the vectors that
+// are still missing are polled again.  A relaxed system-scope load is a full L2 round trip (~0.7 us) even when the
+// data is already there, so taking the t contributions of an all-reduce one after the other costs t round trips;
+// taken together they cost one after the last arrival.  slot[i] for i >= n is ignored (alias any valid slot).
+template <int N>
+__device__ __forceinline__ void lam_take_batch(uint4* const (&slot)[N], int n, uint4 (&v)[N], int tag) {
+  uint32_t pending = (n >= 32) ? 0xffffffffu : ((1u << n) - 1u);
+  SpinGuard g;
+  while (true) {
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+      if ((pending >> i) & 1u) v[i] = ld_relaxed_sys_v4(slot[i]);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      if (((pending >> i) & 1u) &&
+          !(v[i].x == kLamSentinel || v[i].y == kLamSentinel || v[i].z == kLamSentinel || v[i].w == kLamSentinel))
+        pending &= ~(1u << i);
+    }
+    if (pending == 0) break;
+    if (!g.ok()) spin_timeout_trap("lamport vector wait", tag, (int)pending);
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+    if (i < n) *slot[i] = make_uint4(kLamSentinel, kLamSentinel, kLamSentinel, kLamSentinel);
+}
 // &flag[set][slot][0] inside rank `rank`'s region; index by source rank.
 __device__ __forceinline__ uint32_t* symm_flag(const SymmWs& ws, int rank, int set, int slot) {
   return reinterpret_cast<uint32_t*>(ws.peer_base[rank] + (size_t)set * kSymmFlagSetBytes) +

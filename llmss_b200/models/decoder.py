@@ -91,12 +91,20 @@ class DecoderLM(nn.Module):
         self.rank = self.comm.rank
         self.device = torch.device(device)
         self.dtype = dtype
-        if spec.n_heads % self.tp != 0:
-            raise ValueError(f"`num_attention_heads` must be divisible by `num_shards` (got `num_attention_heads`: "
-                             f"{spec.n_heads} and `num_shards`: {self.tp})")
-        self.hq = spec.n_heads // self.tp
+        # Heads that do not divide the shard count (GPT-2 XL: 25 heads at TP=2; the reference raises,
+        # gptj_modeling.py:78-83) are padded with null heads at the end: their q/k/v rows and out-proj columns are
+        # zero, so they attend uniformly over zero values and add nothing; no masking is needed anywhere.
+        self.hq = -(-spec.n_heads // self.tp)
+        self.heads_padded = self.hq * self.tp
+        if self.heads_padded != spec.n_heads and spec.n_kv_heads not in (spec.n_heads, 1):
+            raise ValueError(f"`num_attention_heads` must be divisible by `num_shards` for grouped-query models (got "
+                             f"`num_attention_heads`: {spec.n_heads}, `num_key_value_heads`: {spec.n_kv_heads} and "
+                             f"`num_shards`: {self.tp})")
         # KV heads: shard when there are enough, else replicate (MQA rule, gpt_bigcode_modeling.py:148-155)
-        if spec.n_kv_heads >= self.tp:
+        if spec.n_kv_heads == spec.n_heads:
+            self.hkv = self.hq                      # multi-head: K/V heads follow (and are padded like) the q heads
+            self.kv_head_start = self.rank * self.hkv
+        elif spec.n_kv_heads >= self.tp:
             if spec.n_kv_heads % self.tp != 0:
                 raise ValueError(f"num_key_value_heads={spec.n_kv_heads} not divisible by {self.tp} shards")
             self.hkv = spec.n_kv_heads // self.tp
@@ -339,6 +347,49 @@ class ShardReader:
         if transposed:
             return self.w.get_range(name, 0, start, stop).t().contiguous()
         return self.w.get_range(name, 1, start, stop).contiguous()
+
+    def _pad(self, t, n, dim):
+        if t.shape[dim] == n:
+            return t
+        shape = list(t.shape)
+        shape[dim] = n - t.shape[dim]
+        return torch.cat([t, torch.zeros(shape, dtype=t.dtype, device=t.device)], dim=dim).contiguous()
+
+    def rows_padded(self, name, start, stop, limit, transposed=False):
+        """rows() for head-sharded projections: rows at or beyond ``limit`` (the end of the real heads) are zero."""
+        shape = self.w.get_shape(name)
+        other = None if len(shape) == 1 else (shape[0] if transposed else shape[1])
+        hi = min(stop, limit)
+        if start >= hi:
+            z = (stop - start,) if other is None else (stop - start, other)
+            return torch.zeros(z, dtype=self.m.dtype, device=self.m.device)
+        return self._pad(self.rows(name, start, hi, transposed), stop - start, 0)
+
+    def cols_padded(self, name, start, stop, limit, transposed=False):
+        """cols() for the attention output projection: input columns of null heads are zero."""
+        shape = self.w.get_shape(name)
+        out = shape[1] if transposed else shape[0]
+        hi = min(stop, limit)
+        if start >= hi:
+            return torch.zeros(out, stop - start, dtype=self.m.dtype, device=self.m.device)
+        return self._pad(self.cols(name, start, hi, transposed), stop - start, 1)
+
+    def q_rows(self, name, base=0, transposed=False):
+        """This rank's q-head rows of a projection whose q block starts at row ``base``."""
+        m = self.m
+        lo = base + m.rank * m.q_dim
+        return self.rows_padded(name, lo, lo + m.q_dim, base + m.spec.n_heads * m.d, transposed)
+
+    def kv_rows(self, name, base=0, transposed=False):
+        """This rank's k (or v) head rows of a projection whose k (v) block starts at row ``base``."""
+        m = self.m
+        lo = base + m.kv_head_start * m.d
+        return self.rows_padded(name, lo, lo + m.kv_dim, base + m.spec.n_kv_heads * m.d, transposed)
+
+    def o_cols(self, name, transposed=False):
+        m = self.m
+        lo = m.rank * m.q_dim
+        return self.cols_padded(name, lo, lo + m.q_dim, m.spec.n_heads * m.d, transposed)
 
     def shard_rows(self, name, total, transposed=False):
         blk = total // self.tp

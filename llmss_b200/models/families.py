@@ -45,8 +45,9 @@ def load_gptj(m: DecoderLM, w):
     for i in range(s.n_layers):
         p, L = f"transformer.h.{i}", LayerWeights()
         L.ln1_w, L.ln1_b = r.full(f"{p}.ln_1.weight"), r.full(f"{p}.ln_1.bias")
-        L.wqkv = torch.cat([r.shard_rows(f"{p}.attn.{n}.weight", H) for n in ("q_proj", "k_proj", "v_proj")]).contiguous()
-        L.wo = r.shard_cols(f"{p}.attn.out_proj.weight", H)
+        L.wqkv = torch.cat([r.q_rows(f"{p}.attn.q_proj.weight"), r.kv_rows(f"{p}.attn.k_proj.weight"),
+                            r.kv_rows(f"{p}.attn.v_proj.weight")]).contiguous()
+        L.wo = r.o_cols(f"{p}.attn.out_proj.weight")
         L.wup, L.bup = r.shard_rows(f"{p}.mlp.fc_in.weight", s.ffn), r.shard_rows(f"{p}.mlp.fc_in.bias", s.ffn)
         L.wdown, L.bdown = r.shard_cols(f"{p}.mlp.fc_out.weight", s.ffn), r.full(f"{p}.mlp.fc_out.bias")
         m.layers.append(L)
@@ -76,14 +77,12 @@ def load_bigcode(m: DecoderLM, w):
         L.ln1_w, L.ln1_b = r.full(f"{p}.ln_1.weight"), r.full(f"{p}.ln_1.bias")
         L.ln2_w, L.ln2_b = r.full(f"{p}.ln_2.weight"), r.full(f"{p}.ln_2.bias")
         # fused c_attn rows: [q (H) | k (kvw) | v (kvw)]; q head-sharded, kv sharded or replicated (lazy slices, Q9)
-        k0 = H + m.kv_head_start * d
-        v0 = H + kvw + m.kv_head_start * d
-        parts_w, parts_b = [], []
-        for lo, hi in ((m.rank * m.q_dim, (m.rank + 1) * m.q_dim), (k0, k0 + m.kv_dim), (v0, v0 + m.kv_dim)):
-            parts_w.append(r.rows(f"{p}.attn.c_attn.weight", lo, hi))
-            parts_b.append(r.rows(f"{p}.attn.c_attn.bias", lo, hi))
+        parts_w = [r.q_rows(f"{p}.attn.c_attn.weight"), r.kv_rows(f"{p}.attn.c_attn.weight", H),
+                   r.kv_rows(f"{p}.attn.c_attn.weight", H + kvw)]
+        parts_b = [r.q_rows(f"{p}.attn.c_attn.bias"), r.kv_rows(f"{p}.attn.c_attn.bias", H),
+                   r.kv_rows(f"{p}.attn.c_attn.bias", H + kvw)]
         L.wqkv, L.bqkv = torch.cat(parts_w).contiguous(), torch.cat(parts_b).contiguous()
-        L.wo, L.bo = r.shard_cols(f"{p}.attn.c_proj.weight", H), r.full(f"{p}.attn.c_proj.bias")
+        L.wo, L.bo = r.o_cols(f"{p}.attn.c_proj.weight"), r.full(f"{p}.attn.c_proj.bias")
         L.wup, L.bup = r.shard_rows(f"{p}.mlp.c_fc.weight", s.ffn), r.shard_rows(f"{p}.mlp.c_fc.bias", s.ffn)
         L.wdown, L.bdown = r.shard_cols(f"{p}.mlp.c_proj.weight", s.ffn), r.full(f"{p}.mlp.c_proj.bias")
         m.layers.append(L)
@@ -111,13 +110,11 @@ def load_gpt2(m: DecoderLM, w):
         L.ln1_w, L.ln1_b = r.full(f"{p}.ln_1.weight"), r.full(f"{p}.ln_1.bias")
         L.ln2_w, L.ln2_b = r.full(f"{p}.ln_2.weight"), r.full(f"{p}.ln_2.bias")
         # Conv1D: stored [in, out]; c_attn out = [q | k | v], each H wide
-        ws, bs = [], []
-        for j in range(3):
-            lo = j * H + m.rank * m.q_dim
-            ws.append(r.rows(f"{p}.attn.c_attn.weight", lo, lo + m.q_dim, transposed=True))
-            bs.append(r.rows(f"{p}.attn.c_attn.bias", lo, lo + m.q_dim))
+        ws = [r.q_rows(f"{p}.attn.c_attn.weight", 0, transposed=True), r.kv_rows(f"{p}.attn.c_attn.weight", H, transposed=True),
+              r.kv_rows(f"{p}.attn.c_attn.weight", 2 * H, transposed=True)]
+        bs = [r.q_rows(f"{p}.attn.c_attn.bias", 0), r.kv_rows(f"{p}.attn.c_attn.bias", H), r.kv_rows(f"{p}.attn.c_attn.bias", 2 * H)]
         L.wqkv, L.bqkv = torch.cat(ws).contiguous(), torch.cat(bs).contiguous()
-        L.wo, L.bo = r.shard_cols(f"{p}.attn.c_proj.weight", H, transposed=True), r.full(f"{p}.attn.c_proj.bias")
+        L.wo, L.bo = r.o_cols(f"{p}.attn.c_proj.weight", transposed=True), r.full(f"{p}.attn.c_proj.bias")
         L.wup = r.shard_rows(f"{p}.mlp.c_fc.weight", s.ffn, transposed=True)
         L.bup = r.shard_rows(f"{p}.mlp.c_fc.bias", s.ffn)
         L.wdown, L.bdown = r.shard_cols(f"{p}.mlp.c_proj.weight", s.ffn, transposed=True), r.full(f"{p}.mlp.c_proj.bias")
@@ -147,11 +144,13 @@ def load_opt(m: DecoderLM, w):
         p, L = f"{pre}layers.{i}", LayerWeights()
         L.ln1_w, L.ln1_b = r.full(f"{p}.self_attn_layer_norm.weight"), r.full(f"{p}.self_attn_layer_norm.bias")
         L.ln2_w, L.ln2_b = r.full(f"{p}.final_layer_norm.weight"), r.full(f"{p}.final_layer_norm.bias")
-        names = ("q_proj", "k_proj", "v_proj")
-        L.wqkv = torch.cat([r.shard_rows(f"{p}.self_attn.{n}.weight", H) for n in names]).contiguous()
-        if w.has(f"{p}.self_attn.q_proj.bias"):
-            L.bqkv = torch.cat([r.shard_rows(f"{p}.self_attn.{n}.bias", H) for n in names]).contiguous()
-        L.wo, L.bo = r.shard_cols(f"{p}.self_attn.out_proj.weight", H), r.maybe(f"{p}.self_attn.out_proj.bias")
+        sa = f"{p}.self_attn"
+        L.wqkv = torch.cat([r.q_rows(f"{sa}.q_proj.weight"), r.kv_rows(f"{sa}.k_proj.weight"),
+                            r.kv_rows(f"{sa}.v_proj.weight")]).contiguous()
+        if w.has(f"{sa}.q_proj.bias"):
+            L.bqkv = torch.cat([r.q_rows(f"{sa}.q_proj.bias"), r.kv_rows(f"{sa}.k_proj.bias"),
+                                r.kv_rows(f"{sa}.v_proj.bias")]).contiguous()
+        L.wo, L.bo = r.o_cols(f"{sa}.out_proj.weight"), r.maybe(f"{sa}.out_proj.bias")
         L.wup = r.shard_rows(f"{p}.fc1.weight", s.ffn)
         L.bup = r.shard_rows(f"{p}.fc1.bias", s.ffn) if w.has(f"{p}.fc1.bias") else None
         L.wdown, L.bdown = r.shard_cols(f"{p}.fc2.weight", s.ffn), r.maybe(f"{p}.fc2.bias")
@@ -184,13 +183,13 @@ def load_llama(m: DecoderLM, w):
     for i in range(s.n_layers):
         p, L = f"model.layers.{i}", LayerWeights()
         L.ln1_w, L.ln2_w = r.full(f"{p}.input_layernorm.weight"), r.full(f"{p}.post_attention_layernorm.weight")
-        k0 = m.kv_head_start * d
-        ranges = (("q_proj", m.rank * m.q_dim, (m.rank + 1) * m.q_dim), ("k_proj", k0, k0 + m.kv_dim),
-                  ("v_proj", k0, k0 + m.kv_dim))
-        L.wqkv = torch.cat([r.rows(f"{p}.self_attn.{n}.weight", lo, hi) for n, lo, hi in ranges]).contiguous()
-        if w.has(f"{p}.self_attn.q_proj.bias"):
-            L.bqkv = torch.cat([r.rows(f"{p}.self_attn.{n}.bias", lo, hi) for n, lo, hi in ranges]).contiguous()
-        L.wo, L.bo = r.shard_cols(f"{p}.self_attn.o_proj.weight", s.n_heads * d), r.maybe(f"{p}.self_attn.o_proj.bias")
+        sa = f"{p}.self_attn"
+        L.wqkv = torch.cat([r.q_rows(f"{sa}.q_proj.weight"), r.kv_rows(f"{sa}.k_proj.weight"),
+                            r.kv_rows(f"{sa}.v_proj.weight")]).contiguous()
+        if w.has(f"{sa}.q_proj.bias"):
+            L.bqkv = torch.cat([r.q_rows(f"{sa}.q_proj.bias"), r.kv_rows(f"{sa}.k_proj.bias"),
+                                r.kv_rows(f"{sa}.v_proj.bias")]).contiguous()
+        L.wo, L.bo = r.o_cols(f"{sa}.o_proj.weight"), r.maybe(f"{sa}.o_proj.bias")
         L.wup = interleave_gate_up(r.shard_rows(f"{p}.mlp.gate_proj.weight", s.ffn), r.shard_rows(f"{p}.mlp.up_proj.weight", s.ffn))
         if w.has(f"{p}.mlp.gate_proj.bias"):
             L.bup = interleave_gate_up(r.shard_rows(f"{p}.mlp.gate_proj.bias", s.ffn), r.shard_rows(f"{p}.mlp.up_proj.bias", s.ffn))

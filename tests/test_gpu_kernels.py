@@ -325,11 +325,16 @@ def test_sample_plain_multinomial_never_falls_through():
     one = torch.ones(B, device="cuda")
     for step in range(50):
         rng = torch.tensor([[77 + b, step] for b in range(B)], dtype=torch.int32, device="cuda")
+        rng0 = rng.clone()   # the kernel advances the counter in place
         got = cu.sample(logits, z, one, z, one, rng, vocab=V)
         assert int((got == V - 1).sum()) == 0, f"step {step}: fell through to the last token"
+        rng = rng0
         if step < 4:
-            want, lo, hi = _oracle_choices(lambda r, sh: R.sample(logits, z, one, z, one, r, vocab=V, u_shift=sh), rng)
-            _check_tokens(got, want, lo, hi, f"multinomial step {step}")
+            # index-order CDF over 50k tokens, most of them with weights near the fp32 rounding of the running sum:
+            # the pick may move by a few tokens, but it must stay between the oracle's picks for u -+ 2e-4
+            _, lo, hi = _oracle_choices(lambda r, sh: R.sample(logits, z, one, z, one, r, vocab=V, u_shift=sh), rng)
+            g = got.long().cpu()
+            assert bool(((g >= lo) & (g <= hi)).all()), f"multinomial step {step}: picks outside the oracle's bracket\n{g}\n{lo}\n{hi}"
 
 
 @pytest.mark.parametrize("t", [2, 4, 8])

@@ -158,3 +158,76 @@ def test_consumer_plan_exchange_is_small_and_identical_on_every_rank(tmp_path):
     # polled step -- not a 1 MiB plan per generated token
     assert a["bytes"] == b["bytes"] and a["bytes"] < 4096 + 16 * a["steps"]
     assert a["bytes"] <= 4096 + 16 * (a["steps"] // 4 + 8)            # decode steps between polls exchange nothing
+
+
+# ------------------------------------------------------------------------------------------------
+# head counts that do not divide the shard count (BASELINE config 2 names GPT-2 XL, 25 heads, at TP=2)
+def _padded_heads_worker(rank, world, port, path, ids, out_file):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    os.environ.pop("DEBUG", None)
+    from transformers import AutoConfig
+
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+    from llmss_b200.models import MODEL_REGISTRY
+    from llmss_b200.utils.dist import initialize_torch_distributed
+    from llmss_b200.utils.hub import weight_files
+    from llmss_b200.utils.weights import Weights
+
+    pg, _, _ = initialize_torch_distributed()
+    cfg = AutoConfig.from_pretrained(path)
+    model = MODEL_REGISTRY[cfg.model_type](cfg, Weights(weight_files(path), "cpu", torch.float32, pg)).eval()
+    assert model.core.hq == 3 and model.core.heads_padded == 6      # 5 heads -> 3 per rank, the last one is null
+    out = model(ids, use_cache=True)
+    step = model(ids[:, :1], past_key_values=out.past_key_values, use_cache=True)
+    toks = Engine(model, max_batch=2, max_seq_len=48).generate([ids[0].tolist(), ids[1, :5].tolist()],
+                                                               SamplingParams(max_new_tokens=6, is_greedy=True))
+    torch.save({"logits": out.logits, "step": step.logits, "toks": toks}, f"{out_file}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("family", ["gpt2", "gptj", "opt"])
+def test_indivisible_head_count_is_padded(family, tmp_path):
+    """5 heads on 2 ranks: each rank holds 3 head slots, the sixth is a null head (zero q/k/v rows, zero out-proj
+    columns).  Logits, cached step and greedy tokens must equal TP=1 (the reference raises here)."""
+    from transformers import AutoConfig, GPT2Config, GPT2LMHeadModel, GPTJConfig, GPTJForCausalLM, OPTConfig, OPTForCausalLM
+
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+    from llmss_b200.models import MODEL_REGISTRY
+    from llmss_b200.utils.dist import FakeGroup
+    from llmss_b200.utils.hub import weight_files
+    from llmss_b200.utils.weights import Weights
+
+    torch.manual_seed(0)
+    if family == "gpt2":
+        hf = GPT2LMHeadModel(GPT2Config(vocab_size=131, n_positions=64, n_embd=80, n_layer=2, n_head=5))
+    elif family == "gptj":
+        hf = GPTJForCausalLM(GPTJConfig(vocab_size=128, n_positions=64, n_embd=80, n_layer=2, n_head=5, rotary_dim=8))
+    else:
+        hf = OPTForCausalLM(OPTConfig(vocab_size=128, hidden_size=80, num_hidden_layers=2, ffn_dim=320,
+                                      num_attention_heads=5, max_position_embeddings=64, word_embed_proj_dim=80))
+    hf = hf.eval().float()
+    with torch.no_grad():
+        for _, p in hf.named_parameters():
+            if p.dim() == 1:
+                p.add_(0.1 * torch.randn_like(p))
+    hf.save_pretrained(str(tmp_path), safe_serialization=True)
+    path = str(tmp_path)
+    conf = AutoConfig.from_pretrained(path)
+    single = MODEL_REGISTRY[conf.model_type](conf, Weights(weight_files(path), "cpu", torch.float32, FakeGroup(0, 1))).eval()
+    ids = torch.randint(0, 128, (2, 8))
+    ref = single(ids, use_cache=True)
+    with torch.no_grad():
+        assert torch.allclose(ref.logits, hf(ids).logits, atol=2e-4, rtol=1e-4)
+    ref_step = single(ids[:, :1], past_key_values=ref.past_key_values, use_cache=True)
+    ref_toks = Engine(single, max_batch=2, max_seq_len=48).generate(
+        [ids[0].tolist(), ids[1, :5].tolist()], SamplingParams(max_new_tokens=6, is_greedy=True))
+    out_file = str(tmp_path / "out")
+    mp.spawn(_padded_heads_worker, args=(2, _free_port(), path, ids, out_file), nprocs=2, join=True)
+    for r in range(2):
+        got = torch.load(f"{out_file}.{r}")
+        assert torch.allclose(got["logits"], ref.logits, atol=3e-4, rtol=1e-4), (family, r)
+        assert torch.allclose(got["step"], ref_step.logits, atol=3e-4, rtol=1e-4), (family, r)
+        assert got["toks"] == ref_toks, (family, r)

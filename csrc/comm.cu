@@ -533,7 +533,7 @@ int64_t llmss_twoshot_min_bytes() {
   static int64_t v = -1;
   if (v < 0) {
     const char* e = getenv("LLMSS_TWOSHOT_MIN_BYTES");
-    v = (e != nullptr) ? atoll(e) : (int64_t)(128 << 10);
+    v = (e != nullptr) ? atoll(e) : (int64_t)(256 << 10);
   }
   return v;
 }

@@ -34,7 +34,7 @@ def _warn_once(msg: str):
 
 
 _FUSED_PUSH_MAX = int(os.environ.get("LLMSS_FUSED_AR_MAX_PUSH", str(2 << 20)))
-_TWOSHOT_MIN = int(os.environ.get("LLMSS_TWOSHOT_MIN_BYTES", str(128 << 10)))
+_TWOSHOT_MIN = int(os.environ.get("LLMSS_TWOSHOT_MIN_BYTES", str(256 << 10)))
 _FUSED_TWOSHOT_MAX = int(os.environ.get("LLMSS_FUSED_TWOSHOT_MAX_BYTES", str(8 << 20)))
 
 

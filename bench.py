@@ -193,6 +193,13 @@ def synthetic_prompts(batch: int, prompt_len: int, vocab: int):
 BASELINE_VALUE = None  # the reference publishes no number
 
 
+def bench_config(args, world: int) -> dict:
+    """The workload description -- byte-identical in both arms (implementation details go under "details")."""
+    return {"model": f"{args.model} (random-init, HF safetensors layout)", "global_batch": args.batch,
+            "seq_len": args.prompt_len, "prompt_len": args.prompt_len, "parallelism": f"tp{world}",
+            "l2": "inputs larger than L2 (weights + KV streamed each step)"}
+
+
 # ----------------------------------------------------------------------------- our arm
 def run_ours(args, rank, world, local):
     from llmss_b200.engine.engine import Engine
@@ -288,9 +295,10 @@ def run_ours(args, rank, world, local):
         "warmup": Wm, "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "bf16" if dtype == torch.bfloat16 else "fp16", "data": "synthetic",
         "impl": "ours",
-        "config": {"model": f"{args.model} (random-init, HF safetensors layout)", "global_batch": B, "seq_len": S,
-                   "prompt_len": S, "parallelism": f"tp{world}", "l2": "inputs larger than L2 (weights + KV streamed each step)",
-                   "cuda_graph": not args.no_graph, "fused_parallel_block": eng.core.fuse_parallel},
+        "config": bench_config(args, world),
+        "details": {"cuda_graph": not args.no_graph, "fused_parallel_block": eng.core.fuse_parallel,
+                    "symmetric_heap": getattr(eng.comm.symm, "mode", None), "nvls_multicast": bool(getattr(eng.comm.symm, "has_multicast", False)),
+                    "heads_per_rank": eng.core.hq, "padded_heads": eng.core.heads_padded - eng.core.spec.n_heads},
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1), "unit": "tokens/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": round(1e3 * e2e_s / K, 4)},
@@ -319,7 +327,19 @@ def run_reference(args, rank, world, local):
     path = ensure_checkpoint(args, rank, world)
     K, Wm, B, S = args.steps, args.warmup, args.batch, args.prompt_len
     try:
-        model, process_group, config = build_reference_model(path, local)
+        from transformers import AutoConfig
+
+        mt = AutoConfig.from_pretrained(path).model_type
+        if mt in ("gptj", "gpt_bigcode"):
+            tier = "R1: unmodified reference model code"
+            model, process_group, config = build_reference_model(path, local)
+        else:
+            # the reference has no model file for this family (custom_modeling/__init__.py:4-7): its own TP layer
+            # library assembled to the same shapes (baseline/ref_r2.py)
+            from baseline.ref_r2 import build_r2_model
+
+            tier = "R2: reference library path at equal shapes (reference TP layers + ATen, no reference model file exists)"
+            model, process_group, config = build_r2_model(path, local)
     except Exception as e:  # noqa: BLE001
         if rank == 0:
             print(json.dumps({"impl": "reference", "unavailable": f"reference model build failed: {e}"[:300]}), flush=True)
@@ -344,21 +364,27 @@ def run_reference(args, rank, world, local):
     ttft = time.perf_counter() - t0
     for _ in range(Wm):
         ids, past = step(ids, past)
+    # ---- e2e: the loop as a user of generate.py runs it, tokens read back on the host every step
+    fence(world)
+    step_times = []
+    t_e0 = time.perf_counter()
+    for _ in range(K):
+        ts = time.perf_counter()
+        ids, past = step(ids, past)
+        _ = ids.cpu()
+        step_times.append(time.perf_counter() - ts)
+    fence(world)
+    e2e_s = max_over_ranks(time.perf_counter() - t_e0, world)
+    # ---- device-timed: no host read inside the event window
     fence(world)
     sampler = ClockSampler(local)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    step_times = []
-    t_e0 = time.perf_counter()
     ev0.record()
     for _ in range(K):
-        ts = time.perf_counter()
         ids, past = step(ids, past)
-        _ = ids.cpu()  # the reference decodes on the host each step only at the end; keep a D2H for the e2e number
-        step_times.append(time.perf_counter() - ts)
     ev1.record()
     fence(world)
-    e2e_s = max_over_ranks(time.perf_counter() - t_e0, world)
     clocks = sampler.stop()
     dev_ms = max_over_ranks(ev0.elapsed_time(ev1), world)
     value = B * K / (dev_ms / 1e3)
@@ -366,9 +392,8 @@ def run_reference(args, rank, world, local):
         "metric": "decode_tokens_per_s", "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": K,
         "warmup": Wm, "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "fp16", "data": "synthetic", "impl": "reference",
-        "config": {"model": f"{args.model} (random-init, HF safetensors layout)", "global_batch": B, "seq_len": S,
-                   "prompt_len": S, "parallelism": f"tp{world}", "l2": "inputs larger than L2",
-                   "shims": "accelerate.init_empty_weights stub; PreTrainedModel.get_head_mask; eager attention"},
+        "config": bench_config(args, world),
+        "details": {"tier": tier, "shims": "accelerate.init_empty_weights stub; PreTrainedModel.get_head_mask; eager attention"},
         "clocks": clocks,
         "e2e": {"value": round(B * K / e2e_s, 1), "unit": "tokens/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": B * 8, "ms_per_step": round(1e3 * e2e_s / K, 4)},

@@ -43,6 +43,10 @@ PRESETS: Dict[str, dict] = {
                      num_hidden_layers=24, ffn_dim=8192, num_attention_heads=32, max_position_embeddings=2048,
                      do_layer_norm_before=True, word_embed_proj_dim=2048, activation_function="relu",
                      tie_word_embeddings=True),
+    # GPT-2 XL: 25 heads -- not divisible by 2; BASELINE config 2 names it at TP=2 (heads are padded, models/decoder.py)
+    "gpt2-xl": dict(model_type="gpt2", architectures=["GPT2LMHeadModel"], vocab_size=50257, n_positions=1024, n_embd=1600,
+                    n_layer=48, n_head=25, activation_function="gelu_new", layer_norm_epsilon=1e-5,
+                    tie_word_embeddings=True),
     "gpt2": dict(model_type="gpt2", architectures=["GPT2LMHeadModel"], vocab_size=50257, n_positions=1024, n_embd=768,
                  n_layer=12, n_head=12, activation_function="gelu_new", layer_norm_epsilon=1e-5,
                  tie_word_embeddings=True),

@@ -161,6 +161,8 @@ class ConsumerLoop:
                 self.engine.add_request(ids, sp, request_id=rid)
         if not self.engine.has_work():
             return 0
+        t_it = time.perf_counter()
+        decode_only = not self.engine.waiting
         outs = self.engine.step()
         if self.rank != 0:
             for o in outs:
@@ -192,6 +194,8 @@ class ConsumerLoop:
                         tpot_ms=None if st is None or st.tpot is None else round(1e3 * st.tpot, 3)))
                     del self.live[o.request_id]
                     self.engine.stats.pop(o.request_id, None)
+        if decode_only:  # a whole serving iteration around a decode step (poll + share + step + replies)
+            METRICS.observe("consumer_step_seconds", time.perf_counter() - t_it)
         return len(outs)
 
     def run_forever(self):

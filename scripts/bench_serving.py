@@ -196,7 +196,15 @@ def main():
                   "config": {"model": f"{args.model} (random-init)", "batch": args.batch, "prompt_len": args.prompt_len,
                              "gen": args.gen, "parallelism": f"tp{world}", "greedy": not args.sampling}}
         result.update(json.load(open(result_file)))
-        result.update({"decode_steps_total": eng.runner.stats["decode_steps"], "plan_bytes_shared_total": loop.bytes_shared,
+        from llmss_b200.utils.metrics import METRICS
+
+        ds, ls = METRICS.quantile("decode_step_seconds", 0.5), METRICS.quantile("consumer_step_seconds", 0.5)
+        result.update({"engine_decode_step_p50_ms": None if ds is None else round(1e3 * ds, 4),
+                       "consumer_decode_iteration_p50_ms": None if ls is None else round(1e3 * ls, 4),
+                       "note": "tpot_* is per request, (last - first token) / (n - 1): it includes the prefill steps of "
+                               "requests admitted later (continuous batching); engine_decode_step is Engine.step() for a "
+                               "decode step, consumer_decode_iteration the whole serving-loop iteration around it",
+                       "decode_steps_total": eng.runner.stats["decode_steps"], "plan_bytes_shared_total": loop.bytes_shared,
                        "heap": {"mode": getattr(eng.comm.symm, "mode", None),
                                 "nvls": bool(getattr(eng.comm.symm, "has_multicast", False))}})
         print(json.dumps(result), flush=True)

@@ -43,6 +43,10 @@ struct PCfg {
 
 struct PArgs {
   const int* cu_seqlens;
+  // paged mode (queries over existing context): keys / values come from the paged cache through the block table
+  const int* seq_lens;       // [num_seqs] cached length INCLUDING this step's tokens
+  const int* block_tables;   // [num_seqs, max_blocks]
+  int max_blocks, page;      // page = tokens per cache block (16 / 32 / 64)
   void* out;
   int64_t ldo;
   int hq, hkv;
@@ -96,9 +100,16 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   }
 }
 
-template <typename T, int D>
+// PAGED = false: fresh prefill, K / V are column ranges of the packed activation (tmap).
+// PAGED = true : multi-token queries over prior context (chunked prefill, prefix reuse; the reference handles any
+//                S with a past through the same dense path, gptj_modeling.py:128-169, 229-233): K / V tiles are
+//                assembled page by page from the paged cache (tmap_k / tmap_v, one TMA box per page and 64-column
+//                chunk, addressed through the block table), which already holds this step's keys (rope_kv_write
+//                runs first).  Query i of a sequence sits at position ctx + i, ctx = seq_len - q_len.
+template <typename T, int D, bool PAGED>
 __global__ void __launch_bounds__(kThreads, 1)
-attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PArgs a) {
+attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_k,
+                    const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ PArgs a) {
   using C = PCfg<D>;
   constexpr int BN = C::BN;
   constexpr int DSUB = D / 64;   // 64-column (128-byte) sub-tiles along head_dim
@@ -131,11 +142,16 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
   const int q0 = (gridDim.x - 1 - blockIdx.x) * BM;  // first query (position within the sequence) of this CTA
   if (q0 >= len) return;           // uniform for the whole CTA
   const int kvh = head / (a.hq / a.hkv);
-  const int kv_end = min(len, q0 + BM);        // causal: keys [0, kv_end)
+  const int ctx = PAGED ? a.seq_lens[seq] - len : 0;   // tokens already in the cache before this step's queries
+  const int kv_end = min(ctx + len, ctx + q0 + BM);     // causal: keys [0, kv_end)
   const int n_tiles = (kv_end + BN - 1) / BN;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap);
+    if (PAGED) {
+      tma_prefetch_desc(&tmap_k);
+      tma_prefetch_desc(&tmap_v);
+    }
     mbar_init(bar_q, 1);
     for (int s = 0; s < C::KV_STAGES; ++s) {
       mbar_init(&bar_kfull[s], 1);
@@ -184,17 +200,40 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
         mbar_wait(&bar_kempty[stage], phase ^ 1, 50);
         if (elect_one()) {
           mbar_arrive_expect_tx(&bar_kfull[stage], C::K_BYTES);
+          if constexpr (PAGED) {
+            // BN / page boxes per 64-column chunk; 8-row multiples keep the 128B-swizzle pattern contiguous
+            const int* bt = a.block_tables + (int64_t)seq * a.max_blocks;
+            for (int pg = 0; pg < BN / a.page; ++pg) {
+              const int bi = min(a.max_blocks - 1, (j * BN) / a.page + pg);
+              const int crow = (bt[bi] * a.hkv + kvh) * a.page;
 #pragma unroll
-          for (int c = 0; c < DSUB; ++c)
-            tma_load_2d(sK + stage * C::K_BYTES + c * (BN * 128), &tmap, &bar_kfull[stage], a.k_col + kvh * D + c * 64, row, pol);
+              for (int c = 0; c < DSUB; ++c)
+                tma_load_2d(sK + stage * C::K_BYTES + c * (BN * 128) + pg * a.page * 128, &tmap_k, &bar_kfull[stage], c * 64, crow, pol);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < DSUB; ++c)
+              tma_load_2d(sK + stage * C::K_BYTES + c * (BN * 128), &tmap, &bar_kfull[stage], a.k_col + kvh * D + c * 64, row, pol);
+          }
         }
         __syncwarp();
         mbar_wait(&bar_vempty[stage], phase ^ 1, 51);
         if (elect_one()) {
           mbar_arrive_expect_tx(&bar_vfull[stage], C::V_BYTES);
+          if constexpr (PAGED) {
+            const int* bt = a.block_tables + (int64_t)seq * a.max_blocks;
+            for (int pg = 0; pg < BN / a.page; ++pg) {
+              const int bi = min(a.max_blocks - 1, (j * BN) / a.page + pg);
+              const int crow = (bt[bi] * a.hkv + kvh) * a.page;
 #pragma unroll
-          for (int c = 0; c < DSUB; ++c)
-            tma_load_2d(sV + stage * C::V_BYTES + c * (BN * 128), &tmap, &bar_vfull[stage], a.v_col + kvh * D + c * 64, row, pol);
+              for (int c = 0; c < DSUB; ++c)
+                tma_load_2d(sV + stage * C::V_BYTES + c * (BN * 128) + pg * a.page * 128, &tmap_v, &bar_vfull[stage], c * 64, crow, pol);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < DSUB; ++c)
+              tma_load_2d(sV + stage * C::V_BYTES + c * (BN * 128), &tmap, &bar_vfull[stage], a.v_col + kvh * D + c * 64, row, pol);
+          }
         }
         __syncwarp();
         if (++stage == C::KV_STAGES) { stage = 0; phase ^= 1; }
@@ -257,14 +296,15 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     // ===================== softmax / correction / epilogue: one thread per query row =====================
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;         // query row within the tile == TMEM lane
-    const int qpos = q0 + row;                   // position within the sequence
+    const int qrow = q0 + row;                   // query index within this step's tokens of the sequence
+    const int qpos = ctx + qrow;                 // absolute position (== key index of the same token)
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     float m_run = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_tiles; ++j) {
       mbar_wait(&bar_s[j & 1], (j >> 1) & 1, 70);
       tcgen05_fence_after();
       const int kbase = j * BN;
-      const bool diag = (kbase + BN - 1) > q0;   // some key of this tile may lie above the diagonal
+      const bool diag = (kbase + BN - 1) > ctx + q0;   // some key of this tile may lie above the diagonal
       // the whole S row lives in registers (one TMEM read): raw scores, masked on diagonal tiles
       float sc[BN];
 #pragma unroll
@@ -339,13 +379,13 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     mbar_wait(&bar_o[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1, 72);
     tcgen05_fence_after();
     const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
-    T* orow = reinterpret_cast<T*>(a.out) + (int64_t)(seq_start + qpos) * a.ldo + (int64_t)head * D;
+    T* orow = reinterpret_cast<T*>(a.out) + (int64_t)(seq_start + qrow) * a.ldo + (int64_t)head * D;
 #pragma unroll 1
     for (int c = 0; c < D / 32; ++c) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(tO + lane_off + c * 32, r);
       tmem_ld_wait();
-      if (qpos < len) {
+      if (qrow < len) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           float f8[8];
@@ -380,14 +420,29 @@ PFN_encodeTiled get_encode() {
   return fn;
 }
 
-template <typename T, int D>
-int launch_prefill(const CUtensorMap& tm, const PArgs& a, int num_seqs, int max_seqlen, cudaStream_t stream) {
+template <typename T, int D, bool PAGED>
+int launch_prefill(const CUtensorMap& tm, const CUtensorMap& tk, const CUtensorMap& tv, const PArgs& a, int num_seqs,
+                   int max_seqlen, cudaStream_t stream) {
   using C = PCfg<D>;
   static PerDeviceSmem configured;
-  auto kern = attn_prefill_kernel<T, D>;
+  auto kern = attn_prefill_kernel<T, D, PAGED>;
   LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
   dim3 grid((max_seqlen + BM - 1) / BM, a.hq, num_seqs);
-  LLMSS_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), (size_t)C::SMEM_BYTES, stream, tm, a));
+  LLMSS_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), (size_t)C::SMEM_BYTES, stream, tm, tk, tv, a));
+  return 0;
+}
+
+int encode_2d(CUtensorMap* tm, const void* base, int dtype, int64_t cols, int64_t rows, int64_t ld, int box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  LLMSS_REQUIRE(enc != nullptr, "attn_prefill: cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, dtype == LLMSS_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  LLMSS_REQUIRE(r == CUDA_SUCCESS, "attn_prefill: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return 0;
 }
 
@@ -442,7 +497,7 @@ LLMSS_API int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int6
   a.v_col = (int)v_col;
   a.scale_log2 = scale * 1.4426950408889634f;
   a.dtype = dtype;
-#define LLMSS_PF(T_, D_) return launch_prefill<T_, D_>(tm, a, num_seqs, max_seqlen, stream)
+#define LLMSS_PF(T_, D_) return launch_prefill<T_, D_, false>(tm, tm, tm, a, num_seqs, max_seqlen, stream)
   if (dtype == LLMSS_F16) {
     if (d == 64) LLMSS_PF(__half, 64);
     if (d == 128) LLMSS_PF(__half, 128);
@@ -453,4 +508,53 @@ LLMSS_API int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int6
     LLMSS_PF(__nv_bfloat16, 256);
   }
 #undef LLMSS_PF
+}
+
+// Multi-token queries over prior context (chunked prefill / prefix reuse / speculative verification).
+// q: [total_q, >= hq * d] query rows of the packed activation (row stride ldq); K / V: the paged caches
+// [num_blocks, hkv, block_size, d] which already contain this step's keys and values; seq_lens[i] = cached length of
+// sequence i INCLUDING its cu_q[i+1] - cu_q[i] new tokens; out may alias q.  block_size in {16, 32, 64}.
+LLMSS_API int llmss_attn_prefill_paged(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                                       const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
+                                       const int* cu_q, int num_seqs, int max_q, int total_q, int hq, int hkv, int d,
+                                       int block_size, int num_blocks, float scale, int dtype, cudaStream_t stream) {
+  LLMSS_REQUIRE(dtype == LLMSS_F16 || dtype == LLMSS_BF16, "attn_prefill_paged: dtype must be f16/bf16");
+  LLMSS_REQUIRE(d == 64 || d == 128 || d == 256, "attn_prefill_paged: head_dim=%d unsupported (64/128/256)", d);
+  LLMSS_REQUIRE(hq > 0 && hkv > 0 && hq % hkv == 0, "attn_prefill_paged: bad head grouping hq=%d hkv=%d", hq, hkv);
+  LLMSS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64, "attn_prefill_paged: block_size=%d unsupported (16/32/64)", block_size);
+  LLMSS_REQUIRE(ldo % 8 == 0 && ((uintptr_t)out % 16) == 0 && ((uintptr_t)q % 16) == 0 && (ldq * 2) % 16 == 0,
+                "attn_prefill_paged: q / out must be 16-byte aligned");
+  LLMSS_REQUIRE((int64_t)hq * d <= ldq, "attn_prefill_paged: q columns exceed the row stride");
+  if (num_seqs == 0 || total_q == 0) return 0;
+  const int bn = d >= 256 ? 64 : 128;
+  CUtensorMap tm, tk, tv;
+  if (int e = encode_2d(&tm, q, dtype, (int64_t)hq * d, total_q, ldq, bn)) return e;
+  const int64_t crow = (int64_t)num_blocks * hkv * block_size;
+  if (int e = encode_2d(&tk, k_cache, dtype, d, crow, d, block_size)) return e;
+  if (int e = encode_2d(&tv, v_cache, dtype, d, crow, d, block_size)) return e;
+  PArgs a;
+  memset(&a, 0, sizeof(a));
+  a.cu_seqlens = cu_q;
+  a.seq_lens = seq_lens;
+  a.block_tables = block_tables;
+  a.max_blocks = max_blocks;
+  a.page = block_size;
+  a.out = out;
+  a.ldo = ldo;
+  a.hq = hq;
+  a.hkv = hkv;
+  a.q_col = 0;
+  a.scale_log2 = scale * 1.4426950408889634f;
+  a.dtype = dtype;
+#define LLMSS_PP(T_, D_) return launch_prefill<T_, D_, true>(tm, tk, tv, a, num_seqs, max_q, stream)
+  if (dtype == LLMSS_F16) {
+    if (d == 64) LLMSS_PP(__half, 64);
+    if (d == 128) LLMSS_PP(__half, 128);
+    LLMSS_PP(__half, 256);
+  } else {
+    if (d == 64) LLMSS_PP(__nv_bfloat16, 64);
+    if (d == 128) LLMSS_PP(__nv_bfloat16, 128);
+    LLMSS_PP(__nv_bfloat16, 256);
+  }
+#undef LLMSS_PP
 }

@@ -76,10 +76,11 @@ class SeqState:
 class ModelRunner:
     def __init__(self, core: DecoderLM, max_batch: int = 64, max_seq_len: Optional[int] = None,
                  block_size: Optional[int] = None, num_blocks: Optional[int] = None,
-                 use_cuda_graph: Optional[bool] = None):
+                 use_cuda_graph: Optional[bool] = None, prefill_chunk: Optional[int] = None):
         self.core, self.spec = core, core.spec
         self.device, self.dtype = core.device, core.dtype
         self.max_batch = max_batch
+        self.prefill_chunk = prefill_chunk   # tokens per sequence and prefill round (None: whole prompts at once)
         self.max_seq_len = min(max_seq_len or self.spec.max_pos, self.spec.max_pos)
         if block_size is None:
             # 64-token pages = one key tile of the tcgen05 decode-attention kernel (one TMA op per K / V
@@ -184,15 +185,29 @@ class ModelRunner:
     # ------------------------------------------------------------------ prefill
     @torch.no_grad()
     def prefill(self, seqs: Sequence[SeqState]) -> List[int]:
-        """Run the prompts of ``seqs`` (packed, no padding) and sample their first tokens."""
+        """Run the prompts of ``seqs`` (packed, no padding) and sample their first tokens.
+
+        With ``prefill_chunk`` set, prompts are fed in rounds of at most that many tokens per sequence: round r
+        attends over the r * chunk tokens already in the cache (multi-token queries over prior context: the paged
+        mode of the prefill attention kernel), which bounds the activation memory of very long prompts."""
         for s in seqs:
             s.prompt = s.prompt[-(self.max_seq_len - 1):]  # left-truncate like the reference tokenizer call
             self._grow(s, len(s.prompt))
-        batch = BatchInput.build([s.prompt for s in seqs], [0] * len(seqs), [s.blocks for s in seqs],
-                                 self.block_size, self.device, max_blocks=self.max_blocks_per_seq,
-                                 pad_to=self.core.tp * 16 if self.core.tp > 1 else 1)
-        logits = self.core.forward(batch, self.kv, last_only=True)
-        B = len(seqs)
+        chunk = self.prefill_chunk or max(len(s.prompt) for s in seqs)
+        rounds = -(-max(len(s.prompt) for s in seqs) // chunk)
+        final_logits = [None] * len(seqs)
+        for r in range(rounds):
+            live = [(i, s) for i, s in enumerate(seqs) if len(s.prompt) > r * chunk]
+            batch = BatchInput.build([s.prompt[r * chunk:(r + 1) * chunk] for _, s in live], [r * chunk] * len(live),
+                                     [s.blocks for _, s in live], self.block_size, self.device,
+                                     max_blocks=self.max_blocks_per_seq,
+                                     pad_to=self.core.tp * 16 if self.core.tp > 1 else 1)
+            logits = self.core.forward(batch, self.kv, last_only=True)
+            for row, (i, s) in enumerate(live):
+                if len(s.prompt) <= (r + 1) * chunk:
+                    final_logits[i] = logits[row]
+            self.stats["prefill_tokens"] += int(batch.tokens.numel())
+        logits = torch.stack(final_logits)
         dev = self.device
         greedy = torch.tensor([int(s.params.is_greedy) for s in seqs], dtype=torch.int32, device=dev)
         temp = torch.tensor([s.params.temperature for s in seqs], dtype=torch.float32, device=dev)
@@ -203,7 +218,6 @@ class ModelRunner:
         for s, t in zip(seqs, toks):
             s.length = len(s.prompt)
             s.output.append(int(t))
-        self.stats["prefill_tokens"] += int(batch.tokens.numel())
         return [int(t) for t in toks]
 
     # ------------------------------------------------------------------ decode

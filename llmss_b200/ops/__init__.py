@@ -122,7 +122,8 @@ def attention(qkv, out, batch, k_cache, v_cache, hq, hkv, d, scale, q_off, k_off
 
     decode batches (one query per sequence) -> split-KV paged kernel (K9);
     fresh prefill (no prior context)        -> varlen causal prefill kernel (K8);
-    anything else                           -> generic gather path (oracle math).
+    multi-token queries over prior context  -> the same kernel in paged mode (K / V from the cache);
+    unsupported head sizes / page sizes     -> generic gather path (oracle math).
     """
     T = qkv.shape[0]
     q_view = qkv[:, q_off:q_off + hq * d]
@@ -141,6 +142,13 @@ def attention(qkv, out, batch, k_cache, v_cache, hq, hkv, d, scale, q_off, k_off
         elif batch.is_fresh_prefill and cu._lib.has("llmss_attn_prefill"):
             cu.attn_prefill(q_view, qkv[:, k_off:k_off + hkv * d], qkv[:, v_off:v_off + hkv * d], out_view,
                             batch.cu_q, batch.num_seqs, batch.max_q, hq, hkv, d, scale)
+            return out
+        elif (not batch.is_fresh_prefill and k_cache.shape[2] in (16, 32, 64) and k_cache.is_contiguous()
+              and v_cache.is_contiguous() and cu._lib.has("llmss_attn_prefill_paged")):
+            # multi-token queries over prior context (chunked prefill, HF-style forward with a past): same tcgen05
+            # flash kernel, K / V tiles gathered page by page from the cache through the block table
+            cu.attn_prefill_paged(q_view, k_cache, v_cache, batch.block_tables, batch.seq_lens, out_view, batch.cu_q,
+                                  batch.num_seqs, batch.max_q, hq, hkv, d, scale)
             return out
         elif batch.is_fresh_prefill:
             # LIBRARY FALLBACK (torch SDPA), only reached when the own prefill kernel is absent from

@@ -93,6 +93,9 @@ _SIGS = {
                              c_void_p, c_void_p, c_void_p]),
 }
 _OPTIONAL = {
+    "llmss_attn_prefill_paged": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64,
+                                         c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_int,
+                                         c_void_p]),
     "llmss_attn_prefill": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
                                    c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p]),
 }

@@ -234,6 +234,17 @@ def attn_prefill(q, k, v, out, cu_seqlens, num_seqs, max_seqlen, hq, hkv, d, sca
     _count()
 
 
+def attn_prefill_paged(q_view, k_cache, v_cache, block_tables, seq_lens, out_view, cu_q, num_seqs, max_q, hq, hkv, d, scale):
+    """Multi-token queries over prior context: K / V (this step's included) are read from the paged cache."""
+    lib = _lib.load()
+    rc = lib.llmss_attn_prefill_paged(_ptr(q_view), q_view.stride(0), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables),
+                                      block_tables.shape[1], _ptr(seq_lens), _ptr(out_view), out_view.stride(0), _ptr(cu_q),
+                                      num_seqs, max_q, q_view.shape[0], hq, hkv, d, k_cache.shape[2], k_cache.shape[0],
+                                      float(scale), _DT[q_view.dtype], _stream())
+    _lib.check(rc, "llmss_attn_prefill_paged")
+    _count()
+
+
 # --------------------------------------------------------------------------- embed / sample
 def embed(tokens, wte, positions=None, wpe=None, pos_offset: int = 0):
     lib = _lib.load()

@@ -98,3 +98,17 @@ def test_admission_reserves_worst_case_and_rejects_the_impossible(tmp_path):
         for o in eng2.step():
             got.setdefault(o.request_id, []).append(o.token)
     assert got[never] == [-1] and len(got[ok]) == 4
+
+
+def test_chunked_prefill_matches_whole_prompt_prefill(tmp_path):
+    """Prompts fed in rounds of 5 tokens (queries over prior context) generate what whole-prompt prefill generates."""
+    cfg, hf = make_tiny("llama", tmp_path)
+    torch.manual_seed(1)
+    prompts = [torch.randint(0, cfg.vocab_size, (n,)).tolist() for n in (17, 3, 11, 5)]
+    sp = SamplingParams(max_new_tokens=5, is_greedy=True)
+    whole = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=4, max_seq_len=64)
+    chunked = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=4, max_seq_len=64,
+                                     prefill_chunk=5)
+    a, b = whole.generate(prompts, sp), chunked.generate(prompts, sp)
+    assert a == b
+    assert a[0] == _hf_greedy(hf, prompts[0], 5)

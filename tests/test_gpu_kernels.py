@@ -440,6 +440,48 @@ def test_attn_prefill(hq, hkv, d, dtype):
     assert out[:, hq * d:].abs().sum().item() == 0
 
 
+@pytest.mark.parametrize("bs", [64, 16])
+@pytest.mark.parametrize("hq,hkv,d", [(4, 4, 256), (8, 2, 128), (6, 6, 64), (6, 1, 128)])
+def test_attn_prefill_over_context(hq, hkv, d, bs):
+    """Multi-token queries over prior context (chunked prefill / prefix reuse): K / V come from the paged cache
+    through the block table; compared with the fp32 gather oracle.  Mixes pure prefill (ctx 0), a decode-like
+    row (1 query), chunks that start and end inside pages, and a chunk longer than one query tile."""
+    cu = _cu()
+    torch.manual_seed(4)
+    dtype = torch.bfloat16
+    ctx = [0, 37, 64, 500, 129, 1000, 5]
+    new = [70, 1, 128, 300, 63, 17, 200]
+    B = len(ctx)
+    tot = [c + n for c, n in zip(ctx, new)]
+    maxb = max(-(-t // bs) for t in tot) + 1
+    nb = 1 + B * maxb
+    kc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=dtype)
+    vc = torch.randn(nb, hkv, bs, d, device="cuda", dtype=dtype)
+    perm = (torch.randperm(nb - 1) + 1).tolist()
+    bt = torch.zeros(B, maxb, dtype=torch.int32)
+    for i in range(B):
+        n = -(-tot[i] // bs)
+        bt[i, :n] = torch.tensor(perm[i * maxb:i * maxb + n], dtype=torch.int32)
+    bt = bt.cuda()
+    sl = torch.tensor(tot, dtype=torch.int32, device="cuda")
+    cu_q = torch.tensor([0] + list(torch.tensor(new).cumsum(0)), dtype=torch.int32, device="cuda")
+    T = sum(new)
+    W = 32 + hq * d
+    qbuf = torch.randn(T, W, device="cuda", dtype=dtype)
+    q = qbuf[:, 32:]
+    out = torch.zeros(T, hq * d + 16, device="cuda", dtype=dtype)
+    scale = d ** -0.5
+    cu.attn_prefill_paged(q, kc, vc, bt, sl, out[:, :hq * d], cu_q, B, max(new), hq, hkv, d, scale)
+    torch.cuda.synchronize()
+    ref = R.attention_paged(q.float().reshape(T, hq, d), kc.float(), vc.float(), bt, sl, cu_q, scale).reshape(T, hq * d)
+    _close(out[:, :hq * d], ref, 3e-2, 3e-2, "attn_prefill_paged")
+    assert out[:, hq * d:].abs().sum().item() == 0
+    # in place over q, as the decoder calls it
+    cu.attn_prefill_paged(q, kc, vc, bt, sl, q, cu_q, B, max(new), hq, hkv, d, scale)
+    torch.cuda.synchronize()
+    assert torch.equal(q, out[:, :hq * d])
+
+
 def test_attn_prefill_in_place_over_q():
     """The fused GPT-J block lets the context overwrite q inside the packed activation."""
     cu = _cu()

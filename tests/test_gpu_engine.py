@@ -5,8 +5,36 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("preset,fuse", [("gptj-tiny", True), ("gptj-tiny", False)])
-def test_engine_gpu_matches_cpu_oracle(tmp_path, preset, fuse):
+def _assert_near_argmax(path, prompts, outs, rel_margin=0.03):
+    """Every generated token must be the fp32 oracle's argmax, or within `rel_margin` x max|logit| of it, when
+    the oracle is fed the same prefix (teacher forcing): exact token equality cannot be demanded of a bf16 / fp16
+    run because near-ties flip, but nothing beyond rounding may separate the two."""
+    from transformers import AutoConfig
+
+    from llmss_b200.models import MODEL_REGISTRY
+    from llmss_b200.utils.dist import FakeGroup
+    from llmss_b200.utils.hub import weight_files
+    from llmss_b200.utils.weights import Weights
+
+    conf = AutoConfig.from_pretrained(path)
+    oracle = MODEL_REGISTRY[conf.model_type](conf, Weights(weight_files(path), "cpu", torch.float32, FakeGroup(0, 1))).eval()
+    exact = total = 0
+    for p, o in zip(prompts, outs):
+        ids = torch.tensor([list(p) + list(o)])
+        with torch.no_grad():
+            logits = oracle(ids).logits[0].float()
+        for t, tok in enumerate(o):
+            row = logits[len(p) + t - 1]
+            gap = (row.max() - row[tok]).item()
+            assert gap <= rel_margin * max(1.0, row.abs().max().item()), (p, t, tok, int(row.argmax()), gap)
+            exact += int(row.argmax()) == tok
+            total += 1
+    assert exact >= 0.9 * total, f"only {exact}/{total} tokens are the oracle's argmax"
+
+
+@pytest.mark.parametrize("preset,fuse,dtype", [("gptj-tiny", True, torch.bfloat16), ("gptj-tiny", False, torch.bfloat16),
+                                               ("gptj-tiny", True, torch.float16)])
+def test_engine_gpu_matches_cpu_oracle(tmp_path, preset, fuse, dtype):
     from llmss_b200.engine.engine import Engine
     from llmss_b200.engine.runner import SamplingParams
     from llmss_b200.utils.checkpoint import write_random_checkpoint
@@ -14,15 +42,49 @@ def test_engine_gpu_matches_cpu_oracle(tmp_path, preset, fuse):
     path = str(write_random_checkpoint(tmp_path, preset, dtype=torch.float32, device="cpu", std=0.08))
     prompts = [[3, 14, 15, 92, 65], [35, 89, 79], [32, 38, 46, 26, 43, 38, 32], [7] * 20, [1, 2]]
     sp = SamplingParams(max_new_tokens=12, is_greedy=True)
-    cpu = Engine.from_pretrained(path, device="cpu", max_batch=4, max_seq_len=128, fuse_parallel=fuse)
-    want = cpu.generate(prompts, sp)
-    gpu = Engine.from_pretrained(path, dtype=torch.float32 if False else torch.bfloat16, device="cuda", max_batch=4,
-                                 max_seq_len=128, fuse_parallel=fuse)
+    gpu = Engine.from_pretrained(path, dtype=dtype, device="cuda", max_batch=4, max_seq_len=128, fuse_parallel=fuse)
     got = gpu.generate(prompts, sp)
-    # bf16 vs fp32 can flip near-ties late in a sequence: require the first tokens to agree everywhere
-    agree = sum(g[:4] == w[:4] for g, w in zip(got, want))
-    assert agree >= len(prompts) - 1, (got, want)
     assert gpu.runner.stats["graph_replays"] > 0
+    _assert_near_argmax(path, prompts, got)
+    # enqueue-only decode steps (the device-timed bench loop) must produce what synchronous steps produce:
+    # the pinned staging ring keeps every step's inputs intact until its copy has run
+    a = Engine.from_pretrained(path, dtype=dtype, device="cuda", max_batch=4, max_seq_len=128, fuse_parallel=fuse)
+    for p in prompts[:4]:
+        a.add_request(p, SamplingParams(max_new_tokens=40, is_greedy=True))
+    a.step()                       # prefill
+    a.step()                       # binds the batch, first synchronous decode step
+    log = []
+    for _ in range(20):
+        a.runner.decode_step(sync=False, host_tokens=False)
+        log.append(a.runner.d_in[:4].clone())
+    torch.cuda.synchronize()
+    b = Engine.from_pretrained(path, dtype=dtype, device="cuda", max_batch=4, max_seq_len=128, fuse_parallel=fuse)
+    for p in prompts[:4]:
+        b.add_request(p, SamplingParams(max_new_tokens=40, is_greedy=True))
+    b.step()
+    b.step()
+    for i in range(20):
+        toks = b.runner.decode_step(sync=True)
+        assert log[i].tolist() == toks[:4], f"enqueue-only step {i} diverged from the synchronous run"
+
+
+def test_chunked_prefill_on_gpu(tmp_path):
+    """Prompts fed in 32-token rounds run the paged mode of the prefill attention kernel (queries over prior
+    context); the result must agree with whole-prompt prefill."""
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+    from llmss_b200.utils.checkpoint import write_random_checkpoint
+
+    path = str(write_random_checkpoint(tmp_path, "gptj-tiny", dtype=torch.float32, device="cpu", std=0.08))
+    g = torch.Generator().manual_seed(3)
+    prompts = [torch.randint(1, 500, (n,), generator=g).tolist() for n in (150, 33, 64, 7)]
+    sp = SamplingParams(max_new_tokens=8, is_greedy=True)
+    chunked = Engine.from_pretrained(path, dtype=torch.bfloat16, device="cuda", max_batch=4, max_seq_len=200, prefill_chunk=32)
+    got = chunked.generate(prompts, sp)
+    _assert_near_argmax(path, prompts, got)
+    whole = Engine.from_pretrained(path, dtype=torch.bfloat16, device="cuda", max_batch=4, max_seq_len=200)
+    want = whole.generate(prompts, sp)
+    assert sum(a[:4] == b[:4] for a, b in zip(got, want)) >= 3, (got, want)
 
 
 def test_engine_page_sizes_agree(tmp_path):
@@ -48,8 +110,10 @@ def test_engine_page_sizes_agree(tmp_path):
     assert same >= len(prompts) - 1, (outs[16], outs[64])
 
 
-@pytest.mark.parametrize("family", ["llama", "gpt_bigcode", "gpt2", "opt", "gptj"])
-def test_families_gpu_logits_close_to_cpu(tmp_path, family):
+@pytest.mark.parametrize("family,dtype", [("llama", torch.bfloat16), ("gpt_bigcode", torch.bfloat16), ("gpt2", torch.bfloat16),
+                                          ("opt", torch.bfloat16), ("gptj", torch.bfloat16), ("llama", torch.float16),
+                                          ("gptj", torch.float16)])
+def test_families_gpu_logits_close_to_cpu(tmp_path, family, dtype):
     """Prefill + one decode step logits on GPU (own kernels) vs the CPU oracle for every family."""
     import sys
     from pathlib import Path
@@ -71,14 +135,20 @@ def test_families_gpu_logits_close_to_cpu(tmp_path, family):
         return MODEL_REGISTRY[conf.model_type](conf, w).eval()
 
     ids = torch.randint(0, cfg.vocab_size, (3, 11))
-    cpu, gpu = load("cpu", torch.float32), load("cuda", torch.bfloat16)
+    cpu, gpu = load("cpu", torch.float32), load("cuda", dtype)
     a = cpu(ids, use_cache=True)
     b = gpu(ids.cuda(), use_cache=True)
     err = (a.logits - b.logits.float().cpu()).abs().max().item()
     scale = a.logits.abs().max().item()
-    assert err < 0.06 * max(1.0, scale), (family, err, scale)
+    assert err < 0.03 * max(1.0, scale), (family, err, scale)
     nxt = torch.randint(0, cfg.vocab_size, (3, 1))
     a2 = cpu(nxt, past_key_values=a.past_key_values, use_cache=True)
     b2 = gpu(nxt.cuda(), past_key_values=b.past_key_values, use_cache=True)
     err2 = (a2.logits - b2.logits.float().cpu()).abs().max().item()
-    assert err2 < 0.06 * max(1.0, scale), (family, err2)
+    assert err2 < 0.03 * max(1.0, scale), (family, err2)
+    # a second multi-token call with a past: queries over prior context (paged mode of the prefill kernel)
+    more = torch.randint(0, cfg.vocab_size, (3, 5))
+    a3 = cpu(more, past_key_values=a2.past_key_values, use_cache=True)
+    b3 = gpu(more.cuda(), past_key_values=b2.past_key_values, use_cache=True)
+    err3 = (a3.logits - b3.logits.float().cpu()).abs().max().item()
+    assert err3 < 0.03 * max(1.0, scale), (family, err3)

@@ -42,6 +42,7 @@ GEMM_SHAPES = [
     (1, 128, 64), (1, 4096, 4096), (8, 512, 1024), (16, 384, 256), (17, 256, 512), (32, 4096, 1024),
     (64, 12288, 4096), (64, 4096, 2560), (100, 1000, 328), (128, 2048, 2048), (200, 768, 3072),
     (256, 1024, 1024), (300, 640, 192), (1024, 4096, 4096), (4096, 512, 256),
+    (64, 28672, 4096), (64, 4096, 20480),   # the two GEMMs of the flagship decode step (GPT-J-6B, batch 64, TP=1)
 ]
 
 

@@ -65,7 +65,7 @@ def main():
                 for key in CENSUS:
                     if m.group(1).startswith(key):
                         ops[key] += 1
-        short = re.sub(r"\(.*", "", name).replace("void (anonymous namespace)::", "")
+        short = re.sub(r"\(.*", "", name.replace("void (anonymous namespace)::", ""))
         census_lines.append(f"{short:70s} " + " ".join(f"{k}={ops[k]}" for k in CENSUS if ops[k]) + f" | {len(lines)} lines")
         for stem, rx in PICK:
             if stem not in written and re.search(rx, name):

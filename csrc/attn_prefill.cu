@@ -29,15 +29,27 @@ namespace {
 constexpr int BM = 128;  // queries per CTA
 constexpr int kThreads = 224;
 
+// D = 256: one fat CTA per SM (64-key tiles, P double-buffered).  D = 128 / 64: 64-key tiles and ONE P buffer
+// shrink the CTA to <= 112 KB of shared memory and 256 TMEM columns, so TWO CTAs share an SM: eight softmax
+// warps (two per scheduler) keep the MUFU pipe and the FMA pipe busy at the same time -- with four warps and
+// 128-key tiles the kernel was bound by 128 exponentials + ~8 ALU instructions per key per thread, issued from a
+// single warp per scheduler (0.55-0.64x of the library flash kernel).  The second CTA's softmax also covers the
+// wait for "PV_{j-1} has read P" that a single P buffer introduces.
 template <int D>
 struct PCfg {
-  static constexpr int BN = (D >= 256) ? 64 : 128;          // keys per tile
+  static constexpr int BN = 64;                              // keys per tile
   static constexpr int KV_STAGES = 2;
+  static constexpr int P_BUFS = (D >= 256) ? 2 : 1;
+  static constexpr int MIN_CTAS = (D >= 256) ? 1 : 2;        // CTAs per SM the launch bounds ask for
   static constexpr int Q_BYTES = BM * D * 2;
   static constexpr int K_BYTES = BN * D * 2;
   static constexpr int V_BYTES = BN * D * 2;
   static constexpr int P_BYTES = BM * BN * 2;
-  static constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * (K_BYTES + V_BYTES) + 2 * P_BYTES + 1024 + 256;
+  // two CTAs per SM leave (228 KB - 2 x 1 KB reserved) / 2 = 115,712 bytes each: the tiles (114,688 at D = 128) plus the
+  // barriers leave 768 bytes for aligning the tile base to the 1 KiB swizzle period (the kernel traps if the
+  // dynamic segment starts at an address that needs more)
+  static constexpr int ALIGN_SLACK = (D >= 256) ? 1024 : 768;
+  static constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * (K_BYTES + V_BYTES) + P_BUFS * P_BYTES + ALIGN_SLACK + 192;
   static constexpr int TMEM_COLS = (2 * BN + D <= 256) ? 256 : 512;  // S0 at column 0, S1 at BN, O at 2*BN
 };
 
@@ -107,7 +119,7 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 //                chunk, addressed through the block table), which already holds this step's keys (rope_kv_write
 //                runs first).  Query i of a sequence sits at position ctx + i, ctx = seq_len - q_len.
 template <typename T, int D, bool PAGED>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, PCfg<D>::MIN_CTAS)
 attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ PArgs a) {
   using C = PCfg<D>;
@@ -116,11 +128,15 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
   constexpr int NSUB = BN / 64;  // 64-key sub-tiles of P along the key dimension
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  if (smem - smem_raw > C::ALIGN_SLACK) {
+    if (threadIdx.x == 0) printf("[llmss_b200] attn_prefill: dynamic shared memory base needs %d bytes of alignment slack\n", (int)(smem - smem_raw));
+    __trap();
+  }
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + C::Q_BYTES;
   uint8_t* sV = sK + C::KV_STAGES * C::K_BYTES;
   uint8_t* sP = sV + C::KV_STAGES * C::V_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * C::P_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BUFS * C::P_BYTES);
   uint64_t* bar_q = bars;
   uint64_t* bar_kfull = bars + 1;       // [KV_STAGES]
   uint64_t* bar_vfull = bars + 3;
@@ -277,7 +293,7 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       mbar_wait(&bar_vfull[stage], phase, 63);
       tcgen05_fence_after();
       const uint32_t v_addr = v_base + stage * C::V_BYTES;
-      const uint32_t pj = p_addr + (j & 1) * C::P_BYTES;
+      const uint32_t pj = p_addr + (C::P_BUFS == 2 ? (j & 1) : 0) * C::P_BYTES;
       if (elect_one()) {
 #pragma unroll
         for (int c = 0; c < NSUB; ++c)
@@ -335,9 +351,13 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       m_run = m_new;
       // p = 2^(s*scale - m): one FFMA + one MUFU per element; P -> shared memory (K-major, chunk ^= row & 7)
       const float neg_m = (m_new == -INFINITY) ? 0.f : -m_new;
-      if (j >= 2) mbar_wait(&bar_o[j & 1], ((j >> 1) & 1) ^ 1, 71);  // PV_{j-2} has released this P buffer
+      if constexpr (C::P_BUFS == 2) {
+        if (j >= 2) mbar_wait(&bar_o[j & 1], ((j >> 1) & 1) ^ 1, 71);  // PV_{j-2} has released this P buffer
+      } else {
+        if (j >= 1) mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1, 71);  // single buffer: PV_{j-1} has read it
+      }
       float l_tile = 0.f;
-      uint8_t* pbuf = sP + (j & 1) * C::P_BYTES;
+      uint8_t* pbuf = sP + (C::P_BUFS == 2 ? (j & 1) : 0) * C::P_BYTES;
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t pk[16];
@@ -477,7 +497,7 @@ LLMSS_API int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int6
   CUtensorMap tm;
   cuuint64_t dims[2] = {(cuuint64_t)width, (cuuint64_t)total_tokens};
   cuuint64_t strides[1] = {(cuuint64_t)ldq * 2};
-  const int bn = d >= 256 ? 64 : 128;
+  const int bn = 64;
   // one box shape serves Q (128 rows) and K/V (BN rows) only if they agree; use two loads of BN rows for Q when BN < 128
   cuuint32_t box[2] = {64, (cuuint32_t)bn};
   cuuint32_t estr[2] = {1, 1};
@@ -526,7 +546,7 @@ LLMSS_API int llmss_attn_prefill_paged(const void* q, int64_t ldq, const void* k
                 "attn_prefill_paged: q / out must be 16-byte aligned");
   LLMSS_REQUIRE((int64_t)hq * d <= ldq, "attn_prefill_paged: q columns exceed the row stride");
   if (num_seqs == 0 || total_q == 0) return 0;
-  const int bn = d >= 256 ? 64 : 128;
+  const int bn = 64;
   CUtensorMap tm, tk, tv;
   if (int e = encode_2d(&tm, q, dtype, (int64_t)hq * d, total_q, ldq, bn)) return e;
   const int64_t crow = (int64_t)num_blocks * hkv * block_size;

@@ -24,6 +24,14 @@
 #include <cuda.h>
 #include <string.h>
 
+#ifndef LLMSS_PREFILL_P_TMEM
+#define LLMSS_PREFILL_P_TMEM 1
+#endif
+#ifndef LLMSS_PREFILL_FMA_EXP_EVERY
+#define LLMSS_PREFILL_FMA_EXP_EVERY 0   // n > 0: every n-th pair computes one of its exps on the FMA pipe (measured: no gain, the
+                                        // softmax is bound by issue slots, not by MUFU -- profiles/attn_prefill_ncu.md)
+#endif
+
 namespace {
 
 constexpr int BM = 128;  // queries per CTA
@@ -39,8 +47,13 @@ template <int D>
 struct PCfg {
   static constexpr int BN = 64;                              // keys per tile
   static constexpr int KV_STAGES = 2;
-  static constexpr int P_BUFS = (D >= 256) ? 2 : 1;
+  // D <= 128: P never touches shared memory -- the softmax writes it (packed 16-bit pairs, tcgen05.st) over the S
+  // columns it has just read, and the PV MMA takes its A operand from tensor memory.  S is double-buffered, so P is
+  // too, for free; the QK of tile j+2 then has to wait for PV_j instead of for "S_j is in registers".
+  static constexpr bool P_TMEM = (D < 256) && (LLMSS_PREFILL_P_TMEM != 0);
+  static constexpr int P_BUFS = P_TMEM ? 0 : ((D >= 256) ? 2 : 1);
   static constexpr int MIN_CTAS = (D >= 256) ? 1 : 2;        // CTAs per SM the launch bounds ask for
+  static constexpr int FMA_EXP_EVERY = (D >= 256) ? 0 : LLMSS_PREFILL_FMA_EXP_EVERY;  // every n-th PAIR computes one of its two exps on the FMA pipe (0 = none)
   static constexpr int Q_BYTES = BM * D * 2;
   static constexpr int K_BYTES = BN * D * 2;
   static constexpr int V_BYTES = BN * D * 2;
@@ -99,6 +112,45 @@ __device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU; 2^-inf
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+// 2^x on the FMA pipe (no MUFU): round-to-nearest split x = n + r, r in [-0.5, 0.5], cubic for 2^r (relative error
+// 1.1e-4, far below the bf16 / fp16 rounding of P), exponent added into the float's bits.  A quarter of the
+// exponentials of the softmax go this way: at head_dim 128 / 64 the MUFU pipe (16 ex2 per clock and SM) needs as
+// many cycles per tile as the tensor pipe, so the two cannot both run at full rate unless some of the exps move.
+__device__ __forceinline__ float ex2_fma(float x) {
+  x = fmaxf(x, -125.0f);
+  const float t = x + 12582912.0f;                 // 1.5 * 2^23: the integer part lands in the low mantissa bits
+  const int n = __float_as_int(t) - 0x4B400000;
+  const float r = x - (t - 12582912.0f);
+  float p = fmaf(r, 0.05459282f, 0.24221784f);   // least-squares cubic on [-0.5, 0.5]: max relative error 1.1e-4
+  p = fmaf(r, p, 0.6933686f);
+  p = fmaf(r, p, 1.0f);
+  return __int_as_float(__float_as_int(p) + (n << 23));
+}
+
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (M x 16, 16-bit, two K elements per 32-bit column, row m in
+// lane m) is read from tensor memory.
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// Packed fp32x2 arithmetic (one issue slot for two lanes): the softmax warps are bound by instruction issue
+// (ncu: issue 50 %, tensor pipe 45 %, ~13 instructions per key and thread before this), so the scale-and-shift
+// and the row-sum run as FFMA2 / FADD2.
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n\t.reg .b64 a, b, c, d;\n\tmov.b64 a, {%2, %3};\n\tmov.b64 b, {%4, %5};\n\tmov.b64 c, {%6, %7};\n\t"
+      "fma.rn.f32x2 d, a, b, c;\n\tmov.b64 {%0, %1}, d;\n\t}"
+      : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 a, b, d;\n\tmov.b64 a, {%2, %3};\n\tmov.b64 b, {%4, %5};\n\tadd.rn.f32x2 d, a, b;\n\tmov.b64 {%0, %1}, d;\n\t}"
+      : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
 }
 
 template <typename T>
@@ -264,7 +316,11 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     int stage = 0;
     uint32_t phase = 0;
     for (int j = 0; j < n_tiles; ++j) {
-      if (j >= 2) mbar_wait(&bar_sfree[j & 1], ((j >> 1) & 1) ^ 1, 64);  // softmax_{j-2} has left this S buffer
+      if constexpr (C::P_TMEM) {
+        if (j >= 2) mbar_wait(&bar_o[j & 1], ((j >> 1) & 1) ^ 1, 64);    // PV_{j-2} has read P_{j-2} out of this S buffer
+      } else {
+        if (j >= 2) mbar_wait(&bar_sfree[j & 1], ((j >> 1) & 1) ^ 1, 64);  // softmax_{j-2} has left this S buffer
+      }
       mbar_wait(&bar_kfull[stage], phase, 61);
       tcgen05_fence_after();
       const uint32_t k_addr = k_base + stage * C::K_BYTES;
@@ -298,10 +354,15 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
 #pragma unroll
         for (int c = 0; c < NSUB; ++c)
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_f16_ss(tO, umma_desc_k_sw128(pj + c * (BM * 128) + k * 32),
-                        umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
-                        (j > 0 || c > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) {
+            if constexpr (C::P_TMEM)   // 16 keys = 8 packed columns per step, P_j sits at the start of S buffer j & 1
+              umma_f16_ts(tO, tS + (j & 1) * BN + (c * 4 + k) * 8, umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128),
+                          idesc_o, (j > 0 || c > 0 || k > 0) ? 1u : 0u);
+            else
+              umma_f16_ss(tO, umma_desc_k_sw128(pj + c * (BM * 128) + k * 32),
+                          umma_desc_mn_sw128(v_addr + (c * 64 + k * 16) * 128, BN * 128), idesc_o,
+                          (j > 0 || c > 0 || k > 0) ? 1u : 0u);
+          }
         umma_commit(&bar_o[j & 1]);
         umma_commit(&bar_vempty[stage]);
       }
@@ -323,13 +384,16 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       const bool diag = (kbase + BN - 1) > ctx + q0;   // some key of this tile may lie above the diagonal
       // the whole S row lives in registers (one TMEM read): raw scores, masked on diagonal tiles
       float sc[BN];
+      {
+        // both 32-column loads are in flight before the single wait (a TMEM load has a few hundred cycles of latency)
+        uint32_t r[BN / 32][32];
 #pragma unroll
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tS + (j & 1) * BN + lane_off + c * 32, r);
+        for (int c = 0; c < BN / 32; ++c) tmem_ld_32x32b_x32(tS + (j & 1) * BN + lane_off + c * 32, r[c]);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) sc[c * 32 + i] = __uint_as_float(r[i]);
+        for (int c = 0; c < BN / 32; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) sc[c * 32 + i] = __uint_as_float(r[c][i]);
       }
       tcgen05_fence_before();
       __syncwarp();
@@ -339,9 +403,14 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
         for (int i = 0; i < BN; ++i)
           if (kbase + i > qpos) sc[i] = -INFINITY;
       }
-      float m_tile = -INFINITY;
+      // four independent max chains (two schedulers' worth of latency hiding comes from ILP, not from warps)
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int i = 0; i < BN; ++i) m_tile = fmaxf(m_tile, sc[i]);
+      for (int i = 0; i < BN; i += 8) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mx[u] = fmaxf(mx[u], fmaxf(sc[i + 2 * u], sc[i + 2 * u + 1]));
+      }
+      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       // Lazy running max (scale > 0: max commutes with scaling): keep the old reference unless this tile
       // exceeds it by more than 2^8 -- p stays <= 256, far inside fp32 / bf16 / fp16 range.
       const float m_tile_s = m_tile * a.scale_log2;
@@ -351,30 +420,46 @@ attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
       m_run = m_new;
       // p = 2^(s*scale - m): one FFMA + one MUFU per element; P -> shared memory (K-major, chunk ^= row & 7)
       const float neg_m = (m_new == -INFINITY) ? 0.f : -m_new;
-      if constexpr (C::P_BUFS == 2) {
+      if constexpr (C::P_TMEM) {
+        // nothing to wait for: QK_j was only issued after PV_{j-2} had finished with this buffer
+      } else if constexpr (C::P_BUFS == 2) {
         if (j >= 2) mbar_wait(&bar_o[j & 1], ((j >> 1) & 1) ^ 1, 71);  // PV_{j-2} has released this P buffer
       } else {
         if (j >= 1) mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1, 71);  // single buffer: PV_{j-1} has read it
       }
-      float l_tile = 0.f;
+      float la[4] = {0.f, 0.f, 0.f, 0.f}, lb[4] = {0.f, 0.f, 0.f, 0.f};  // four independent packed sum chains
       uint8_t* pbuf = sP + (C::P_BUFS == 2 ? (j & 1) : 0) * C::P_BYTES;
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          const float p0 = ex2_approx(fmaf(sc[c * 32 + i], a.scale_log2, neg_m));
-          const float p1 = ex2_approx(fmaf(sc[c * 32 + i + 1], a.scale_log2, neg_m));
-          l_tile += p0 + p1;
+          float e0, e1;
+          ffma2(e0, e1, sc[c * 32 + i], sc[c * 32 + i + 1], a.scale_log2, a.scale_log2, neg_m, neg_m);
+          const float p0 = ex2_approx(e0);
+          const float p1 = (C::FMA_EXP_EVERY > 0 && ((i >> 1) % (C::FMA_EXP_EVERY > 0 ? C::FMA_EXP_EVERY : 1)) == 0) ? ex2_fma(e1) : ex2_approx(e1);
+          fadd2(la[(i >> 1) & 3], lb[(i >> 1) & 3], la[(i >> 1) & 3], lb[(i >> 1) & 3], p0, p1);
           pk[i >> 1] = pack2<T>(p0, p1);
         }
-        uint8_t* sub = pbuf + (c >> 1) * (BM * 128) + row * 128;
+        if constexpr (C::P_TMEM) {
+          // 32 keys -> 16 packed columns of this row's lane, over the S columns that are already in registers
+          asm volatile(
+              "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+              "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(tS + (j & 1) * BN + lane_off + c * 16),
+              "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7]), "r"(pk[8]),
+              "r"(pk[9]), "r"(pk[10]), "r"(pk[11]), "r"(pk[12]), "r"(pk[13]), "r"(pk[14]), "r"(pk[15])
+              : "memory");
+        } else {
+          uint8_t* sub = pbuf + (c >> 1) * (BM * 128) + row * 128;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int chunk = ((c & 1) * 4 + q) ^ (row & 7);
-          *reinterpret_cast<uint4*>(sub + chunk * 16) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+          for (int q = 0; q < 4; ++q) {
+            const int chunk = ((c & 1) * 4 + q) ^ (row & 7);
+            *reinterpret_cast<uint4*>(sub + chunk * 16) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+          }
         }
       }
+      if constexpr (C::P_TMEM) tmem_st_wait();
+      const float l_tile = ((la[0] + lb[0]) + (la[1] + lb[1])) + ((la[2] + lb[2]) + (la[3] + lb[3]));
       if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
         mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1, 73);  // PV_{j-1} retired: O is stable
         tcgen05_fence_after();

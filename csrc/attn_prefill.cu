@@ -28,8 +28,8 @@
 #define LLMSS_PREFILL_P_TMEM 1
 #endif
 #ifndef LLMSS_PREFILL_FMA_EXP_EVERY
-#define LLMSS_PREFILL_FMA_EXP_EVERY 0   // n > 0: every n-th pair computes one of its exps on the FMA pipe (measured: no gain, the
-                                        // softmax is bound by issue slots, not by MUFU -- profiles/attn_prefill_ncu.md)
+#define LLMSS_PREFILL_FMA_EXP_EVERY 2   // n > 0: every n-th pair computes one of its two exps on the FMA pipe (1 in 4 at n = 2:
+                                        // +2 % at head_dim 128 once P moved to tensor memory; no gain before that)
 #endif
 
 namespace {

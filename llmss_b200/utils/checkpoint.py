@@ -27,6 +27,14 @@ PRESETS: Dict[str, dict] = {
     "gptj-tiny8": dict(model_type="gptj", architectures=["GPTJForCausalLM"], vocab_size=512, n_positions=256,
                        n_embd=512, n_layer=2, n_head=8, rotary_dim=32, n_inner=None, activation_function="gelu_new",
                        layer_norm_epsilon=1e-5, tie_word_embeddings=False, bos_token_id=0, eos_token_id=0),
+    # 8-rank test models: GQA (16 q heads over 8 kv heads: one kv head per rank at TP=8) and MQA (kv replicated)
+    "llama-tiny8": dict(model_type="llama", architectures=["LlamaForCausalLM"], vocab_size=512, hidden_size=1024,
+                        intermediate_size=2048, num_hidden_layers=2, num_attention_heads=16, num_key_value_heads=8,
+                        max_position_embeddings=256, rms_norm_eps=1e-5, hidden_act="silu", rope_theta=10000.0,
+                        tie_word_embeddings=False),
+    "bigcode-tiny8": dict(model_type="gpt_bigcode", architectures=["GPTBigCodeForCausalLM"], vocab_size=512,
+                          n_positions=256, n_embd=512, n_layer=2, n_head=8, n_inner=2048, multi_query=True,
+                          activation_function="gelu_pytorch_tanh", layer_norm_epsilon=1e-5, tie_word_embeddings=True),
     # StarCoder shape (MQA) -- the reference's second family
     "starcoder": dict(model_type="gpt_bigcode", architectures=["GPTBigCodeForCausalLM"], vocab_size=49152,
                       n_positions=8192, n_embd=6144, n_layer=40, n_head=48, n_inner=24576, multi_query=True,

@@ -1135,16 +1135,24 @@ int clusters_for(int dtype, int bn, int split) {
 
 int pick_cluster_split(int tiles, int kb_total, int bn, int sms, int dtype) {
   static int forced = -1;
+  static int min_kb = -1;  // k-blocks (64 x 16-bit columns, 16 KB of weights) every CTA of a split must at least stream
   if (forced < 0) {
     const char* e = getenv("LLMSS_GEMM_MODE");
     forced = (e == nullptr) ? 0 : (strcmp(e, "streamk") == 0 ? 1 : (strcmp(e, "cluster") == 0 ? 2 : 0));
+    const char* m = getenv("LLMSS_GEMM_MIN_KB_PER_CTA");
+    min_kb = (m != nullptr) ? atoi(m) : 8;
+    if (min_kb < 1) min_kb = 1;
   }
   if (forced == 1) return 0;
-  for (int s = 8; s >= 2; --s) {
-    if (kb_total / s < 2) continue;
-    if (forced != 2 && (tiles * s > sms || tiles > clusters_for(dtype, bn, s))) continue;
-    // stream-K uses every SM; take the cluster kernel only if it occupies at least ~70% of them
-    if (forced != 2 && tiles * s * 10 < sms * 7) return 0;
+  // Splitting K over a cluster buys bandwidth (more CTAs streaming weights) and costs a cluster barrier plus a DSMEM
+  // reduction (~2 us): it pays only while every CTA still streams a good number of k-blocks.  Short-K GEMMs (the
+  // TP=8 o_proj: K = 512) run one CTA per tile -- a "cluster" of one, same kernel, same fused epilogues.
+  for (int s = 8; s >= 1; --s) {
+    if (s > 1 && kb_total / s < min_kb) continue;
+    if (forced != 2 && (tiles * s > sms || (s > 1 && tiles > clusters_for(dtype, bn, s)))) continue;
+    // stream-K uses every SM; take the tile-per-CTA / cluster kernel only if it occupies a fair share of them, or if
+    // the whole GEMM is so small that the stream-K fix-up would dominate
+    if (forced != 2 && tiles * s * 10 < sms * 7 && (int64_t)tiles * kb_total > 4 * sms) return 0;
     return s;
   }
   return 0;

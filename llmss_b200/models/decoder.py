@@ -165,7 +165,10 @@ class DecoderLM(nn.Module):
         q_off, k_off, v_off = 0, self.q_dim, self.q_dim + self.kv_dim
         ops.rope_kv_write(qkv, batch.positions, batch.slot_mapping, kc, vc, self.hq, self.hkv, self.d, s.rotary_dim,
                           s.rope, s.rope_base, q_off, k_off, v_off)
-        ctx = torch.empty(qkv.shape[0], self.q_dim, dtype=qkv.dtype, device=qkv.device)
+        # prefill: zeros, not empty -- padding rows (inert tokens that round the batch up for TP) are never written by the
+        # prefill attention kernel, and a NaN left there would reach real rows through the next layer's 0 x V products
+        # (decode rows only ever attend to their own sequence's cache, so the graph keeps the cheaper empty)
+        ctx = (torch.empty if batch.is_decode else torch.zeros)(qkv.shape[0], self.q_dim, dtype=qkv.dtype, device=qkv.device)
         ops.attention(qkv, ctx, batch, kc, vc, self.hq, self.hkv, self.d, s.scale, q_off, k_off, v_off)
         if s.parallel_residual:
             o = ops.linear(ctx, L.wo, L.bo, comm=self.comm)
@@ -245,7 +248,7 @@ class DecoderLM(nn.Module):
                 q_off, k_off, v_off = 0, self.q_dim, self.q_dim + self.kv_dim
                 ops.rope_kv_write(qkv, batch.positions, batch.slot_mapping, kc, vc, self.hq, self.hkv, self.d,
                                   s.rotary_dim, s.rope, s.rope_base, q_off, k_off, v_off)
-                ctx = torch.empty(T, self.q_dim, dtype=qkv.dtype, device=qkv.device)
+                ctx = torch.zeros(T, self.q_dim, dtype=qkv.dtype, device=qkv.device)
                 ops.attention(qkv, ctx, batch, kc, vc, self.hq, self.hkv, self.d, s.scale, q_off, k_off, v_off)
                 if s.parallel_residual:
                     o = cu.linear_reduce_scatter(ctx, L.wo, symm, bias=L.bo)

@@ -57,6 +57,22 @@ struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
 };
 
+// Cluster split-K kernel: for token tiles up to 128 wide the CTAs PUSH their partial slices into the owner's shared
+// memory (st.shared::cluster, posted, hidden behind the cluster barrier) instead of the owner pulling them afterwards
+// (ld.shared::cluster: a ~1 us round trip on the critical path of a ~10 us kernel).  The receive area cannot alias
+// the TMA ring -- a fast peer would write into stages that are still landing -- so the ring gives up that much.
+template <int BN>
+struct CCfg {
+  static constexpr bool PUSH = BN <= 128;
+  static constexpr int W_BYTES = BM * BK * 2;
+  static constexpr int X_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = W_BYTES + X_BYTES;
+  static constexpr int RECV_BYTES = PUSH ? (BM * BN * 4 + 8 * 32 * 32) : 0;   // one fp32 tile + per-CTA rounding slack
+  static constexpr int STAGES_RAW = (196 * 1024 - RECV_BYTES) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 12 ? 12 : STAGES_RAW;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ + RECV_BYTES;
+};
+
 struct GemmArgs {
   int M, N, K;
   int tiles_n, tiles_m, kb_total;
@@ -674,11 +690,35 @@ __device__ __forceinline__ void dsmem_reduce_pair(uint32_t stage_u32, int S, int
   }
 }
 
+// Push mode: the S partials of an item already sit in this CTA's receive area ([source CTA][half][item] float4 planes).
+__device__ __forceinline__ void recv_reduce_pair(const float4* recv, int per, int S, int li0, int li1, bool two,
+                                                 float (&v0)[8], float (&v1)[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v0[j] = v1[j] = 0.f;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {  // CTA order: deterministic
+    if (q < S) {
+      const float4 lo0 = recv[(q * 2 + 0) * per + li0], hi0 = recv[(q * 2 + 1) * per + li0];
+      v0[0] += lo0.x; v0[1] += lo0.y; v0[2] += lo0.z; v0[3] += lo0.w;
+      v0[4] += hi0.x; v0[5] += hi0.y; v0[6] += hi0.z; v0[7] += hi0.w;
+      if (two) {
+        const float4 lo1 = recv[(q * 2 + 0) * per + li1], hi1 = recv[(q * 2 + 1) * per + li1];
+        v1[0] += lo1.x; v1[1] += lo1.y; v1[2] += lo1.z; v1[3] += lo1.w;
+        v1[4] += hi1.x; v1[5] += hi1.y; v1[6] += hi1.z; v1[7] += hi1.w;
+      }
+    }
+  }
+}
+__device__ __forceinline__ void st_dsmem_f4(uint32_t cluster_addr, const float4& v) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
 template <typename T, int BN>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                     const __grid_constant__ GemmArgs a) {
-  using C = Cfg<BN>;
+  using C = CCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
@@ -714,8 +754,15 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  // push mode: a CTA may only be written to once it is known to be running.  Everybody arrives here and waits later,
+  // just before its first remote store (epilogue warps) or after its loop (TMA / MMA warps): the barrier costs nothing
+  // on the critical path.
+  if constexpr (C::PUSH) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
-  float4* staging = reinterpret_cast<float4*>(smem);  // [NG*2][128] float4, reuses the drained TMA ring
+  float4* staging = reinterpret_cast<float4*>(smem);  // pull mode: [NG*2][128] float4, reuses the drained TMA ring
+  float4* recv = reinterpret_cast<float4*>(smem + C::STAGES * C::STAGE_BYTES + 512);  // push mode: never aliases the ring
+  const int total_items_c = NG * BM;
+  const int per_c = ((total_items_c + S - 1) / S + 31) / 32 * 32;   // items owned by each CTA of the cluster
   pdl_wait();  // everything below reads what earlier kernels of the stream wrote (x, workspaces, epoch)
   uint32_t epoch = 0;
   if (a.ar) epoch = *a.ws.epoch + 1;
@@ -738,6 +785,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
       __syncwarp();
       if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
     }
+    if constexpr (C::PUSH) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
   } else if (warp == 1) {
     const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, BM, BN);
     const uint32_t smem_base = smem_u32(smem);
@@ -762,7 +810,9 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     if (elect_one()) umma_commit(&tfull_bar[0]);
     __syncwarp();
     if (lane == 0) LLMSS_STAMP(4);
+    if constexpr (C::PUSH) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
   } else {
+    if constexpr (C::PUSH) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");  // all peers are running
     // park the accumulator in shared memory: [(cg*2 + half)][feature] float4, conflict-free
     const int quarter = warp & 3;
     const int f = quarter * 32 + lane;
@@ -770,13 +820,25 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     mbar_wait(&tfull_bar[0], 0, 42);  // all MMAs retired => every TMA stage has landed and been consumed
     tcgen05_fence_after();
     if (threadIdx.x == 64) LLMSS_STAMP(5);
+    const uint32_t recv_u32 = smem_u32(recv);
 #pragma unroll 1
     for (int cg = 0; cg < NG; ++cg) {
       uint32_t q[8];
       tmem_ld_32x32b_x8(t_addr + cg * 8, q);
       tmem_ld_wait();
-      staging[(cg * 2 + 0) * BM + f] = make_float4(__uint_as_float(q[0]), __uint_as_float(q[1]), __uint_as_float(q[2]), __uint_as_float(q[3]));
-      staging[(cg * 2 + 1) * BM + f] = make_float4(__uint_as_float(q[4]), __uint_as_float(q[5]), __uint_as_float(q[6]), __uint_as_float(q[7]));
+      const float4 lo = make_float4(__uint_as_float(q[0]), __uint_as_float(q[1]), __uint_as_float(q[2]), __uint_as_float(q[3]));
+      const float4 hi = make_float4(__uint_as_float(q[4]), __uint_as_float(q[5]), __uint_as_float(q[6]), __uint_as_float(q[7]));
+      if constexpr (C::PUSH) {
+        // hand the 8 token columns of this feature to the CTA that owns the item (posted remote shared-memory stores)
+        const int item = cg * BM + f;
+        const int owner = item / per_c, li = item - owner * per_c;
+        const uint32_t dst = mapa_shared(recv_u32 + (uint32_t)(((r * 2) * per_c + li) * 16), (uint32_t)owner);
+        st_dsmem_f4(dst, lo);
+        st_dsmem_f4(dst + (uint32_t)per_c * 16, hi);
+      } else {
+        staging[(cg * 2 + 0) * BM + f] = lo;
+        staging[(cg * 2 + 1) * BM + f] = hi;
+      }
     }
   }
   __syncwarp();
@@ -809,7 +871,8 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const bool two = it0 + 128 < my_items;
         const int item0 = r * per + it0, item1 = two ? item0 + 128 : item0;
         float va[8], vb[8];
-        dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
+        if constexpr (C::PUSH) recv_reduce_pair(recv, per, S, it0, it0 + 128, two, va, vb);
+        else dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
         *reinterpret_cast<uint4*>(part + tile_off + (size_t)item0 * 16) = pack8<T>(va);
         if (two) *reinterpret_cast<uint4*>(part + tile_off + (size_t)item1 * 16) = pack8<T>(vb);
       }
@@ -862,7 +925,8 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const bool two = it0 + 128 < my_items;
         const int item0 = r * per + it0, item1 = two ? item0 + 128 : item0;
         float va[8], vb[8];
-        dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
+        if constexpr (C::PUSH) recv_reduce_pair(recv, per, S, it0, it0 + 128, two, va, vb);
+        else dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
         *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, it0 / sub, par) + (size_t)me * ar_slot_bytes + tile_off +
                                   (size_t)item0 * 16) = lam_sanitize<2>(pack8<T>(va));
         if (two)
@@ -945,7 +1009,10 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
       for (int it0 = epi_tid; it0 < my_items; it0 += 256) {
         const bool two = it0 + 128 < my_items;
         float vv[2][8];
-        if (pass == 0) dsmem_reduce_pair(stage_u32, S, r * per + it0, r * per + (two ? it0 + 128 : it0), two, vv[0], vv[1]);
+        if (pass == 0) {
+          if constexpr (C::PUSH) recv_reduce_pair(recv, per, S, it0, it0 + 128, two, vv[0], vv[1]);
+          else dsmem_reduce_pair(stage_u32, S, r * per + it0, r * per + (two ? it0 + 128 : it0), two, vv[0], vv[1]);
+        }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           if (u == 1 && !two) break;
@@ -1066,7 +1133,7 @@ int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int 
 template <typename T, int BN>
 int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int tiles, int split,
                    cudaStream_t stream) {
-  using C = Cfg<BN>;
+  using C = CCfg<BN>;
   static PerDeviceSmem configured;
   auto kern = gemm_cluster_kernel<T, BN>;
   LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
@@ -1095,7 +1162,7 @@ template <typename T, int BN>
 int max_active_clusters(int split) {
   static int cache[9] = {-1, -1, -1, -1, -1, -1, -1, -1, -1};
   if (cache[split] >= 0) return cache[split];
-  using C = Cfg<BN>;
+  using C = CCfg<BN>;
   auto kern = gemm_cluster_kernel<T, BN>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
   cudaLaunchConfig_t cfg;
@@ -1140,13 +1207,15 @@ int pick_cluster_split(int tiles, int kb_total, int bn, int sms, int dtype) {
     const char* e = getenv("LLMSS_GEMM_MODE");
     forced = (e == nullptr) ? 0 : (strcmp(e, "streamk") == 0 ? 1 : (strcmp(e, "cluster") == 0 ? 2 : 0));
     const char* m = getenv("LLMSS_GEMM_MIN_KB_PER_CTA");
-    min_kb = (m != nullptr) ? atoi(m) : 8;
+    min_kb = (m != nullptr) ? atoi(m) : 2;
     if (min_kb < 1) min_kb = 1;
   }
   if (forced == 1) return 0;
-  // Splitting K over a cluster buys bandwidth (more CTAs streaming weights) and costs a cluster barrier plus a DSMEM
-  // reduction (~2 us): it pays only while every CTA still streams a good number of k-blocks.  Short-K GEMMs (the
-  // TP=8 o_proj: K = 512) run one CTA per tile -- a "cluster" of one, same kernel, same fused epilogues.
+  // Splitting K over a cluster divides the weight stream AND the epilogue (each CTA finishes 1/S of the tile) at the
+  // price of a cluster barrier and a DSMEM exchange.  Measured on the TP=8 per-rank shapes (M = 16..128, K = 512..2560,
+  // scripts/bench_gemm_small.py): the deepest split that leaves two k-blocks per CTA wins everywhere -- 8.2 us vs
+  // 12.0 us for one CTA per tile at M=64, K=512 -- because the epilogue, not the stream, is the long pole.  A "cluster"
+  // of one (K of one or two k-blocks) still runs this kernel, so the fused all-reduce epilogues stay available.
   for (int s = 8; s >= 1; --s) {
     if (s > 1 && kb_total / s < min_kb) continue;
     if (forced != 2 && (tiles * s > sms || (s > 1 && tiles > clusters_for(dtype, bn, s)))) continue;

@@ -51,6 +51,11 @@ if len(sys.argv) > 1 and sys.argv[1] == "small":
     run(64, 4096, 2560, bias=True)
     run(64, 4096, 4096)
     sys.exit(0)
+if len(sys.argv) > 1 and sys.argv[1] == "tp8":
+    run(64, 4096, 512)
+    run(64, 4096, 2560)
+    run(64, 3584, 4096, bias=True, act=1, act_start=1536)
+    sys.exit(0)
 if len(sys.argv) > 1 and sys.argv[1] == "epi":
     run(64, 28672, 4096)
     run(64, 28672, 4096, bias=True, act=1, act_start=12288)

@@ -556,7 +556,7 @@ LLMSS_API int llmss_allreduce(SymmWs* ws, const void* in, void* out, int64_t n, 
   const bool nvls_fits = ws->mc_base != nullptr && (nvls_can_lam || nvls_can_flag);
   const bool two_lam_fits = (size_t)bytes * (ws->nranks + 1) <= ws->lam_bytes;
   if (algo == 0 && nvls_fits && bytes >= llmss_nvls_min_bytes()) algo = 3;
-  if (algo == 0 && two_lam_fits && ws->nranks >= 4 && bytes >= llmss_twoshot_min_bytes()) algo = 4;
+  if (algo == 0 && two_lam_fits && ((ws->nranks >= 4 && bytes >= llmss_twoshot_min_bytes()) || bytes > (int64_t)(1 << 20))) algo = 4;
   if (algo == 4) {
     LLMSS_REQUIRE(two_lam_fits, "allreduce: message of %lld bytes needs %lld bytes of Lamport buffer (have %zu)",
                   (long long)bytes, (long long)bytes * (ws->nranks + 1), ws->lam_bytes);

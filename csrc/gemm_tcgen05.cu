@@ -1370,7 +1370,8 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
     // from 4 ranks and LLMSS_TWOSHOT_MIN_BYTES upwards the two-shot form wins (profiles/bench_gemm_ar.md)
     if (collective == 4) ar_mode = 3;
     else if (collective == 6) ar_mode = 4;
-    else if (collective == 1 && two_ok && ws->nranks >= 4 && (int64_t)M * N * 2 >= llmss_twoshot_min_bytes()) ar_mode = 4;
+    else if (collective == 1 && two_ok && ((ws->nranks >= 4 && (int64_t)M * N * 2 >= llmss_twoshot_min_bytes()) ||
+                                          (int64_t)M * N * 2 >= (1 << 20))) ar_mode = 4;
     LLMSS_REQUIRE(ar_mode != 1 || (size_t)p.ar_bytes <= ws->lam_bytes, "gemm: fused all-reduce needs %lld bytes of Lamport buffer (have %zu)",
                   (long long)p.ar_bytes, ws->lam_bytes);
   }

@@ -53,9 +53,9 @@ def _fused_ar_mode(cu, symm, M: int, N: int, K: int, esz: int) -> int:
         return 0
     msg = M * N * esz
     padded = plan.tiles * 128 * plan.bn * esz
-    if (symm.nranks >= 4 and msg >= _TWOSHOT_MIN and padded <= _FUSED_TWOSHOT_MAX
-            and (symm.nranks + 1) * padded <= symm.lam_bytes):
-        return 6
+    two_fits = padded <= _FUSED_TWOSHOT_MAX and (symm.nranks + 1) * padded <= symm.lam_bytes
+    if two_fits and ((symm.nranks >= 4 and msg >= _TWOSHOT_MIN) or msg >= (1 << 20)):
+        return 6   # measured: from 256 KB at 4+ ranks, from 1 MB even at 2 ranks (profiles/bench_gemm_ar.md)
     if plan.ar_bytes <= symm.lam_bytes and msg * (symm.nranks - 1) <= _FUSED_PUSH_MAX:
         return 5
     return 0

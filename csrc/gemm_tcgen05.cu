@@ -691,22 +691,25 @@ __device__ __forceinline__ void dsmem_reduce_pair(uint32_t stage_u32, int S, int
 }
 
 // Push mode: the S partials of an item already sit in this CTA's receive area ([source CTA][half][item] float4 planes).
-__device__ __forceinline__ void recv_reduce_pair(const float4* recv, int per, int S, int li0, int li1, bool two,
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void recv_reduce_pair(uint32_t recv_u32, int per, int S, int li0, int li1, bool two,
                                                  float (&v0)[8], float (&v1)[8]) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) v0[j] = v1[j] = 0.f;
-#pragma unroll
-  for (int q = 0; q < 8; ++q) {  // CTA order: deterministic
-    if (q < S) {
-      const float4 lo0 = recv[(q * 2 + 0) * per + li0], hi0 = recv[(q * 2 + 1) * per + li0];
-      v0[0] += lo0.x; v0[1] += lo0.y; v0[2] += lo0.z; v0[3] += lo0.w;
-      v0[4] += hi0.x; v0[5] += hi0.y; v0[6] += hi0.z; v0[7] += hi0.w;
-      if (two) {
-        const float4 lo1 = recv[(q * 2 + 0) * per + li1], hi1 = recv[(q * 2 + 1) * per + li1];
-        v1[0] += lo1.x; v1[1] += lo1.y; v1[2] += lo1.z; v1[3] += lo1.w;
-        v1[4] += hi1.x; v1[5] += hi1.y; v1[6] += hi1.z; v1[7] += hi1.w;
-      }
-    }
+  if (!two) li1 = li0;
+#pragma unroll 1
+  for (int q = 0; q < S; ++q) {  // CTA order: deterministic; a rolled loop keeps the once-executed epilogue short
+    const uint32_t base = recv_u32 + (uint32_t)(q * 2 * per) * 16;
+    const float4 lo0 = lds_f4(base + li0 * 16), hi0 = lds_f4(base + (per + li0) * 16);
+    const float4 lo1 = lds_f4(base + li1 * 16), hi1 = lds_f4(base + (per + li1) * 16);
+    v0[0] += lo0.x; v0[1] += lo0.y; v0[2] += lo0.z; v0[3] += lo0.w;
+    v0[4] += hi0.x; v0[5] += hi0.y; v0[6] += hi0.z; v0[7] += hi0.w;
+    v1[0] += lo1.x; v1[1] += lo1.y; v1[2] += lo1.z; v1[3] += lo1.w;
+    v1[4] += hi1.x; v1[5] += hi1.y; v1[6] += hi1.z; v1[7] += hi1.w;
   }
 }
 __device__ __forceinline__ void st_dsmem_f4(uint32_t cluster_addr, const float4& v) {
@@ -714,7 +717,9 @@ __device__ __forceinline__ void st_dsmem_f4(uint32_t cluster_addr, const float4&
                : "memory");
 }
 
-template <typename T, int BN>
+// AR = false: the instantiation without any collective code (column-parallel GEMMs, TP=1): its epilogue -- executed
+// once per CTA, so every instruction-cache line it touches is a miss -- stays compact.
+template <typename T, int BN, bool AR>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                     const __grid_constant__ GemmArgs a) {
@@ -765,7 +770,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   const int per_c = ((total_items_c + S - 1) / S + 31) / 32 * 32;   // items owned by each CTA of the cluster
   pdl_wait();  // everything below reads what earlier kernels of the stream wrote (x, workspaces, epoch)
   uint32_t epoch = 0;
-  if (a.ar) epoch = *a.ws.epoch + 1;
+  if constexpr (AR) epoch = *a.ws.epoch + 1;
   if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
@@ -856,7 +861,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     const size_t ar_slot_bytes = (size_t)tiles * BM * BN * sizeof(T);
     const int par = epoch & 1;
     const uint32_t stage_u32 = smem_u32(staging);
-    if (a.ar == 3) {
+    if (AR && a.ar == 3) {
       // ---- NVLS all-reduce (K1, in-switch): (A) the reduced bf16/fp16 slice goes to this rank's OWN bulk buffer
       // (local stores, nothing on the wire) and one multicast flag store tells every rank that this CTA slot
       // of this rank is staged; (B) rank q sums the q-th share of the slot with multimem.ld_reduce -- the
@@ -871,7 +876,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const bool two = it0 + 128 < my_items;
         const int item0 = r * per + it0, item1 = two ? item0 + 128 : item0;
         float va[8], vb[8];
-        if constexpr (C::PUSH) recv_reduce_pair(recv, per, S, it0, it0 + 128, two, va, vb);
+        if constexpr (C::PUSH) recv_reduce_pair(smem_u32(recv), per, S, it0, it0 + 128, two, va, vb);
         else dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
         *reinterpret_cast<uint4*>(part + tile_off + (size_t)item0 * 16) = pack8<T>(va);
         if (two) *reinterpret_cast<uint4*>(part + tile_off + (size_t)item1 * 16) = pack8<T>(vb);
@@ -907,10 +912,10 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);  // ahead of the wait
         unpack8<T>(lam_take(reinterpret_cast<uint4*>(mine + tile_off + (size_t)item * 16), 45), v[0]);
         const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-        store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+        store_chunk_t<T, 1, EPI_PLAIN, LLMSS_ACT_NONE>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
       }
     }
-    if (a.ar == 4) {
+    if (AR && a.ar == 4) {
       // ---- two-shot all-reduce without flags (K1 for t >= 4): (A) every vector of this CTA's slice goes to the ONE
       // rank that owns it (1/t of the slice each) as a self-validating Lamport vector; (B) the owner sums the t
       // contributions in rank order and broadcasts the result -- one multicast store through the NVSwitch when
@@ -925,7 +930,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const bool two = it0 + 128 < my_items;
         const int item0 = r * per + it0, item1 = two ? item0 + 128 : item0;
         float va[8], vb[8];
-        if constexpr (C::PUSH) recv_reduce_pair(recv, per, S, it0, it0 + 128, two, va, vb);
+        if constexpr (C::PUSH) recv_reduce_pair(smem_u32(recv), per, S, it0, it0 + 128, two, va, vb);
         else dsmem_reduce_pair(stage_u32, S, item0, item1, two, va, vb);
         *reinterpret_cast<uint4*>(symm_lam<uint8_t>(a.ws, it0 / sub, par) + (size_t)me * ar_slot_bytes + tile_off +
                                   (size_t)item0 * 16) = lam_sanitize<2>(pack8<T>(va));
@@ -997,12 +1002,12 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
 #pragma unroll
             for (int j = 0; j < 8; ++j) rv1[0][j] = rv[u][j];
             const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-            store_chunk<T, 1>(a, v, rv1, n, tm * BN + cg * 8, lane, bval, a.M);
+            store_chunk_t<T, 1, EPI_PLAIN, LLMSS_ACT_NONE>(a, v, rv1, n, tm * BN + cg * 8, lane, bval, a.M);  // fused collectives: plain epilogue only
           }
         }
       }
     }
-    const int n_pass = a.ar >= 3 ? 0 : (a.ar ? 2 : 1);
+    const int n_pass = !AR ? 1 : (a.ar >= 3 ? 0 : (a.ar ? 2 : 1));
 #pragma unroll 1
     for (int pass = 0; pass < n_pass; ++pass) {
 #pragma unroll 1
@@ -1010,7 +1015,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const bool two = it0 + 128 < my_items;
         float vv[2][8];
         if (pass == 0) {
-          if constexpr (C::PUSH) recv_reduce_pair(recv, per, S, it0, it0 + 128, two, vv[0], vv[1]);
+          if constexpr (C::PUSH) recv_reduce_pair(smem_u32(recv), per, S, it0, it0 + 128, two, vv[0], vv[1]);
           else dsmem_reduce_pair(stage_u32, S, r * per + it0, r * per + (two ? it0 + 128 : it0), two, vv[0], vv[1]);
         }
 #pragma unroll
@@ -1025,7 +1030,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
           if (pass == 0) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[0][j] = vv[u][j];
-            if (a.ar) {
+            if (AR && a.ar) {
               const uint4 vec = lam_sanitize<2>(pack8<T>(v[0]));
 #pragma unroll 1
               for (int p = 0; p < a.ws.nranks; ++p) {
@@ -1034,7 +1039,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
               }
               continue;
             }
-          } else {
+          } else if constexpr (AR) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[0][j] = 0.f;
             uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
@@ -1055,7 +1060,8 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
             }
           }
           const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-          store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+          if constexpr (AR) store_chunk_t<T, 1, EPI_PLAIN, LLMSS_ACT_NONE>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+          else store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
         }
       }
     }
@@ -1070,7 +1076,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, TCOLS);
   }
-  if (a.ar) symm_finish(a.ws, epoch);
+  if constexpr (AR) symm_finish(a.ws, epoch);
   if (threadIdx.x == 0) LLMSS_STAMP(7);
 }
 
@@ -1130,12 +1136,12 @@ int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int 
   return 0;
 }
 
-template <typename T, int BN>
-int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int tiles, int split,
-                   cudaStream_t stream) {
+template <typename T, int BN, bool AR>
+int launch_cluster_ar(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int tiles, int split,
+                      cudaStream_t stream) {
   using C = CCfg<BN>;
   static PerDeviceSmem configured;
-  auto kern = gemm_cluster_kernel<T, BN>;
+  auto kern = gemm_cluster_kernel<T, BN, AR>;
   LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -1156,6 +1162,13 @@ int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs&
   return 0;
 }
 
+template <typename T, int BN>
+int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int tiles, int split,
+                   cudaStream_t stream) {
+  return a.ar ? launch_cluster_ar<T, BN, true>(tw, tx, a, tiles, split, stream)
+              : launch_cluster_ar<T, BN, false>(tw, tx, a, tiles, split, stream);
+}
+
 // Largest cluster size (2..8) for which all `tiles` clusters are co-resident (one wave) and every CTA still
 // streams >= 2 k-blocks; 0 = use the stream-K persistent kernel.  LLMSS_GEMM_MODE=streamk|cluster forces one.
 template <typename T, int BN>
@@ -1163,7 +1176,7 @@ int max_active_clusters(int split) {
   static int cache[9] = {-1, -1, -1, -1, -1, -1, -1, -1, -1};
   if (cache[split] >= 0) return cache[split];
   using C = CCfg<BN>;
-  auto kern = gemm_cluster_kernel<T, BN>;
+  auto kern = gemm_cluster_kernel<T, BN, false>;  // both instantiations have the same launch footprint
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

@@ -286,7 +286,8 @@ __device__ __forceinline__ float4 ld_dsmem_f4(uint32_t cluster_addr) {
   return v;
 }
 
-template <typename T, int BN>
+// COLL = false: no collective code at all (TP=1, column-parallel GEMMs, LM head): a shorter once-executed epilogue.
+template <typename T, int BN, bool COLL>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                    const __grid_constant__ GemmArgs a) {
@@ -330,7 +331,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // everything below reads what earlier kernels of the stream wrote (x, workspaces, epoch)
   uint32_t epoch = 0;
-  if (a.ar || a.ag) epoch = *a.ws.epoch + 1;
+  if constexpr (COLL) { if (a.ar || a.ag) epoch = *a.ws.epoch + 1; }
   if (threadIdx.x == 0) LLMSS_STAMP(1);
 
   if (warp == 0) {
@@ -347,9 +348,9 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         const int tn = sg.tile % a.tiles_n, tm = (sg.tile / a.tiles_n + a.tm_rot) % a.tiles_m;
         const void* xmap = &tmap_x;
         int xrow = tm * BN;
-        if (a.ag && xrow / a.rs_rows == a.ws.rank) {
+        if (COLL && a.ag && xrow / a.rs_rows == a.ws.rank) {
           xrow -= a.ws.rank * a.rs_rows;  // own shard: tmap_x covers it in place, no waiting
-        } else if (a.ag) {
+        } else if (COLL && a.ag) {
           const int q = xrow / a.rs_rows;  // rank whose shard holds these token rows
           if (!(acquired & (1u << q))) {
             wait_flag_ge(symm_flag(a.ws, a.ws.rank, 1, 0) + q, epoch, 11);
@@ -427,7 +428,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     const size_t ar_slot_bytes = (size_t)(a.ar == 2 ? tiles / a.ws.nranks : tiles) * BM * BN * sizeof(T);
     const int par = epoch & 1;
 
-    if (a.ag) {
+    if (COLL && a.ag) {
       // ---- fused all-gather (K3): while the TMA / MMA warps already work on the token tiles of this
       // rank's own shard, the (still idle) epilogue warps push that shard into every rank's gathered
       // activation buffer over NVLink; the last CTA to finish raises the "shard landed" flags.  Readers
@@ -514,10 +515,10 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         //         store it (no AR) or push it to every rank's exchange buffer (AR);
         // pass 1: (AR only) after the per-tile handshake, sum the ranks' tiles and store.
         // reduce-scatter: the tile goes only to the rank that owns its token rows, which alone runs pass 1
-        const int owner = (a.ar == 2) ? m0 / a.rs_rows : -1;
-        const int n_pass = (a.ar == 1 || (a.ar == 2 && owner == a.ws.rank)) ? 2 : 1;
+        const int owner = (COLL && a.ar == 2) ? m0 / a.rs_rows : -1;
+        const int n_pass = (COLL && (a.ar == 1 || (a.ar == 2 && owner == a.ws.rank))) ? 2 : 1;
         // exchange-buffer tile index: global for all-reduce, compact (tiles owned by one rank) for reduce-scatter
-        const int xtile = (a.ar == 2) ? (tm - owner * (a.rs_rows / BN)) * a.tiles_n + tn : sg.tile;
+        const int xtile = (COLL && a.ar == 2) ? (tm - owner * (a.rs_rows / BN)) * a.tiles_n + tn : sg.tile;
 #pragma unroll 1
         for (int pass = 0; pass < n_pass; ++pass) {
           if (pass == 1 && full_tile) {
@@ -530,8 +531,8 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
           // L2 round trip per chunk and contributor instead of one per group.
           constexpr int CH = NG < 4 ? NG : 4;
           const bool storing = (pass == n_pass - 1);
-          const int mrow0 = (a.ar == 2) ? m0 - a.ws.rank * a.rs_rows : m0;
-          const int mlim = (a.ar == 2) ? a.rs_rows : a.M;
+          const int mrow0 = (COLL && a.ar == 2) ? m0 - a.ws.rank * a.rs_rows : m0;
+          const int mlim = (COLL && a.ar == 2) ? a.rs_rows : a.M;
 #pragma unroll 1
           for (int cg0 = 0; cg0 < NG; cg0 += CH) {
             float v[CH][8], rv[CH][8];
@@ -576,7 +577,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                   }
                 }
               }
-              if (a.ar) {
+              if (COLL && a.ar) {
 #pragma unroll
                 for (int u = 0; u < CH; ++u) {
                   const size_t xoff = ((size_t)xtile * NG + cg0 + u) * (BM * 16) + (size_t)f * 16;  // exchange-buffer offset
@@ -594,7 +595,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 }
                 continue;
               }
-            } else {
+            } else if constexpr (COLL) {
               uint8_t* mine = symm_lam<uint8_t>(a.ws, a.ws.rank, par);
 #pragma unroll
               for (int u = 0; u < CH; ++u) {
@@ -619,7 +620,8 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 }
               }
             }
-            store_chunk<T, CH>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
+            if constexpr (COLL) store_chunk_t<T, CH, EPI_PLAIN, LLMSS_ACT_NONE>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
+            else store_chunk<T, CH>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
           }
         }
         if (full_tile && n_pass == 1) {
@@ -640,7 +642,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
   }
-  if (a.ar || a.ag) symm_finish(a.ws, epoch);
+  if constexpr (COLL) { if (a.ar || a.ag) symm_finish(a.ws, epoch); }
   if (threadIdx.x == 0) LLMSS_STAMP(7);
 }
 
@@ -1125,15 +1127,20 @@ int num_sms() {
   return g_num_sms;
 }
 
-template <typename T, int BN>
-int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
+template <typename T, int BN, bool COLL>
+int launch_coll(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
   using C = Cfg<BN>;
   static PerDeviceSmem configured;
-  auto kern = gemm_swapab_kernel<T, BN>;
+  auto kern = gemm_swapab_kernel<T, BN, COLL>;
   LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
   LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, a));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+template <typename T, int BN>
+int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
+  return (a.ar || a.ag) ? launch_coll<T, BN, true>(tw, tx, a, grid, stream) : launch_coll<T, BN, false>(tw, tx, a, grid, stream);
 }
 
 template <typename T, int BN, bool AR>

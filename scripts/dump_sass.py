@@ -20,8 +20,8 @@ OUT = os.path.join(ROOT, "profiles", "sass")
 
 # representative instantiations: (file stem, regex on the demangled name)
 PICK = [
-    ("gemm_swapab_bf16_bn64", r"gemm_swapab_kernel<__nv_bfloat16, 64>"),
-    ("gemm_swapab_bf16_bn256", r"gemm_swapab_kernel<__nv_bfloat16, 256>"),
+    ("gemm_swapab_bf16_bn64", r"gemm_swapab_kernel<__nv_bfloat16, 64, false>"),
+    ("gemm_swapab_bf16_bn256", r"gemm_swapab_kernel<__nv_bfloat16, 256, false>"),
     ("gemm_cluster_bf16_bn64", r"gemm_cluster_kernel<__nv_bfloat16, 64, false>"),
     ("gemm_cluster_allreduce_bf16_bn64", r"gemm_cluster_kernel<__nv_bfloat16, 64, true>"),
     ("attn_decode_tc_bf16_d256_r1", r"attn_decode_tc_kernel<__nv_bfloat16, 256, 1>"),

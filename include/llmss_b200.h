@@ -6,7 +6,7 @@
  * symmetric-memory set-up calls.  dtype: 0 = fp16, 1 = bf16, 2 = fp32.
  *
  * Each declaration cites the reference (jongwon-jay-lee/llmss) code it replaces; see
- * SURVEY.md sections 2.5 / 2.6 for the N*/G* numbering.
+ * SURVEY.md sections 2.5 / 2.6 for the N-number / G-number labels.
  */
 #ifndef LLMSS_B200_H_
 #define LLMSS_B200_H_
@@ -38,7 +38,43 @@ int llmss_symm_create(int rank, int nranks, void* const* peer_bases, size_t buf_
 int llmss_symm_destroy(llmss_symm_t* ws);
 int llmss_symm_epoch(llmss_symm_t* ws, uint32_t* out_host);
 
+/* ---- symmetric heap on the CUDA VMM API + NVLS multicast (csrc/vmm.cu) ----
+ * Each rank: llmss_vmm_padded_size (identical on all ranks) -> llmss_vmm_alloc -> llmss_symm_init_region on
+ * llmss_vmm_ptr -> llmss_vmm_export_fd once per peer, descriptor sent with llmss_fdx_send / received with
+ * llmss_fdx_recv (abstract Unix datagram sockets, SCM_RIGHTS) -> llmss_vmm_import.  Optional NVLS: rank 0
+ * llmss_mc_create + descriptor to every peer (llmss_mc_import), all llmss_mc_add_device, barrier, all
+ * llmss_mc_bind_and_map, barrier; llmss_vmm_mc_ptr is then the multicast mapping (a store lands on every GPU,
+ * multimem.ld_reduce sums all copies in the switch).  llmss_symm_create2 takes the peer mappings and that pointer
+ * (null: P2P only).  The reference has none of this: its buffers belong to NCCL (dist.py:44-73). */
+typedef struct llmss_vmm_region llmss_vmm_region;
+int llmss_vmm_caps(int* caps); /* bit 0: VMM + POSIX-fd handles, bit 1: multicast objects */
+int llmss_vmm_padded_size(size_t bytes, int nranks, int want_multicast, size_t* padded);
+int llmss_vmm_alloc(size_t padded, llmss_vmm_region** out);
+void* llmss_vmm_ptr(llmss_vmm_region* r);
+void* llmss_vmm_mc_ptr(llmss_vmm_region* r);
+size_t llmss_vmm_bytes(llmss_vmm_region* r);
+int llmss_vmm_export_fd(llmss_vmm_region* r, int* fd);
+int llmss_vmm_import(int fd, size_t padded, void** ptr); /* closes fd */
+int llmss_vmm_unmap(void* ptr, size_t padded);
+int llmss_vmm_free(llmss_vmm_region* r);
+int llmss_mc_create(int nranks, size_t padded, unsigned long long* mc, int* fd);
+int llmss_mc_import(int fd, unsigned long long* mc);
+int llmss_mc_add_device(unsigned long long mc);
+int llmss_mc_bind_and_map(unsigned long long mc, llmss_vmm_region* r);
+int llmss_mc_release(unsigned long long mc);
+int llmss_fdx_open(const char* name, int* sock);
+int llmss_fdx_send(int sock, const char* peer_name, int tag, int fd);
+int llmss_fdx_recv(int sock, int timeout_ms, int* tag, int* fd);
+int llmss_fdx_close(int sock);
+int llmss_fd_close(int fd);
+int llmss_symm_init_region(void* ptr, size_t buf_bytes, size_t lam_bytes); /* zero flags, arm the Lamport area */
+int llmss_symm_create2(int rank, int nranks, void* const* peer_bases, void* mc_base, size_t buf_bytes, size_t lam_bytes,
+                       llmss_symm_t** out);
+int llmss_symm_has_multicast(llmss_symm_t* ws);
+
 /* ---- K4 collectives over NVLink peer memory (N1/N2: layers.py:178,213; N3: layers.py:133) ---- */
+/* algo: 0 auto | 1 one-shot Lamport push | 2 two-shot with flags | 3 NVLS (stage locally, multimem.ld_reduce of the owned
+ * 1/t, multimem.st broadcast) | 4 two-shot on Lamport vectors (reduce-scatter by peer stores, multicast broadcast) */
 int llmss_allreduce(llmss_symm_t* ws, const void* in, void* out, int64_t n, int dtype, int algo,
                     llmss_stream_t stream);
 int llmss_allgather(llmss_symm_t* ws, const void* in, void* out, int64_t bytes, llmss_stream_t stream);
@@ -50,7 +86,7 @@ int llmss_allgather_cols(llmss_symm_t* ws, const void* in, void* out, int64_t ro
 /* ---- K5/K1/K2 tcgen05 GEMM (+ fused all-reduce epilogue) (G3,G4,G9,G10,G12,G14; layers.py:62,175-179) ---- */
 typedef struct llmss_gemm_plan {
   int bn, tiles, kb_total, grid;
-  int split; /* 0 = stream-K persistent kernel, 2..8 = thread-block-cluster split-K factor */
+  int split; /* 0 = stream-K persistent kernel, 1..8 = thread-block-cluster split-K factor (1: one CTA per tile) */
   int64_t sk_ws_floats;
   int64_t sk_counters;
   int64_t ar_bytes;
@@ -63,8 +99,10 @@ int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw, const voi
                int act_start, int gated, float* sk_ws, uint32_t* sk_counters, llmss_symm_t* ws, int max_ctas,
                llmss_stream_t stream);
 
-/* collective: 0 none | 1 GEMM -> all-reduce | 2 GEMM -> reduce-scatter over token rows (K2) |
- * 3 all-gather -> GEMM (K3: x is this rank's row shard, tiles are pulled from peers with TMA). */
+/* collective: 0 none | 1 GEMM -> all-reduce (exchange chosen by size and rank count) | 2 GEMM -> reduce-scatter over
+ * token rows (K2) | 3 all-gather -> GEMM (K3: x is this rank's row shard; shards are staged into every rank's own
+ * buffer -- one multicast store each when the heap is multicast-bound -- and TMA-read from local memory) |
+ * 4 / 5 / 6 pin the all-reduce exchange: in-switch multimem.ld_reduce / one-shot push / two-shot Lamport. */
 int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias, const void* residual,
                   int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype, int out_f32, int act,
                   int act_start, int gated, float* sk_ws, uint32_t* sk_counters, llmss_symm_t* ws, int max_ctas,
@@ -109,6 +147,14 @@ int llmss_attn_prefill(const void* q, int64_t ldq, const void* k, int64_t ldk, c
                        int64_t ldo, const int* cu_seqlens, int num_seqs, int max_seqlen, int total_tokens, int hq,
                        int hkv, int d, float scale, int dtype, llmss_stream_t stream);
 
+/* Multi-token queries over prior context (chunked prefill, prefix reuse; gptj_modeling.py:128-169 with a past,
+ * 229-233): same tcgen05 kernel, K / V tiles gathered page by page from the paged cache (which already holds this
+ * step's keys); seq_lens[i] includes the cu_q[i+1] - cu_q[i] new tokens; block_size 16 / 32 / 64; out may alias q. */
+int llmss_attn_prefill_paged(const void* q, int64_t ldq, const void* k_cache, const void* v_cache,
+                             const int* block_tables, int max_blocks, const int* seq_lens, void* out, int64_t ldo,
+                             const int* cu_q, int num_seqs, int max_q, int total_q, int hq, int hkv, int d,
+                             int block_size, int num_blocks, float scale, int dtype, llmss_stream_t stream);
+
 /* No counterpart in the reference (it has no native code and allocates freely through torch).
  * Same operation as llmss_attn_decode for hosts that cannot allocate: servers whose HBM is fully
  * committed to weights + KV pages, decode loops that cannot afford the device-wide sync of
@@ -134,7 +180,19 @@ int llmss_argmax_local(const float* logits, int64_t ld, int B, int n_valid, int 
 int llmss_argmax_merge(const void* cand_all, int nranks, int B, int* out_tokens, long long* out_tokens64,
                        llmss_stream_t stream);
 
-/* ---- K11 fused sampler (G15, G16, N6; generate.py:109-144) ---- */
+/* ---- K11 (general case) vocab-parallel top-k / top-p / temperature sampling (generate.py:109-126, layers.py:131-135):
+ * step 1 on every rank: one record of llmss_vp_record_floats(ks) floats per row -- [max, sum-exp, count, 0, vals[ks],
+ * idx[ks]] -- from its fp32 shard; gather the records with llmss_allgather_cols; step 2 on every rank: merge + draw
+ * (identical tokens everywhere, rng_state advanced).  Exact for 1 <= top_k <= ks; nranks * ks <= 1024. ---- */
+int llmss_vp_record_floats(int ks);
+int llmss_vp_summary(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, const int* greedy,
+                     const int* top_k, float* recs, int ks, llmss_stream_t stream);
+int llmss_vp_merge_sample(const float* recs_all, int nranks, int ks, int B, int vocab, const int* greedy,
+                          const float* temperature, const int* top_k, const float* top_p, uint32_t* rng_state,
+                          int* out_tokens, long long* out_tokens64, llmss_stream_t stream);
+
+/* ---- K11 fused sampler (G15, G16, N6; generate.py:109-144) ----
+ * rng_state: [B][2] = (request seed, tokens sampled so far); the draw depends on nothing else (not on the row). */
 int llmss_sample(const float* logits, int64_t ld, int B, int vocab, const int* greedy, const float* temperature,
                  const int* top_k, const float* top_p, uint32_t* rng_state, int* out_tokens,
                  long long* out_tokens64, llmss_stream_t stream);

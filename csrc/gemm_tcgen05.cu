@@ -73,6 +73,12 @@ struct CCfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/ + RECV_BYTES;
 };
 
+// all-gather mode: tensor maps over the gathered [M, K] activation in this rank's own bulk buffer, one per epoch
+// parity.  Passed as a kernel parameter (no host-to-device copy: the launch stays capturable in a CUDA graph).
+struct AgMaps {
+  CUtensorMap m[2];
+};
+
 struct GemmArgs {
   int M, N, K;
   int tiles_n, tiles_m, kb_total;
@@ -93,7 +99,6 @@ struct GemmArgs {
   int ag;                 // x rows are sharded over the ranks' symmetric buffers (all-gather fused into the loads)
   const void* ag_src;     // ag: this rank's [rs_rows, K] shard (row stride ag_ld), staged into the symmetric buffer
   int64_t ag_ld;
-  const CUtensorMap* ag_maps;  // ag: device array [2 parities] of maps over the gathered [M, K] activation (local)
   int tm_rot;                  // token-tile rotation: with ag, every rank starts on the tiles of its own shard
   unsigned long long* dbg;  // optional per-CTA phase timestamps [grid][8] (globaltimer ns), see llmss_gemm_set_debug
   SymmWs ws;
@@ -290,7 +295,7 @@ __device__ __forceinline__ float4 ld_dsmem_f4(uint32_t cluster_addr) {
 template <typename T, int BN, bool COLL>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
-                   const __grid_constant__ GemmArgs a) {
+                   const __grid_constant__ AgMaps ag_maps, const __grid_constant__ GemmArgs a) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -357,7 +362,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             asm volatile("fence.proxy.async.global;" ::: "memory");  // peers' generic stores -> our TMA reads
             acquired |= 1u << q;
           }
-          xmap = a.ag_maps + (epoch & 1);  // the gathered [M, K] activation in this rank's own bulk buffer
+          xmap = &ag_maps.m[epoch & 1];  // the gathered [M, K] activation in this rank's own bulk buffer
         }
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, 10);
@@ -1099,7 +1104,40 @@ PFN_encodeTiled get_encode() {
 }
 
 // 2-D row-major [rows, cols] 16-bit tensor with row stride `ld` elements; box = [box_rows, 64 cols], 128B swizzle.
+// cuTensorMapEncodeTiled costs a few microseconds of host time and every eager launch (prefill: 2-4 GEMMs x layers)
+// needs two maps; weights and the static activation buffers recur, so each host thread keeps the last 256 encodings.
+struct TmapKey {
+  const void* ptr;
+  int64_t rows, cols, ld;
+  int dtype, box_rows;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && dtype == o.dtype && box_rows == o.box_rows;
+  }
+};
+struct TmapCache {
+  static constexpr int N = 256;
+  TmapKey key[N];
+  CUtensorMap map[N];
+  bool used[N] = {false};
+};
+int make_tmap_uncached(CUtensorMap* map, const void* ptr, int dtype, int64_t rows, int64_t cols, int64_t ld, int box_rows);
 int make_tmap(CUtensorMap* map, const void* ptr, int dtype, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+  static thread_local TmapCache* cache = new TmapCache();
+  const TmapKey k{ptr, rows, cols, ld, dtype, box_rows};
+  uint64_t h = (uint64_t)(uintptr_t)ptr * 0x9E3779B97F4A7C15ull ^ (uint64_t)rows * 0xC2B2AE3D27D4EB4Full ^
+               (uint64_t)cols * 0x165667B19E3779F9ull ^ (uint64_t)(ld * 31 + box_rows * 7 + dtype);
+  const int slot = (int)((h >> 40) % TmapCache::N);
+  if (cache->used[slot] && cache->key[slot] == k) {
+    *map = cache->map[slot];
+    return 0;
+  }
+  if (int e = make_tmap_uncached(map, ptr, dtype, rows, cols, ld, box_rows)) return e;
+  cache->key[slot] = k;
+  cache->map[slot] = *map;
+  cache->used[slot] = true;
+  return 0;
+}
+int make_tmap_uncached(CUtensorMap* map, const void* ptr, int dtype, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
   PFN_encodeTiled enc = get_encode();
   LLMSS_REQUIRE(enc != nullptr, "gemm: cuTensorMapEncodeTiled entry point not available");
   LLMSS_REQUIRE(((uintptr_t)ptr % 16) == 0 && (ld * 2) % 16 == 0, "gemm: operand base / row stride must be 16-byte aligned");
@@ -1128,19 +1166,19 @@ int num_sms() {
 }
 
 template <typename T, int BN, bool COLL>
-int launch_coll(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
+int launch_coll(const CUtensorMap& tw, const CUtensorMap& tx, const AgMaps& ag, const GemmArgs& a, int grid, cudaStream_t stream) {
   using C = Cfg<BN>;
   static PerDeviceSmem configured;
   auto kern = gemm_swapab_kernel<T, BN, COLL>;
   LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
-  LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, a));
+  LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, ag, a));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 template <typename T, int BN>
-int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
-  return (a.ar || a.ag) ? launch_coll<T, BN, true>(tw, tx, a, grid, stream) : launch_coll<T, BN, false>(tw, tx, a, grid, stream);
+int launch(const CUtensorMap& tw, const CUtensorMap& tx, const AgMaps& ag, const GemmArgs& a, int grid, cudaStream_t stream) {
+  return (a.ar || a.ag) ? launch_coll<T, BN, true>(tw, tx, ag, a, grid, stream) : launch_coll<T, BN, false>(tw, tx, ag, a, grid, stream);
 }
 
 template <typename T, int BN, bool AR>
@@ -1273,10 +1311,17 @@ LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_b
 LLMSS_API int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p) {
   return llmss_gemm_plan_query2(M, N, K, nranks, elem_bytes, max_ctas, LLMSS_BF16, p);
 }
-static int g_force_bn = 0;  // set (host-side, transiently) by the reduce-scatter / all-gather modes
+static int gemm_plan_impl(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype, int force_bn,
+                          llmss_gemm_plan* p);
 LLMSS_API int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype,
                                      llmss_gemm_plan* p) {
-  const int bn = g_force_bn > 0 ? g_force_bn : pick_bn(M);
+  return gemm_plan_impl(M, N, K, nranks, elem_bytes, max_ctas, dtype, 0, p);
+}
+// force_bn > 0: token-tile width imposed by the reduce-scatter / all-gather modes (an argument, not a global: two host
+// threads may plan GEMMs at the same time)
+static int gemm_plan_impl(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype, int force_bn,
+                          llmss_gemm_plan* p) {
+  const int bn = force_bn > 0 ? force_bn : pick_bn(M);
   const int tiles_n = (N + BM - 1) / BM, tiles_m = (M + bn - 1) / bn;
   const int tiles = tiles_n * tiles_m;
   const int kb_total = (K + BK - 1) / BK;
@@ -1332,7 +1377,7 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
 
 // collective: 0 none | 1 GEMM -> all-reduce | 2 GEMM -> reduce-scatter over token rows (out / residual are this
 // rank's [M/t, N] shard) | 3 all-gather -> GEMM (x is this rank's [M/t, K] shard; M is the gathered row count;
-// ag_maps_dev: 64-byte aligned device scratch of 2 * 8 * 128 bytes for the peer tensor maps).
+// ag_maps_dev: unused (kept for ABI compatibility; the tensor maps of the gathered activation are kernel parameters)).
 LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
                             const void* residual, int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype,
                             int out_f32, int act, int act_start, int gated, float* sk_ws, uint32_t* sk_counters,
@@ -1348,7 +1393,7 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   LLMSS_REQUIRE(!((ar || rs) && (gated || act != LLMSS_ACT_NONE || out_f32)),
                 "gemm: fused all-reduce / reduce-scatter support bias/residual epilogues only");
   llmss_gemm_plan p;
-  int rs_rows = 0;
+  int rs_rows = 0, force_bn = 0;
   if (rs || ag) {
     // token rows are owned by ranks in contiguous blocks; tiles must not straddle two owners, so the
     // token tile is the largest power of two (16..256) that divides the rows per rank
@@ -1357,10 +1402,9 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
     int bn = 256;
     while (bn > 16 && rs_rows % bn != 0) bn >>= 1;
     LLMSS_REQUIRE(rs_rows % bn == 0, "gemm: rows per rank (%d) must be a multiple of 16", rs_rows);
-    g_force_bn = bn;
+    force_bn = bn;
   }
-  llmss_gemm_plan_query2(M, N, K, (ar || rs) ? ws->nranks : 1, 2, max_ctas, dtype, &p);
-  g_force_bn = 0;
+  gemm_plan_impl(M, N, K, (ar || rs) ? ws->nranks : 1, 2, max_ctas, dtype, force_bn, &p);
   if (rs || ag) {
     p.split = 0;  // these modes live in the persistent stream-K kernel
     int sms = max_ctas > 0 ? max_ctas : num_sms();
@@ -1401,21 +1445,20 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
                   ws->lam_bytes);
   }
   CUtensorMap tw, tx;
+  AgMaps ag_maps;  // only read by the kernel in all-gather mode
   memset(&tx, 0, sizeof(tx));
+  memset(&ag_maps, 0, sizeof(ag_maps));
+  (void)ag_maps_dev;  // older callers pass a device scratch for the maps: no longer needed
   if (int e = make_tmap(&tw, w, dtype, N, K, ldw, BM)) return e;
   if (ag) {
     // x is this rank's [rs_rows, K] shard; every rank stages its shard in its symmetric bulk buffer and the
     // kernel's TMA producer pulls token tiles from the owners (peer HBM over NVLink).
-    LLMSS_REQUIRE(ag_maps_dev != nullptr && ((uintptr_t)ag_maps_dev % 64) == 0, "gemm: all-gather mode needs a 64-byte aligned map scratch");
     LLMSS_REQUIRE((size_t)M * K * 2 <= ws->buf_bytes, "gemm: gathered activation of %zu bytes exceeds the symmetric bulk buffer (%zu)",
                   (size_t)M * K * 2, ws->buf_bytes);
-    CUtensorMap maps[2];
-    memset(maps, 0, sizeof(maps));
     for (int par = 0; par < 2; ++par) {
       const char* base = ws->peer_base[ws->rank] + kSymmDataOffset + 2 * ws->lam_bytes + (size_t)par * ws->buf_bytes;
-      if (int e = make_tmap(&maps[par], base, dtype, M, K, K, p.bn)) return e;
+      if (int e = make_tmap(&ag_maps.m[par], base, dtype, M, K, K, p.bn)) return e;
     }
-    LLMSS_CHECK_CUDA(cudaMemcpyAsync(ag_maps_dev, maps, sizeof(maps), cudaMemcpyHostToDevice, stream));
     if (int e = make_tmap(&tx, x, dtype, rs_rows, K, ldx, p.bn)) return e;  // this rank's own shard, read in place
   } else {
     if (int e = make_tmap(&tx, x, dtype, M, K, ldx, p.bn)) return e;
@@ -1438,12 +1481,11 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   a.ag = ag ? 1 : 0;
   a.ag_src = x;
   a.ag_ld = ldx;
-  a.ag_maps = reinterpret_cast<const CUtensorMap*>(ag_maps_dev);
   a.tm_rot = ag ? ws->rank * (rs_rows / p.bn) : 0;
   a.dbg = g_dbg;
   if (collective) a.ws = *ws;
 #define LLMSS_LAUNCH(T_, BN_) \
-  return p.split > 0 ? launch_cluster<T_, BN_>(tw, tx, a, p.tiles, p.split, stream) : launch<T_, BN_>(tw, tx, a, p.grid, stream)
+  return p.split > 0 ? launch_cluster<T_, BN_>(tw, tx, a, p.tiles, p.split, stream) : launch<T_, BN_>(tw, tx, ag_maps, a, p.grid, stream)
   if (dtype == LLMSS_F16) {
     switch (p.bn) {
       case 16: LLMSS_LAUNCH(__half, 16);

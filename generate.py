@@ -11,6 +11,7 @@ Differences from the reference (all deliberate):
   * generation stops at the model's maximum length instead of a sliding window (Q7).
 Extra flags: --dtype {float16,bfloat16,float32} (default float16 like the reference), --seed.
 """
+import os
 from argparse import ArgumentParser
 from time import time
 
@@ -71,7 +72,9 @@ def main(argv=None):
 
     params = SamplingParams(max_new_tokens=args.max_new_tokens, is_greedy=args.is_greedy, temperature=args.temperature,
                             top_p=args.top_p, top_k=args.top_k, seed=args.seed)
-    outputs = engine.generate(prompt_ids, params)
+    # --use_cache off: the reference recomputes the whole sequence every step (generate.py:147-190); same tokens, O(S^2)
+    outputs = engine.generate(prompt_ids, params) if (args.use_cache or os.environ.get("LLMSS_ALWAYS_CACHE", "0") == "1") \
+        else engine.generate_no_cache(prompt_ids, params)
 
     if rank == 0:
         end_time = time()

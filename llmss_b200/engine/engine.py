@@ -216,3 +216,35 @@ class Engine:
                 if o.request_id in out and o.token >= 0:
                     out[o.request_id].append(o.token)
         return [out[i] for i in ids]
+
+    def generate_no_cache(self, prompts: Sequence[Sequence[int]], params=None) -> List[List[int]]:
+        """The reference's generation mode without `--use_cache` (generate.py:147-190): every step recomputes the whole
+        sequence (prompt + tokens so far) and keeps nothing between steps.  O(S^2) per token; kept for CLI parity and as
+        an independent check of the cached path -- it samples with the same RNG streams, so it returns the same tokens."""
+        from .runner import request_seed
+
+        if params is None or isinstance(params, SamplingParams):
+            params = [params or SamplingParams()] * len(prompts)
+        r = self.runner
+        outs: List[List[int]] = [[] for _ in prompts]
+        live = list(range(len(prompts)))
+        step = 0
+        while live:
+            seqs = []
+            for i in live:
+                s = SeqState(self._next_id + i, list(prompts[i]) + outs[i], params[i], eos=self.eos_token_id)
+                seqs.append(s)
+            # the counter RNG of request i has already produced len(outs[i]) draws
+            toks = r.prefill(seqs, rng_steps=[len(outs[i]) for i in live])
+            for s in seqs:
+                r.release(s)
+            nxt = []
+            for i, t in zip(live, toks):
+                outs[i].append(int(t))
+                full = len(prompts[i]) + len(outs[i]) >= r.max_seq_len
+                if len(outs[i]) < params[i].max_new_tokens and not full and not (self.eos_token_id is not None and t == self.eos_token_id):
+                    nxt.append(i)
+            live = nxt
+            step += 1
+        self._next_id += len(prompts)
+        return outs

@@ -184,7 +184,7 @@ class ModelRunner:
 
     # ------------------------------------------------------------------ prefill
     @torch.no_grad()
-    def prefill(self, seqs: Sequence[SeqState]) -> List[int]:
+    def prefill(self, seqs: Sequence[SeqState], rng_steps: Optional[Sequence[int]] = None) -> List[int]:
         """Run the prompts of ``seqs`` (packed, no padding) and sample their first tokens.
 
         With ``prefill_chunk`` set, prompts are fed in rounds of at most that many tokens per sequence: round r
@@ -213,7 +213,8 @@ class ModelRunner:
         temp = torch.tensor([s.params.temperature for s in seqs], dtype=torch.float32, device=dev)
         top_k = torch.tensor([s.params.top_k for s in seqs], dtype=torch.int32, device=dev)
         top_p = torch.tensor([s.params.top_p for s in seqs], dtype=torch.float32, device=dev)
-        rng = torch.tensor([[request_seed(s.params, s.seq_id), 0] for s in seqs], dtype=torch.int32, device=dev)
+        steps = list(rng_steps) if rng_steps is not None else [0] * len(seqs)
+        rng = torch.tensor([[request_seed(s.params, s.seq_id), st] for s, st in zip(seqs, steps)], dtype=torch.int32, device=dev)
         toks = ops.sample(logits, greedy, temp, top_k, top_p, rng, vocab=self.spec.vocab).tolist()
         for s, t in zip(seqs, toks):
             s.length = len(s.prompt)

@@ -112,3 +112,18 @@ def test_chunked_prefill_matches_whole_prompt_prefill(tmp_path):
     a, b = whole.generate(prompts, sp), chunked.generate(prompts, sp)
     assert a == b
     assert a[0] == _hf_greedy(hf, prompts[0], 5)
+
+
+def test_no_cache_mode_matches_cached_generation(tmp_path):
+    """The reference's `--use_cache`-off loop (whole sequence recomputed every step) must give the cached tokens,
+    greedy and sampled (same per-request RNG stream)."""
+    cfg, hf = make_tiny("gptj", tmp_path)
+    torch.manual_seed(2)
+    prompts = [torch.randint(0, cfg.vocab_size, (n,)).tolist() for n in (6, 3, 9)]
+    eng = Engine.from_pretrained(str(tmp_path), dtype=torch.float32, device="cpu", max_batch=4, max_seq_len=64)
+    g = SamplingParams(max_new_tokens=6, is_greedy=True)
+    assert eng.generate_no_cache(prompts, g) == eng.generate(prompts, g)
+    assert eng.generate_no_cache(prompts, g)[0] == _hf_greedy(hf, prompts[0], 6)
+    sp = SamplingParams(max_new_tokens=6, top_k=20, top_p=0.9, temperature=0.8, seed=21)
+    assert eng.generate_no_cache(prompts, sp) == eng.generate(prompts, sp)
+    assert eng.runner.alloc.num_free == eng.runner.alloc.num_blocks - 1

@@ -74,7 +74,7 @@ struct CCfg {
 };
 
 // all-gather mode: tensor maps over the gathered [M, K] activation in this rank's own bulk buffer, one per epoch
-// parity.  Passed as a kernel parameter (no host-to-device copy: the launch stays capturable in a CUDA graph).
+// parity (built on the host, copied to a caller-provided device scratch per call).
 struct AgMaps {
   CUtensorMap m[2];
 };
@@ -99,6 +99,7 @@ struct GemmArgs {
   int ag;                 // x rows are sharded over the ranks' symmetric buffers (all-gather fused into the loads)
   const void* ag_src;     // ag: this rank's [rs_rows, K] shard (row stride ag_ld), staged into the symmetric buffer
   int64_t ag_ld;
+  const CUtensorMap* ag_maps;  // ag: device array [2 parities] of maps over the gathered [M, K] activation (local)
   int tm_rot;                  // token-tile rotation: with ag, every rank starts on the tiles of its own shard
   unsigned long long* dbg;  // optional per-CTA phase timestamps [grid][8] (globaltimer ns), see llmss_gemm_set_debug
   SymmWs ws;
@@ -295,7 +296,7 @@ __device__ __forceinline__ float4 ld_dsmem_f4(uint32_t cluster_addr) {
 template <typename T, int BN, bool COLL>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
-                   const __grid_constant__ AgMaps ag_maps, const __grid_constant__ GemmArgs a) {
+                   const __grid_constant__ GemmArgs a) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -362,7 +363,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             asm volatile("fence.proxy.async.global;" ::: "memory");  // peers' generic stores -> our TMA reads
             acquired |= 1u << q;
           }
-          xmap = &ag_maps.m[epoch & 1];  // the gathered [M, K] activation in this rank's own bulk buffer
+          xmap = a.ag_maps + (epoch & 1);  // the gathered [M, K] activation in this rank's own bulk buffer
         }
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, 10);
@@ -625,7 +626,8 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 }
               }
             }
-            if constexpr (COLL) store_chunk_t<T, CH, EPI_PLAIN, LLMSS_ACT_NONE>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
+            // all-reduce / reduce-scatter epilogues are plain (bias + residual); all-gather -> GEMM keeps every flavour
+            if (COLL && a.ar) store_chunk_t<T, CH, EPI_PLAIN, LLMSS_ACT_NONE>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
             else store_chunk<T, CH>(a, v, rv, n, mrow0 + cg0 * 8, lane, bval, mlim);
           }
         }
@@ -1166,19 +1168,19 @@ int num_sms() {
 }
 
 template <typename T, int BN, bool COLL>
-int launch_coll(const CUtensorMap& tw, const CUtensorMap& tx, const AgMaps& ag, const GemmArgs& a, int grid, cudaStream_t stream) {
+int launch_coll(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
   using C = Cfg<BN>;
   static PerDeviceSmem configured;
   auto kern = gemm_swapab_kernel<T, BN, COLL>;
   LLMSS_CHECK_CUDA(configured.ensure(kern, C::SMEM_BYTES));
-  LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, ag, a));
+  LLMSS_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), (size_t)C::SMEM_BYTES, stream, tw, tx, a));
   LLMSS_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 template <typename T, int BN>
-int launch(const CUtensorMap& tw, const CUtensorMap& tx, const AgMaps& ag, const GemmArgs& a, int grid, cudaStream_t stream) {
-  return (a.ar || a.ag) ? launch_coll<T, BN, true>(tw, tx, ag, a, grid, stream) : launch_coll<T, BN, false>(tw, tx, ag, a, grid, stream);
+int launch(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int grid, cudaStream_t stream) {
+  return (a.ar || a.ag) ? launch_coll<T, BN, true>(tw, tx, a, grid, stream) : launch_coll<T, BN, false>(tw, tx, a, grid, stream);
 }
 
 template <typename T, int BN, bool AR>
@@ -1377,7 +1379,7 @@ LLMSS_API int llmss_gemm(const void* x, int64_t ldx, const void* w, int64_t ldw,
 
 // collective: 0 none | 1 GEMM -> all-reduce | 2 GEMM -> reduce-scatter over token rows (out / residual are this
 // rank's [M/t, N] shard) | 3 all-gather -> GEMM (x is this rank's [M/t, K] shard; M is the gathered row count;
-// ag_maps_dev: unused (kept for ABI compatibility; the tensor maps of the gathered activation are kernel parameters)).
+// ag_maps_dev: 64-byte aligned device scratch of 2 * 128 bytes for the tensor maps of the gathered activation).
 LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
                             const void* residual, int64_t ldr, void* out, int64_t ldo, int M, int N, int K, int dtype,
                             int out_f32, int act, int act_start, int gated, float* sk_ws, uint32_t* sk_counters,
@@ -1445,20 +1447,23 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
                   ws->lam_bytes);
   }
   CUtensorMap tw, tx;
-  AgMaps ag_maps;  // only read by the kernel in all-gather mode
+  AgMaps ag_maps;  // all-gather mode only
   memset(&tx, 0, sizeof(tx));
   memset(&ag_maps, 0, sizeof(ag_maps));
-  (void)ag_maps_dev;  // older callers pass a device scratch for the maps: no longer needed
   if (int e = make_tmap(&tw, w, dtype, N, K, ldw, BM)) return e;
   if (ag) {
     // x is this rank's [rs_rows, K] shard; every rank stages its shard in its symmetric bulk buffer and the
     // kernel's TMA producer pulls token tiles from the owners (peer HBM over NVLink).
+    LLMSS_REQUIRE(ag_maps_dev != nullptr && ((uintptr_t)ag_maps_dev % 64) == 0, "gemm: all-gather mode needs a 64-byte aligned map scratch");
     LLMSS_REQUIRE((size_t)M * K * 2 <= ws->buf_bytes, "gemm: gathered activation of %zu bytes exceeds the symmetric bulk buffer (%zu)",
                   (size_t)M * K * 2, ws->buf_bytes);
     for (int par = 0; par < 2; ++par) {
       const char* base = ws->peer_base[ws->rank] + kSymmDataOffset + 2 * ws->lam_bytes + (size_t)par * ws->buf_bytes;
       if (int e = make_tmap(&ag_maps.m[par], base, dtype, M, K, K, p.bn)) return e;
     }
+    // the maps live in device memory (copied per call from this stack frame: pageable source, so the copy is staged
+    // synchronously and the launch is NOT capturable in a CUDA graph in this mode)
+    LLMSS_CHECK_CUDA(cudaMemcpyAsync(ag_maps_dev, &ag_maps, sizeof(ag_maps), cudaMemcpyHostToDevice, stream));
     if (int e = make_tmap(&tx, x, dtype, rs_rows, K, ldx, p.bn)) return e;  // this rank's own shard, read in place
   } else {
     if (int e = make_tmap(&tx, x, dtype, M, K, ldx, p.bn)) return e;
@@ -1481,11 +1486,12 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
   a.ag = ag ? 1 : 0;
   a.ag_src = x;
   a.ag_ld = ldx;
+  a.ag_maps = reinterpret_cast<const CUtensorMap*>(ag_maps_dev);
   a.tm_rot = ag ? ws->rank * (rs_rows / p.bn) : 0;
   a.dbg = g_dbg;
   if (collective) a.ws = *ws;
 #define LLMSS_LAUNCH(T_, BN_) \
-  return p.split > 0 ? launch_cluster<T_, BN_>(tw, tx, a, p.tiles, p.split, stream) : launch<T_, BN_>(tw, tx, ag_maps, a, p.grid, stream)
+  return p.split > 0 ? launch_cluster<T_, BN_>(tw, tx, a, p.tiles, p.split, stream) : launch<T_, BN_>(tw, tx, a, p.grid, stream)
   if (dtype == LLMSS_F16) {
     switch (p.bn) {
       case 16: LLMSS_LAUNCH(__half, 16);

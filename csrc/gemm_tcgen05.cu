@@ -1287,7 +1287,16 @@ int pick_cluster_split(int tiles, int kb_total, int bn, int sms, int dtype) {
   return 0;
 }
 
-int pick_bn(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256; }
+int pick_bn(int M) {
+  static int max_bn = -1;  // LLMSS_GEMM_MAX_BN caps the token-tile width (A/B aid: 128 halves the epilogue of a CTA at M = 256)
+  if (max_bn < 0) {
+    const char* e = getenv("LLMSS_GEMM_MAX_BN");
+    max_bn = (e != nullptr) ? atoi(e) : 256;
+    if (max_bn != 16 && max_bn != 32 && max_bn != 64 && max_bn != 128) max_bn = 256;
+  }
+  const int bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
+  return bn < max_bn ? bn : max_bn;
+}
 
 }  // namespace
 

@@ -6,7 +6,7 @@ Here every call site goes through a :class:`Communicator`, which picks per messa
 
   * world_size == 1 / `FakeGroup`         -> no-op (fixes SURVEY Q2)
   * CUDA + symmetric-memory workspace       -> hand-written one-shot / two-shot P2P kernels
-                                              over NVLink (csrc/allreduce.cu), CUDA-graph safe
+                                              over NVLink / NVSwitch multicast (csrc/comm.cu), CUDA-graph safe
   * otherwise (CPU gloo, or message too big for the workspace) -> torch.distributed
 
 The fused GEMM->all-reduce kernel does not go through here at all: it owns the same

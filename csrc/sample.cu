@@ -392,11 +392,12 @@ __global__ void argmax_merge_kernel(const Cand* __restrict__ cand, int nranks, i
 // value, nucleus, temperature, one draw with the request's counter RNG.  An element >= the global k-th value is
 // >= its own rank's local k-th value, so the union is complete and the result equals sample_kernel's on the
 // gathered logits (oracle: ops/reference.py:sample_vocab_parallel).
-// Record layout (floats): [max, sumexp, count(int), 0, vals[KS], idx[KS](int)].
+// Record layout (floats): [max, sumexp, count(int), sumexp at the row's temperature (top_k = 0 rows), vals[KS], idx[KS](int)].
 __global__ void __launch_bounds__(kThreads) vp_summary_kernel(const float* __restrict__ logits, int64_t ld, int n_valid,
                                                               int idx_offset, const int* __restrict__ greedy,
-                                                              const int* __restrict__ top_k, float* __restrict__ recs,
-                                                              int KS) {
+                                                              const int* __restrict__ top_k,
+                                                              const float* __restrict__ temperature,
+                                                              float* __restrict__ recs, int KS) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float red[32];
@@ -428,13 +429,21 @@ __global__ void __launch_bounds__(kThreads) vp_summary_kernel(const float* __res
   float part = 0.f;
   for (int i = tid; i < n_valid; i += kThreads) part += __expf(x[i] - xmax);
   const float sumexp = block_sum_f(part, red);
+  // rows sampled from the whole distribution (top_k = 0) also need the weight sum at their temperature
+  float sumexp_t = 0.f;
+  if (!greedy[row] && top_k[row] <= 0 && temperature != nullptr) {
+    const float inv_t = 1.0f / temperature[row];
+    float pt = 0.f;
+    for (int i = tid; i < n_valid; i += kThreads) pt += __expf((x[i] - xmax) * inv_t);
+    sumexp_t = block_sum_f(pt, red);
+  }
   int k = greedy[row] ? 1 : top_k[row];
   if (k <= 0 || k > KS) k = KS;
   if (k > n_valid) k = n_valid;
   const uint32_t thr_key = block_radix_kth(x, n_valid, k, hist, &s_prefix, &s_krem);
   int count = block_gather_sorted(x, n_valid, thr_key, idx_offset, cval, cidx, &s_count);
   count = min(count, KS);  // more than KS - k + 1 exact ties at the k-th value: the highest indices are dropped
-  if (tid == 0) { rec[0] = xmax; rec[1] = sumexp; reinterpret_cast<int*>(rec)[2] = count; rec[3] = 0.f; }
+  if (tid == 0) { rec[0] = xmax; rec[1] = sumexp; reinterpret_cast<int*>(rec)[2] = count; rec[3] = sumexp_t; }
   for (int i = tid; i < count; i += kThreads) {
     rec[4 + i] = cval[i];
     reinterpret_cast<int*>(rec)[4 + KS + i] = cidx[i];
@@ -506,6 +515,131 @@ __global__ void __launch_bounds__(kThreads) vp_merge_sample_kernel(
   }
 }
 
+// ---- vocab-parallel draw from the WHOLE distribution (top_k = 0, top_p = 1: what the reference's sampling loop
+// effectively does, quirk Q1).  From the gathered record headers every rank knows the global max and every rank's
+// weight sum at the row's temperature, hence the total and each rank's CDF interval in rank (= index) order.  The
+// one rank whose interval holds u * total walks its own shard for the token; 16 bytes per row are gathered and
+// the owner's answer replaces the row's token.  Runs BEFORE vp_merge_sample (which advances the RNG counter).
+__global__ void __launch_bounds__(kThreads) vp_multinomial_pick_kernel(
+    const float* __restrict__ logits, int64_t ld, int n_valid, int idx_offset, const float* __restrict__ recs_all,
+    int nranks, int rank, int KS, const int* __restrict__ greedy, const float* __restrict__ temperature,
+    const int* __restrict__ top_k, const float* __restrict__ top_p, const uint32_t* __restrict__ rng_state,
+    int* __restrict__ cand /* [B][4] */) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float red[32];
+  __shared__ int s_owner_thread;
+  __shared__ int s_pick;
+  __shared__ float s_f;
+  const int row = blockIdx.x, tid = threadIdx.x;
+  int* my = cand + (int64_t)row * 4;
+  const bool plain = !greedy[row] && top_k[row] <= 0 && top_p[row] >= 1.0f;
+  if (!plain) {
+    if (tid == 0) { my[0] = -1; my[1] = my[2] = my[3] = 0; }
+    return;
+  }
+  const int rf = 4 + 2 * KS;
+  const float* base = recs_all + (int64_t)row * nranks * rf;
+  const float inv_t = 1.0f / temperature[row];
+  float M = -INFINITY;
+  for (int r = 0; r < nranks; ++r) M = fmaxf(M, base[(int64_t)r * rf]);
+  float lower = 0.f, mine_w = 0.f, total = 0.f;
+  int last_nonempty = -1;
+  for (int r = 0; r < nranks; ++r) {  // rank order = index order; identical arithmetic on every rank
+    const float s_r = base[(int64_t)r * rf + 3];
+    const float w = s_r > 0.f ? s_r * __expf((base[(int64_t)r * rf] - M) * inv_t) : 0.f;
+    if (r == rank) { lower = total; mine_w = w; }
+    if (w > 0.f) last_nonempty = r;
+    total += w;
+  }
+  const float u01 = rng_uniform(rng_state[2 * row], rng_state[2 * row + 1]);
+  const float target = u01 * total;
+  // owner = first rank whose upper bound exceeds the target; the last non-empty rank also takes target >= total
+  int owner = last_nonempty;
+  {
+    float acc = 0.f;
+    for (int r = 0; r < nranks; ++r) {
+      const float s_r = base[(int64_t)r * rf + 3];
+      const float w = s_r > 0.f ? s_r * __expf((base[(int64_t)r * rf] - M) * inv_t) : 0.f;
+      acc += w;
+      if (w > 0.f && target < acc) { owner = r; break; }
+    }
+  }
+  if (owner != rank || n_valid <= 0) {
+    if (tid == 0) { my[0] = -1; my[1] = my[2] = my[3] = 0; }
+    return;
+  }
+  // local units: weights relative to this rank's own maximum
+  const float xmax = base[(int64_t)rank * rf];
+  const float s_local = base[(int64_t)rank * rf + 3];
+  const float t_local = fminf(fmaxf((target - lower) / fmaxf(mine_w, 1e-30f), 0.f), 1.f) * s_local;
+  const float* x = logits + (int64_t)row * ld;
+  const int per = (n_valid + kThreads - 1) / kThreads;
+  const int i0 = tid * per, i1 = min(n_valid, i0 + per);
+  float part = 0.f;
+  for (int i = i0; i < i1; ++i) part += __expf((x[i] - xmax) * inv_t);
+  float incl = part;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    float n = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((tid & 31) >= o) incl += n;
+  }
+  if ((tid & 31) == 31) red[tid >> 5] = incl;
+  if (tid == 0) { s_owner_thread = kThreads; s_pick = -1; }
+  __syncthreads();
+  if (tid < 32) {
+    float w = red[tid], wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      float n = __shfl_up_sync(0xffffffffu, wi, o);
+      if (tid >= o) wi += n;
+    }
+    red[tid] = wi - w;
+    if (tid == 31) s_f = wi;
+  }
+  __syncthreads();
+  const float cum = red[tid >> 5] + incl;
+  if (part > 0.f && t_local < cum) atomicMin(&s_owner_thread, tid);
+  __syncthreads();
+  if (tid == s_owner_thread) {
+    float c = cum - part;
+    int pick = -1, last_pos = -1;
+    for (int i = i0; i < i1; ++i) {
+      const float w = __expf((x[i] - xmax) * inv_t);
+      c += w;
+      if (w > 0.f) last_pos = i;
+      if (t_local < c) { pick = i; break; }
+    }
+    s_pick = pick >= 0 ? pick : last_pos;
+  }
+  __syncthreads();
+  if (s_owner_thread == kThreads) {
+    // rounding left the target past this shard's total: the last token of positive weight
+    int lp = -1;
+    for (int i = i1 - 1; i >= i0; --i)
+      if (__expf((x[i] - xmax) * inv_t) > 0.f) { lp = i; break; }
+    if (lp >= 0) atomicMax(&s_pick, lp);
+    __syncthreads();
+  }
+  if (tid == 0) {
+    my[0] = (s_pick >= 0 ? s_pick : 0) + idx_offset;
+    my[1] = my[2] = my[3] = 0;
+  }
+}
+
+__global__ void vp_multinomial_merge_kernel(const int* __restrict__ cand_all, int nranks, int B, int* __restrict__ out32,
+                                            long long* __restrict__ out64) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= B) return;
+  int tok = -1;
+  for (int r = 0; r < nranks; ++r) tok = max(tok, cand_all[((int64_t)row * nranks + r) * 4]);
+  if (tok < 0) return;  // not a whole-distribution row: keep what vp_merge_sample wrote
+  if (out32) out32[row] = tok;
+  if (out64) out64[row] = tok;
+}
+
 }  // namespace
 
 // cand: [B] 16-byte records (this rank's best logit of each row and its global vocabulary index).
@@ -532,12 +666,12 @@ LLMSS_API int llmss_argmax_merge(const void* cand_all, int nranks, int B, int* o
 // (even, so records are 16-byte multiples; 1 <= top_k <= ks is exact; nranks * ks <= 1024).
 LLMSS_API int llmss_vp_record_floats(int ks) { return 4 + 2 * ks; }
 LLMSS_API int llmss_vp_summary(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, const int* greedy,
-                               const int* top_k, float* recs, int ks, cudaStream_t stream) {
+                               const int* top_k, const float* temperature, float* recs, int ks, cudaStream_t stream) {
   LLMSS_REQUIRE(ks >= 2 && ks <= kMaxCand && ks % 2 == 0, "vp_summary: ks=%d must be even and within [2, %d]", ks, kMaxCand);
   LLMSS_REQUIRE(n_valid >= 0 && ld >= n_valid, "vp_summary: bad shard width");
   if (B == 0) return 0;
   LLMSS_CHECK_CUDA(launch_pdl(vp_summary_kernel, dim3(B), dim3(kThreads), 0, stream, logits, ld, n_valid, idx_offset,
-                              greedy, top_k, recs, ks));
+                              greedy, top_k, temperature, recs, ks));
   return 0;
 }
 // Step 2 (every rank, on the column-gathered records [B][nranks][record]): merge + sample; advances rng_state.
@@ -549,6 +683,28 @@ LLMSS_API int llmss_vp_merge_sample(const float* recs_all, int nranks, int ks, i
   if (B == 0) return 0;
   LLMSS_CHECK_CUDA(launch_pdl(vp_merge_sample_kernel, dim3(B), dim3(kThreads), 0, stream, recs_all, nranks, ks, vocab,
                               greedy, temperature, top_k, top_p, rng_state, out_tokens, out_tokens64));
+  return 0;
+}
+
+// Whole-distribution rows (top_k = 0, top_p = 1) of a vocab-parallel batch.  Call order per step: llmss_vp_summary ->
+// gather records -> llmss_vp_multinomial_pick (every rank, on its shard + the gathered records; does NOT advance the RNG)
+// -> gather `cand` ([B][4] int32, 16 bytes per row) with llmss_allgather_cols -> llmss_vp_merge_sample (all rows, advances
+// the RNG) -> llmss_vp_multinomial_merge (overwrites the tokens of the whole-distribution rows).
+LLMSS_API int llmss_vp_multinomial_pick(const float* logits, int64_t ld, int B, int n_valid, int idx_offset,
+                                        const float* recs_all, int nranks, int rank, int ks, const int* greedy,
+                                        const float* temperature, const int* top_k, const float* top_p,
+                                        const uint32_t* rng_state, int* cand, cudaStream_t stream) {
+  LLMSS_REQUIRE(nranks >= 1 && nranks <= 8 && rank >= 0 && rank < nranks, "vp_multinomial_pick: bad rank %d of %d", rank, nranks);
+  if (B == 0) return 0;
+  LLMSS_CHECK_CUDA(launch_pdl(vp_multinomial_pick_kernel, dim3(B), dim3(kThreads), 0, stream, logits, ld, n_valid, idx_offset,
+                              recs_all, nranks, rank, ks, greedy, temperature, top_k, top_p, rng_state, cand));
+  return 0;
+}
+LLMSS_API int llmss_vp_multinomial_merge(const int* cand_all, int nranks, int B, int* out_tokens, long long* out_tokens64,
+                                         cudaStream_t stream) {
+  if (B == 0) return 0;
+  LLMSS_CHECK_CUDA(launch_pdl(vp_multinomial_merge_kernel, dim3((B + 127) / 128), dim3(128), 0, stream, cand_all, nranks, B,
+                              out_tokens, out_tokens64));
   return 0;
 }
 

@@ -181,12 +181,21 @@ int llmss_argmax_merge(const void* cand_all, int nranks, int B, int* out_tokens,
                        llmss_stream_t stream);
 
 /* ---- K11 (general case) vocab-parallel top-k / top-p / temperature sampling (generate.py:109-126, layers.py:131-135):
- * step 1 on every rank: one record of llmss_vp_record_floats(ks) floats per row -- [max, sum-exp, count, 0, vals[ks],
- * idx[ks]] -- from its fp32 shard; gather the records with llmss_allgather_cols; step 2 on every rank: merge + draw
+ * step 1 on every rank: one record of llmss_vp_record_floats(ks) floats per row -- [max, sum-exp, count, sum-exp at the row's temperature,
+ * vals[ks], idx[ks]] -- from its fp32 shard; gather the records with llmss_allgather_cols; step 2 on every rank: merge + draw
  * (identical tokens everywhere, rng_state advanced).  Exact for 1 <= top_k <= ks; nranks * ks <= 1024. ---- */
 int llmss_vp_record_floats(int ks);
 int llmss_vp_summary(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, const int* greedy,
-                     const int* top_k, float* recs, int ks, llmss_stream_t stream);
+                     const int* top_k, const float* temperature, float* recs, int ks, llmss_stream_t stream);
+/* rows drawn from the whole distribution (top_k = 0, top_p = 1 -- what the reference's loop effectively samples, quirk Q1):
+ * after the record gather every rank runs llmss_vp_multinomial_pick (the rank whose CDF interval holds the draw names the
+ * token, all others answer -1; does not advance the RNG), `cand` ([B][4] int32) is gathered with llmss_allgather_cols,
+ * llmss_vp_merge_sample runs for all rows and llmss_vp_multinomial_merge overwrites the tokens of those rows. */
+int llmss_vp_multinomial_pick(const float* logits, int64_t ld, int B, int n_valid, int idx_offset, const float* recs_all,
+                              int nranks, int rank, int ks, const int* greedy, const float* temperature, const int* top_k,
+                              const float* top_p, const uint32_t* rng_state, int* cand, llmss_stream_t stream);
+int llmss_vp_multinomial_merge(const int* cand_all, int nranks, int B, int* out_tokens, long long* out_tokens64,
+                               llmss_stream_t stream);
 int llmss_vp_merge_sample(const float* recs_all, int nranks, int ks, int B, int vocab, const int* greedy,
                           const float* temperature, const int* top_k, const float* top_p, uint32_t* rng_state,
                           int* out_tokens, long long* out_tokens64, llmss_stream_t stream);

@@ -99,6 +99,7 @@ class ModelRunner:
         self.launches_per_graph: Dict[int, int] = {}   # own-kernel launches captured per decode graph
         self._all_greedy = True
         self._vp_sampling_ok = True
+        self._vp_plain_rows = False
         self._tuned_splits: Dict[int, int] = {}
         self.tuning_log: Dict[int, dict] = {}
         self.graph_pool = None
@@ -242,8 +243,10 @@ class ModelRunner:
         self.np_nblk[:] = 0
         self._all_greedy = all(s.params.is_greedy for s in seqs)
         # vocab-parallel sampling keeps 128 candidates per rank: exact for 1 <= top_k <= 128 (ops/cuda_impl.VP_KS)
+        plain = [(not s.params.is_greedy) and s.params.top_k <= 0 and s.params.top_p >= 1.0 for s in seqs]
+        self._vp_plain_rows = any(plain)   # whole-distribution rows: owner pick + 16-byte gather on top of the records
         self._vp_sampling_ok = self.core.tp * 128 <= 1024 and all(
-            s.params.is_greedy or 1 <= s.params.top_k <= 128 for s in seqs)
+            s.params.is_greedy or 1 <= s.params.top_k <= 128 or p for s, p in zip(seqs, plain))
         for i, s in enumerate(seqs):
             s.slot = i
             self.h_samp_i[i] = int(s.params.is_greedy)
@@ -288,14 +291,17 @@ class ModelRunner:
 
     def _vp_greedy(self) -> int:
         """Vocab-parallel token choice (no [B, V] logits all-gather) at TP > 1 on CUDA: 1 = every bound request is
-        greedy (16-byte argmax candidates), 2 = mixed greedy / top-k sampling (1 KiB candidate records), 0 = a
-        request needs the whole distribution (top_k = 0 or > 128) or the path is switched off (LLMSS_VP_GREEDY=0)."""
+        greedy (16-byte argmax candidates), 2 = mixed greedy / top-k sampling (1 KiB candidate records), 3 = as 2 plus rows
+        drawn from the whole distribution (top_k = 0, top_p = 1), 0 = a request is outside those (top_k > 128, or top_k = 0
+        with top_p < 1) or the path is switched off (LLMSS_VP_GREEDY=0)."""
         c = self.core.comm
         if not (self.cuda and not c.single and c.symm is not None and os.environ.get("LLMSS_VP_GREEDY", "1") == "1"):
             return 0
         if self._all_greedy:
             return 1
-        return 2 if self._vp_sampling_ok else 0
+        if not self._vp_sampling_ok:
+            return 0
+        return 3 if self._vp_plain_rows else 2
 
     def _decode_body(self, Bp: int, splits: int, vp_greedy: int = 0):
         tok, pos, slot, slen, bt = self._dev_views(Bp)
@@ -314,7 +320,7 @@ class ModelRunner:
             else:
                 cu.sample_vocab_parallel(local, self.core.comm.symm, self.spec.vocab, self.d_samp_i[:Bp],
                                          self.d_samp_f[:Bp], self.d_samp_i[MB:MB + Bp], self.d_samp_f[MB:MB + Bp],
-                                         self.d_rng[:Bp], out=tok)
+                                         self.d_rng[:Bp], out=tok, whole_distribution_rows=(vp_greedy == 3))
             return
         logits = self.core.forward(batch, self.kv, last_only=False)  # every row is a last token
         ops.sample(logits, self.d_samp_i[:Bp], self.d_samp_f[:Bp], self.d_samp_i[MB:MB + Bp],

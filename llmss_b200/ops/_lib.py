@@ -61,7 +61,11 @@ _SIGS = {
     "llmss_argmax_local": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
     "llmss_argmax_merge": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "llmss_vp_record_floats": (c_int, [c_int]),
-    "llmss_vp_summary": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "llmss_vp_summary": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                 c_void_p]),
+    "llmss_vp_multinomial_pick": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p,
+                                          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "llmss_vp_multinomial_merge": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "llmss_vp_merge_sample": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                       c_void_p, c_void_p, c_void_p, c_void_p]),
     "llmss_allgather_cols": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),

@@ -298,14 +298,14 @@ def greedy_vocab_parallel(local_logits, symm, vocab: int, out=None):
 VP_KS = 128  # candidates a rank contributes per row: exact for 1 <= top_k <= 128 (8 ranks x 128 = the merge's 1024 slots)
 
 
-def vp_summary(local_logits, n_valid: int, idx_offset: int, greedy, top_k, ks: int = VP_KS):
+def vp_summary(local_logits, n_valid: int, idx_offset: int, greedy, top_k, ks: int = VP_KS, temperature=None):
     """Per-row record of this rank's shard: [max, sum-exp, count, 0, vals[ks], idx[ks]] (fp32 / int32 bits)."""
     lib = _lib.load()
     B = local_logits.shape[0]
     assert local_logits.dtype == torch.float32 and local_logits.stride(1) == 1
     rec = torch.empty(B, 4 + 2 * ks, dtype=torch.float32, device=local_logits.device)
     _lib.check(lib.llmss_vp_summary(_ptr(local_logits), local_logits.stride(0), B, n_valid, idx_offset, _ptr(greedy),
-                                    _ptr(top_k), _ptr(rec), ks, _stream()), "llmss_vp_summary")
+                                    _ptr(top_k), _ptr(temperature), _ptr(rec), ks, _stream()), "llmss_vp_summary")
     _count()
     return rec
 
@@ -327,12 +327,47 @@ def vp_merge_sample(recs_all, nranks: int, vocab: int, greedy, temperature, top_
     return out
 
 
-def sample_vocab_parallel(local_logits, symm, vocab: int, greedy, temperature, top_k, top_p, rng_state, out=None):
+def vp_multinomial_pick(local_logits, n_valid: int, idx_offset: int, recs_all, nranks: int, rank: int, greedy, temperature,
+                        top_k, top_p, rng_state, ks: int = VP_KS):
+    """Whole-distribution rows (top_k = 0, top_p = 1): the rank whose CDF interval holds the draw names the token; every
+    other rank (and every other kind of row) answers -1.  Returns [B, 4] int32 (16 bytes per row for the gather)."""
+    lib = _lib.load()
+    B = local_logits.shape[0]
+    cand = torch.empty(B, 4, dtype=torch.int32, device=local_logits.device)
+    _lib.check(lib.llmss_vp_multinomial_pick(_ptr(local_logits), local_logits.stride(0), B, n_valid, idx_offset, _ptr(recs_all),
+                                             nranks, rank, ks, _ptr(greedy), _ptr(temperature), _ptr(top_k), _ptr(top_p),
+                                             _ptr(rng_state), _ptr(cand), _stream()), "llmss_vp_multinomial_pick")
+    _count()
+    return cand
+
+
+def vp_multinomial_merge(cand_all, nranks: int, out):
+    lib = _lib.load()
+    o32 = _ptr(out) if out.dtype == torch.int32 else None
+    o64 = _ptr(out) if out.dtype == torch.int64 else None
+    _lib.check(lib.llmss_vp_multinomial_merge(_ptr(cand_all), nranks, out.shape[0], o32, o64, _stream()),
+               "llmss_vp_multinomial_merge")
+    _count()
+    return out
+
+
+def sample_vocab_parallel(local_logits, symm, vocab: int, greedy, temperature, top_k, top_p, rng_state, out=None,
+                          whole_distribution_rows: bool = False):
     """K11: top-k / top-p / temperature sampling over vocab-sharded logits [B, V/t] without gathering them
     (reference path: list all_gather of [B, S, V/t] at layers.py:131-135 + rank-0 warpers + broadcast,
-    generate.py:109-144).  Three launches: shard summary, 1 KiB-per-row record gather, identical merge + draw."""
+    generate.py:109-144).  Three launches: shard summary, 1 KiB-per-row record gather, identical merge + draw; batches
+    with whole-distribution rows (top_k = 0, top_p = 1) add the owner pick, a 16-byte-per-row gather and its merge."""
     B, Vb = local_logits.shape
     off = symm.rank * Vb
-    rec = vp_summary(local_logits, max(0, min(Vb, vocab - off)), off, greedy, top_k)
+    n_valid = max(0, min(Vb, vocab - off))
+    rec = vp_summary(local_logits, n_valid, off, greedy, top_k, temperature=temperature)
     allr = symm.all_gather_cols(rec)
-    return vp_merge_sample(allr, symm.nranks, vocab, greedy, temperature, top_k, top_p, rng_state, out)
+    cand_all = None
+    if whole_distribution_rows:
+        cand = vp_multinomial_pick(local_logits, n_valid, off, allr, symm.nranks, symm.rank, greedy, temperature, top_k, top_p,
+                                   rng_state)
+        cand_all = symm.all_gather_cols(cand)
+    out = vp_merge_sample(allr, symm.nranks, vocab, greedy, temperature, top_k, top_p, rng_state, out)
+    if cand_all is not None:
+        vp_multinomial_merge(cand_all, symm.nranks, out)
+    return out

@@ -36,6 +36,7 @@ PICK = [
     ("sample", r"::sample_kernel"),
     ("vp_summary", r"::vp_summary_kernel"),
     ("vp_merge_sample", r"::vp_merge_sample_kernel"),
+    ("vp_multinomial_pick", r"::vp_multinomial_pick_kernel"),
     ("argmax_local", r"::argmax_local_kernel"),
     ("allreduce_oneshot_bf16", r"allreduce_oneshot_kernel<__nv_bfloat16>"),
     ("allreduce_twoshot_lamport_bf16", r"allreduce_twoshot_lam_kernel<__nv_bfloat16>"),

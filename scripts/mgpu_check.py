@@ -293,8 +293,10 @@ def main():
         if rank == 0:
             write_random_checkpoint(path, preset, dtype=torch.float32, device="cpu", std=0.05)
         dist.barrier()
-        for sampling in (False, True):
+        for sampling in (False, True, "plain"):
             sp = SamplingParams(max_new_tokens=n_new, is_greedy=not sampling, top_k=20, top_p=0.9, temperature=0.8, seed=5)
+            if sampling == "plain":   # whole-distribution rows: owner pick + 16-byte gather (vocab-parallel mode 3)
+                sp = SamplingParams(max_new_tokens=n_new, is_greedy=False, top_k=0, top_p=1.0, temperature=0.9, seed=5)
             tp = Engine.from_pretrained(path, dtype=torch.bfloat16, device=dev, process_group=pg, max_batch=4, max_seq_len=192)
             got = tp.generate(prompts[:2], sp)
             tp.core.sp_prefill = True  # long prompts: exercise the sequence-parallel prefill dataflow end to end
@@ -309,6 +311,10 @@ def main():
             if any(o != all_out[0] for o in all_out):
                 ok = False
                 log(f"FAIL {preset} sampling={sampling}: ranks disagree on the generated tokens")
+            want_mode = {False: 1, True: 2, "plain": 3}[sampling]
+            if not any(k[1] == want_mode for k in tp.runner.graphs):
+                ok = False
+                log(f"FAIL {preset} sampling={sampling}: vocab-parallel mode {want_mode} was not the one captured: {list(tp.runner.graphs)}")
             if sampling:
                 continue   # sampled tokens are compared across ranks only (vocab-parallel sampler, same RNG stream)
             single = Engine.from_pretrained(path, dtype=torch.bfloat16, device=dev, process_group=FakeGroup(0, 1),

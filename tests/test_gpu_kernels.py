@@ -354,6 +354,9 @@ def test_vocab_parallel_sampling_kernels(t):
     temp = torch.tensor([1.0, 0.7, 0.5, 1.0] * (B // 4), device="cuda")
     top_k = torch.tensor([50, 5, 128, 1, 64, 20] * (B // 6), dtype=torch.int32, device="cuda")
     top_p = torch.tensor([0.95, 0.5, 1.0, 0.9] * (B // 4), device="cuda")
+    plain_rows = [1, 8, 13, 22]            # drawn from the whole distribution: top_k = 0, top_p = 1
+    for r_ in plain_rows:
+        top_k[r_], top_p[r_], greedy[r_] = 0, 1.0, 0
     shards = [full[:, r * Vb:(r + 1) * Vb].contiguous() for r in range(t)]
     cpu = lambda x: x.cpu()  # noqa: E731
     for step in range(4):
@@ -361,15 +364,27 @@ def test_vocab_parallel_sampling_kernels(t):
         want, lo, hi = _oracle_choices(
             lambda r, sh: R.sample_vocab_parallel([cpu(x) for x in shards], cpu(greedy), cpu(temp), cpu(top_k), cpu(top_p),
                                                   cpu(r), V, k_summary=cu.VP_KS, u_shift=sh), rng)
-        recs = [cu.vp_summary(shards[r], max(0, min(Vb, V - r * Vb)), r * Vb, greedy, top_k) for r in range(t)]
-        got = cu.vp_merge_sample(torch.cat(recs, dim=1).contiguous(), t, V, greedy, temp, top_k, top_p, rng)
+        nv = [max(0, min(Vb, V - r * Vb)) for r in range(t)]
+        recs = [cu.vp_summary(shards[r], nv[r], r * Vb, greedy, top_k, temperature=temp) for r in range(t)]
+        allr = torch.cat(recs, dim=1).contiguous()
+        cands = [cu.vp_multinomial_pick(shards[r], nv[r], r * Vb, allr, t, r, greedy, temp, top_k, top_p, rng) for r in range(t)]
+        got = cu.vp_merge_sample(allr, t, V, greedy, temp, top_k, top_p, rng)
+        cu.vp_multinomial_merge(torch.cat(cands, dim=1).contiguous(), t, got)
         torch.cuda.synchronize()
         assert rng[:, 1].tolist() == [step + 1] * B
-        _check_tokens(got, want, lo, hi, f"t={t} step {step}")
+        call = torch.stack([c[:, 0] for c in cands], 1).cpu()      # exactly one rank names a token for a plain row
+        for b in range(B):
+            n_named = int((call[b] >= 0).sum())
+            assert n_named == (1 if b in plain_rows else 0), (b, call[b].tolist())
+        other = [b for b in range(B) if b not in plain_rows]
+        _check_tokens(got[other], want[other], lo[other], hi[other], f"t={t} step {step}")
+        g = got.long().cpu()                                       # index-order CDF: bracket instead of equality
+        for b in plain_rows:
+            assert min(lo[b], hi[b]) <= g[b] <= max(lo[b], hi[b]), (t, step, b, int(g[b]), int(lo[b]), int(hi[b]))
         assert int(got.max()) < V
         single = cu.sample(full[:, :V].contiguous(), greedy, temp, top_k, top_p,
                            torch.tensor([[900 + 13 * b, step] for b in range(B)], dtype=torch.int32, device="cuda"), vocab=V)
-        assert (single.long() == got.long()).float().mean().item() >= 0.9
+        assert (single.long()[other] == got.long()[other]).float().mean().item() >= 0.9
     assert got.tolist()[3] == 100
 
 

@@ -113,6 +113,15 @@ LLMSS_API int llmss_symm_create(int rank, int nranks, void* const* peer_bases, s
                                  SymmWs** out) {
   return llmss_symm_create2(rank, nranks, peer_bases, nullptr, buf_bytes, lam_bytes, out);
 }
+// Failure-detection self test: waits for a flag nobody will ever raise, so the device watchdog (SpinGuard,
+// common.cuh) must end the kernel with a trap after LLMSS_SPIN_TIMEOUT_NS instead of spinning for ever.  The CUDA
+// context is unusable afterwards: run it in a process of its own (tests/test_gpu_watchdog.py).
+__global__ void debug_wait_flag_kernel(const uint32_t* flag, uint32_t want) { wait_flag_ge(flag, want, 99); }
+LLMSS_API int llmss_debug_wait_flag(const uint32_t* flag, uint32_t want, cudaStream_t stream) {
+  debug_wait_flag_kernel<<<1, 1, 0, stream>>>(flag, want);
+  LLMSS_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
 LLMSS_API int llmss_symm_has_multicast(SymmWs* ws) { return (ws != nullptr && ws->mc_base != nullptr) ? 1 : 0; }
 LLMSS_API int llmss_symm_create2(int rank, int nranks, void* const* peer_bases, void* mc_base, size_t buf_bytes,
                                   size_t lam_bytes, SymmWs** out) {

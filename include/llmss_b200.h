@@ -71,6 +71,9 @@ int llmss_symm_init_region(void* ptr, size_t buf_bytes, size_t lam_bytes); /* ze
 int llmss_symm_create2(int rank, int nranks, void* const* peer_bases, void* mc_base, size_t buf_bytes, size_t lam_bytes,
                        llmss_symm_t** out);
 int llmss_symm_has_multicast(llmss_symm_t* ws);
+/* watchdog self test: waits on `flag` (a device uint32 nobody raises to `want`); the kernel traps after the 4 s spin
+ * limit and the context is lost -- call it from a throw-away process only */
+int llmss_debug_wait_flag(const uint32_t* flag, uint32_t want, llmss_stream_t stream);
 
 /* ---- K4 collectives over NVLink peer memory (N1/N2: layers.py:178,213; N3: layers.py:133) ---- */
 /* algo: 0 auto | 1 one-shot Lamport push | 2 two-shot with flags | 3 NVLS (stage locally, multimem.ld_reduce of the owned

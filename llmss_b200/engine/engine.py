@@ -113,6 +113,22 @@ class Engine:
     def has_work(self) -> bool:
         return bool(self.waiting or self.running)
 
+    def abort_all(self) -> List[int]:
+        """Drop every waiting and running request and give their KV blocks back (failure recovery / shutdown).
+        Returns the ids that were dropped; on a TP job every rank must call it at the same point."""
+        dropped = [s.seq_id for s in self.waiting] + [s.seq_id for s in self.running if not s.finished]
+        for s in self.running:
+            if not s.finished:
+                s.finished = True
+                self._finish(s)
+        self.waiting.clear()
+        self.running = []
+        self.runner.set_batch([])
+        self._dirty = True
+        for rid in dropped:
+            self.stats.pop(rid, None)
+        return dropped
+
     # ------------------------------------------------------------------ scheduling
     def _admit(self) -> List[SeqState]:
         admitted, budget = [], self.max_prefill_tokens

@@ -35,6 +35,7 @@ _SIGS = {
     "llmss_symm_init_region": (c_int, [c_void_p, c_size_t, c_size_t]),
     "llmss_symm_create2": (c_int, [c_int, c_int, C.POINTER(c_void_p), c_void_p, c_size_t, c_size_t, C.POINTER(c_void_p)]),
     "llmss_symm_has_multicast": (c_int, [c_void_p]),
+    "llmss_debug_wait_flag": (c_int, [c_void_p, C.c_uint32, c_void_p]),
     "llmss_vmm_caps": (c_int, [C.POINTER(c_int)]),
     "llmss_vmm_padded_size": (c_int, [c_size_t, c_int, c_int, C.POINTER(c_size_t)]),
     "llmss_vmm_alloc": (c_int, [c_size_t, C.POINTER(c_void_p)]),

@@ -145,6 +145,8 @@ class InProcBroker:
             self._s.strings[key] = self._b(value)
             if ex:
                 self._s.expiry[key] = time.monotonic() + ex
+            else:
+                self._s.expiry.pop(key, None)   # SET without EX clears an earlier time to live
         return True
 
     def get(self, key) -> Optional[str]:
@@ -245,6 +247,7 @@ class _Handler(socketserver.StreamRequestHandler):
         if cmd == "SET":
             with store.lock:
                 store.strings[s(a[0])] = a[1]
+                store.expiry.pop(s(a[0]), None)
                 for i in range(2, len(a) - 1):
                     if a[i].upper() == b"EX":
                         store.expiry[s(a[0])] = time.monotonic() + float(a[i + 1])

@@ -9,7 +9,10 @@ JSON bodies).  Differences, all deliberate (quirk Q14, SURVEY.md section 5.3/5.9
   * when idle, rank 0 blocks in BRPOP with a timeout and the other ranks block in the broadcast:
     nobody spins;
   * a malformed request produces an error response for that request only; the server lives on;
-  * responses go to the request's own reply list when it names one (`reply_to`), else to `squeue`.
+  * responses go to the request's own reply list when it names one (`reply_to`), else to `squeue`;
+  * rank 0 keeps a heartbeat in the broker; when the loop dies (device watchdog trap, NCCL error, engine bug) every
+    request in flight is answered with an error, the heartbeat turns to `failed` and the exception propagates so
+    the launcher takes the job down (serving/health.py).
 """
 from __future__ import annotations
 
@@ -22,6 +25,7 @@ import torch
 from ..engine.engine import Engine
 from ..utils.logging import logger
 from ..utils.metrics import METRICS
+from . import health
 from .broker import PRODUCER_QUEUE, SUBSCRIBER_QUEUE
 from .protocol import GenerateRequest, GenerateResponse
 
@@ -63,11 +67,41 @@ class ConsumerLoop:
         self.live: Dict[int, _Live] = {}
         self._next_rid = 0
         self.stop = False
+        self._last_beat = 0.0
+        self.reply_ttl_s = 600   # an answer nobody collects (client gave up) does not stay in the broker for ever
 
     # ------------------------------------------------------------------ rank 0: intake
     def _reply(self, req: GenerateRequest, resp: GenerateResponse):
         resp.request_id = req.request_id
         self.broker.lpush(req.reply_to or SUBSCRIBER_QUEUE, resp.to_json())
+        if req.reply_to and resp.done is not False:
+            self.broker.expire(req.reply_to, self.reply_ttl_s)
+
+    def _beat(self, force: bool = False):
+        now = time.monotonic()
+        if self.rank == 0 and (force or now - self._last_beat >= health.HEARTBEAT_PERIOD_S):
+            self._last_beat = now
+            health.beat(self.broker, "ok", tp=self.comm.size, step=self._step_idx, in_flight=len(self.live),
+                        waiting=len(self.engine.waiting))
+
+    def _fail_all(self, exc: BaseException):
+        """The loop is dying: answer what is in flight, mark the heartbeat, count it (rank 0; best effort)."""
+        METRICS.inc("engine_failures")
+        msg = f"{type(exc).__name__}: {exc}"[:500]
+        logger.error(f"serving loop failed on rank {self.rank}: {msg}")
+        if self.rank != 0:
+            return
+        for lv in list(self.live.values()):
+            try:
+                self._reply(lv.req, GenerateResponse(prompt=lv.req.prompt, continuation="", done=True,
+                                                     error=f"model server failed: {msg}"))
+            except Exception:  # noqa: BLE001 - the broker may be what failed
+                break
+        self.live.clear()
+        try:
+            health.beat(self.broker, "failed", ttl_s=health.FAILED_TTL_S, error=msg, step=self._step_idx)
+        except Exception:  # noqa: BLE001
+            pass
 
     def _pull(self, block: bool) -> List[tuple]:
         """[(request, token ids)], validated and tokenised (rank 0 only)."""
@@ -155,6 +189,7 @@ class ConsumerLoop:
         """One scheduling iteration; returns the number of tokens produced."""
         idle = not self.engine.has_work()
         self._step_idx += 1
+        self._beat()
         if idle or self._step_idx % self.poll_every == 0:   # same decision on every rank (replicated engine state)
             new = self._pull(block=idle) if self.rank == 0 else []
             for rid, ids, sp in self._share(new):
@@ -201,8 +236,18 @@ class ConsumerLoop:
     def run_forever(self):
         if self.rank == 0:
             logger.info(f"{type(self.engine.model).__name__} setup is done.")
-        while not self.stop:
-            self.step()
-        # drain what is in flight before leaving
-        while self.engine.has_work():
-            self.step()
+        try:
+            self._beat(force=True)
+            while not self.stop:
+                self.step()
+            # drain what is in flight before leaving
+            while self.engine.has_work():
+                self.step()
+        except BaseException as e:
+            self._fail_all(e)
+            raise
+        if self.rank == 0:
+            try:
+                health.clear(self.broker)
+            except Exception:  # noqa: BLE001 - the broker may already be gone at shutdown
+                pass

@@ -27,6 +27,7 @@ import grpc
 from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
 
 from ..utils.metrics import METRICS
+from . import health as _health
 from . import protocol
 from .broker import PRODUCER_QUEUE
 
@@ -80,8 +81,8 @@ def _to_pb(r: protocol.GenerateResponse):
 
 
 class LLMSSServicer:
-    def __init__(self, broker_factory: Callable[[], object], timeout_s: float = 600.0):
-        self.broker_factory, self.timeout_s = broker_factory, timeout_s
+    def __init__(self, broker_factory: Callable[[], object], timeout_s: float = 600.0, down_grace_s: float = 30.0):
+        self.broker_factory, self.timeout_s, self.down_grace_s = broker_factory, timeout_s, down_grace_s
 
     def _submit(self, pb, stream: bool, context):
         req = _to_internal(pb, stream)
@@ -98,7 +99,9 @@ class LLMSSServicer:
         METRICS.inc("grpc_requests_total")
         req, client = self._submit(pb, False, context)
         try:
-            got = client.brpop(req.reply_to, timeout=self.timeout_s)
+            got = _health.wait_reply(client, req.reply_to, self.timeout_s, down_grace_s=self.down_grace_s)
+        except _health.ConsumerDown as e:
+            context.abort(grpc.StatusCode.UNAVAILABLE, str(e))
         finally:
             getattr(client, "close", lambda: None)()
         if got is None:
@@ -113,7 +116,10 @@ class LLMSSServicer:
         req, client = self._submit(pb, True, context)
         try:
             while True:
-                got = client.brpop(req.reply_to, timeout=self.timeout_s)
+                try:
+                    got = _health.wait_reply(client, req.reply_to, self.timeout_s, down_grace_s=self.down_grace_s)
+                except _health.ConsumerDown as e:
+                    context.abort(grpc.StatusCode.UNAVAILABLE, str(e))
                 if got is None:
                     context.abort(grpc.StatusCode.DEADLINE_EXCEEDED, "no response from the model server")
                 resp = protocol.GenerateResponse.from_json(got[1])
@@ -124,11 +130,7 @@ class LLMSSServicer:
             getattr(client, "close", lambda: None)()
 
     def Health(self, pb, context):
-        try:
-            ok = bool(self.broker_factory().ping())
-        except Exception:
-            ok = False
-        return HealthResponsePB(status="ok" if ok else "broker-unreachable")
+        return HealthResponsePB(status=_health.status(self.broker_factory)["status"])
 
 
 def add_servicer(server: grpc.Server, servicer: LLMSSServicer):
@@ -141,9 +143,10 @@ def add_servicer(server: grpc.Server, servicer: LLMSSServicer):
     server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler(SERVICE, handlers),))
 
 
-def serve(broker_factory, host: str = "127.0.0.1", port: int = 50051, max_workers: int = 32):
+def serve(broker_factory, host: str = "127.0.0.1", port: int = 50051, max_workers: int = 32, timeout_s: float = 600.0,
+          down_grace_s: float = 30.0):
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=max_workers))
-    add_servicer(server, LLMSSServicer(broker_factory))
+    add_servicer(server, LLMSSServicer(broker_factory, timeout_s, down_grace_s))
     bound = server.add_insecure_port(f"{host}:{port}")
     server.start()
     return server, bound

@@ -17,6 +17,7 @@ from fastapi.responses import PlainTextResponse, StreamingResponse
 from pydantic import BaseModel
 
 from ..utils.metrics import METRICS
+from . import health as _health
 from .broker import PRODUCER_QUEUE
 from .protocol import GenerateRequest, GenerateResponse
 
@@ -36,7 +37,7 @@ class Response(BaseModel):
     continuation: str
 
 
-def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0) -> FastAPI:
+def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0, down_grace_s: float = 30.0) -> FastAPI:
     """`broker_factory()` returns a client with lpush/brpop (one per worker thread)."""
     app = FastAPI(title="llmss_b200 producer")
 
@@ -45,7 +46,7 @@ def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0) -
         try:
             req.with_routing()
             client.lpush(PRODUCER_QUEUE, req.to_json())
-            got = client.brpop(req.reply_to, timeout=timeout_s)
+            got = _health.wait_reply(client, req.reply_to, timeout_s, down_grace_s=down_grace_s)
             if got is None:
                 raise TimeoutError("no response from the model server")
             return GenerateResponse.from_json(got[1])
@@ -66,6 +67,8 @@ def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0) -
             resp = await asyncio.get_running_loop().run_in_executor(None, _submit_and_wait, req)
         except TimeoutError as e:
             raise HTTPException(status_code=504, detail=str(e))
+        except _health.ConsumerDown as e:
+            raise HTTPException(status_code=503, detail=str(e))
         if resp.error:
             raise HTTPException(status_code=500, detail=resp.error)
         return Response(prompt=resp.prompt, continuation=resp.continuation)
@@ -80,7 +83,12 @@ def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0) -
         async def events():
             try:
                 while True:
-                    got = await loop.run_in_executor(None, lambda: client.brpop(req.reply_to, timeout=timeout_s))
+                    try:
+                        got = await loop.run_in_executor(
+                            None, lambda: _health.wait_reply(client, req.reply_to, timeout_s, down_grace_s=down_grace_s))
+                    except _health.ConsumerDown as e:
+                        yield f"event: error\ndata: {e}\n\n"
+                        return
                     if got is None:
                         yield "event: error\ndata: timeout\n\n"
                         return
@@ -96,11 +104,8 @@ def create_app(broker_factory: Callable[[], object], timeout_s: float = 600.0) -
 
     @app.get("/health")
     async def health():
-        try:
-            ok = bool(broker_factory().ping())
-        except Exception:
-            ok = False
-        return {"status": "ok" if ok else "broker-unreachable"}
+        # status: ok | consumer-down (no heartbeat) | consumer-failed | broker-unreachable; `consumer` is the heartbeat
+        return _health.status(broker_factory)
 
     @app.get("/metrics", response_class=PlainTextResponse)
     async def metrics():

@@ -150,3 +150,71 @@ def test_http_and_grpc_front_ends(engine):
         loop.stop = True
         t.join(timeout=10)
         srv.stop()
+
+
+def test_failure_detection_heartbeat_and_error_replies(engine):
+    """a dying serving loop answers what is in flight, marks its heartbeat `failed` and re-raises; the
+    front ends report the consumer's state and stop waiting for a consumer that is not there."""
+    from fastapi.testclient import TestClient
+
+    from llmss_b200.serving import health
+    from llmss_b200.serving.http import create_app
+
+    broker = InProcBroker()
+    factory = lambda: broker  # noqa: E731
+    app = TestClient(create_app(factory, timeout_s=20, down_grace_s=0.3))
+    assert health.status(factory)["status"] == "consumer-down"          # nobody has ever said hello
+    assert app.get("/health").json()["status"] == "consumer-down"
+    t0 = time.monotonic()
+    r = app.post("/generate", json={"prompt": "anyone?", "max_new_tokens": 3, "is_greedy": True})
+    assert r.status_code == 503 and "heartbeat" in r.json()["detail"] and time.monotonic() - t0 < 15
+    assert broker.rpop(PRODUCER_QUEUE) is not None                       # drop the unanswered request again
+
+    loop = ConsumerLoop(engine, ByteTokenizer(), broker, idle_block_s=0.02)
+    raised = []
+
+    def run():
+        try:
+            loop.run_forever()
+        except RuntimeError as e:
+            raised.append(e)
+
+    real_step, calls = engine.step, [0]
+
+    def dying_step():
+        calls[0] += 1
+        if calls[0] == 3:      # prefill and one decode step run, then the "device" fails
+            raise RuntimeError("CUDA error: unspecified launch failure (device watchdog: peer flag wait timed out)")
+        return real_step()
+
+    engine.step = dying_step
+    t = threading.Thread(target=run, daemon=True)
+    try:
+        t.start()
+        for _ in range(200):
+            if health.status(factory)["status"] == "ok":
+                break
+            time.sleep(0.01)
+        hb = health.status(factory)
+        assert hb["status"] == "ok" and hb["consumer"]["tp"] == 1 and hb["consumer"]["age_s"] < 5
+        reqs = [GenerateRequest(prompt=f"doomed {i}", max_new_tokens=30, is_greedy=True).with_routing() for i in range(3)]
+        for q in reqs:
+            broker.lpush(PRODUCER_QUEUE, q.to_json())
+        for q in reqs:
+            got = health.wait_reply(broker, q.reply_to, timeout_s=30, poll_s=0.05)
+            resp = GenerateResponse.from_json(got[1])
+            assert resp.request_id == q.request_id and resp.error and "device watchdog" in resp.error
+        t.join(timeout=10)
+        assert not t.is_alive() and raised and "watchdog" in str(raised[0])
+        st = health.status(factory)
+        assert st["status"] == "consumer-failed" and "watchdog" in st["consumer"]["error"]
+        # a request that arrives after the failure is refused at once instead of waiting out its timeout
+        t0 = time.monotonic()
+        r = app.post("/generate", json={"prompt": "too late", "max_new_tokens": 3, "is_greedy": True})
+        assert r.status_code == 503 and "model server failed" in r.json()["detail"] and time.monotonic() - t0 < 10
+    finally:
+        engine.step = real_step
+        loop.stop = True
+        dropped = engine.abort_all()          # leave the shared engine clean: blocks back, nothing bound
+        assert len(dropped) == 3 and not engine.has_work()
+        assert engine.runner._outstanding == 0

@@ -278,6 +278,11 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// execution-only rendezvous of the cluster (no memory ordering: no MEMBAR / cache invalidation in the SASS)
+__device__ __forceinline__ void cluster_sync_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+}
 __device__ __forceinline__ uint32_t mapa_shared(uint32_t local_smem_addr, uint32_t cta_rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(cta_rank));
@@ -667,18 +672,18 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
 // DSMEM loads of both items are in flight before the first is consumed -- the reduce is bound by the DSMEM round
 // trip, not by its bandwidth -- and the sum runs in CTA order (deterministic).
 __device__ __forceinline__ void dsmem_reduce_pair(uint32_t stage_u32, int S, int item0, int item1, bool two,
-                                                  float (&v0)[8], float (&v1)[8]) {
+                                                  float (&v0)[8], float (&v1)[8], int rank_stride = 1, int rank_base = 0) {
   const uint32_t off0 = (uint32_t)((((item0 / BM) * 2) * BM + item0 % BM) * 16);
   const uint32_t off1 = (uint32_t)((((item1 / BM) * 2) * BM + item1 % BM) * 16);
   float4 lo0[8], hi0[8], lo1[8], hi1[8];
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
     if (q < S) {
-      const uint32_t b0 = mapa_shared(stage_u32 + off0, (uint32_t)q);
+      const uint32_t b0 = mapa_shared(stage_u32 + off0, (uint32_t)(q * rank_stride + rank_base));
       lo0[q] = ld_dsmem_f4(b0);
       hi0[q] = ld_dsmem_f4(b0 + BM * 16);
       if (two) {
-        const uint32_t b1 = mapa_shared(stage_u32 + off1, (uint32_t)q);
+        const uint32_t b1 = mapa_shared(stage_u32 + off1, (uint32_t)(q * rank_stride + rank_base));
         lo1[q] = ld_dsmem_f4(b1);
         hi1[q] = ld_dsmem_f4(b1 + BM * 16);
       }
@@ -1089,6 +1094,275 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   if (threadIdx.x == 0) LLMSS_STAMP(7);
 }
 
+// ======================================================================================
+// CTA-pair kernel (tcgen05 cta_group::2) for token dimensions above 128.
+//
+// With 128-feature tiles every CTA re-reads the whole 256-token activation tile per k-block: 32 KB of activations from
+// L2 for 16 KB of weights, and from M = 256 upwards the L2 -> SM traffic and the bytes a 4-stage ring can keep in
+// flight (not HBM, not the tensor pipe) bound the GEMM.  Here two CTAs on the two SMs of a TPC share one
+// 256 x 256 x 16 MMA: each CTA loads its own 128 weight rows and HALF of the token rows (both at the same shared-memory
+// offsets), the even CTA issues `tcgen05.mma.cta_group::2`, the tensor cores of both SMs read both halves of the
+// activation tile, and each CTA's tensor memory receives the accumulator of its own 128 features.  Activation traffic per
+// weight byte halves and the ring holds 6 stages instead of 4 (measured: 313 ns per k-block of 256 x 256 x 64, against
+// ~410 ns for two single-CTA tiles at M = 8192).
+//
+// Two schedules, chosen on the host:
+//  * persistent (clusters of 2, S = 1): every pair walks tiles p, p + P, p + 2P, ... with TWO accumulators of 256 columns
+//    in each CTA's tensor memory, so the epilogue of one tile (straight out of tensor memory: bias / activation / gating
+//    / residual / store) runs under the main loop of the next;
+//  * split-K (clusters of 2 x S, one tile per cluster, few-tile shapes): pair p = rank / 2 streams the p-th share of K,
+//    parity h = rank % 2 selects the feature half; the S partial tiles of one parity are reduced out of the peers' shared
+//    memory like in the cluster kernel above (pull mode, CTA order, deterministic), each CTA finishing 1/S of its tile.
+//
+// Protocol: every CTA's TMA warp fills its own ring and arms its own `full` barrier.  The odd CTA's warp 1 forwards
+// each `full` completion to the even CTA's `peer_full` barrier (remote mbarrier arrive); the even CTA's warp 1 waits
+// for both before it issues, and frees the stage in BOTH CTAs with one multicast commit.  Accumulator hand-over: one
+// multicast commit raises `tfull` in both CTAs; the epilogue warps of both CTAs arrive on the EVEN CTA's `tempty`
+// (8 arrivals: 4 local, 4 remote) when they have drained a buffer.  All loads are plain per-CTA TMA loads of this
+// GPU's own operands.
+// ======================================================================================
+struct PCfg2 {
+  static constexpr int BN = 256;                 // token columns of the pair's accumulator
+  static constexpr int XH = BN / 2;              // token rows each CTA loads
+  static constexpr int W_BYTES = BM * BK * 2;
+  static constexpr int X_BYTES = XH * BK * 2;
+  static constexpr int STAGE_BYTES = W_BYTES + X_BYTES;
+  static constexpr int STAGES = 6;               // 192 KB ring; the parked fp32 tile of the split-K schedule (128 KB) reuses it
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                 const __grid_constant__ GemmArgs a) {
+  using C = PCfg2;
+  constexpr int BN = C::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* full_bar = bars;                       // own ring stage landed (TMA transaction bytes)
+  uint64_t* empty_bar = bars + C::STAGES;          // stage consumed (multicast commit of the even CTA)
+  uint64_t* peer_full_bar = bars + 2 * C::STAGES;  // even CTA only: the odd CTA's stage landed
+  uint64_t* tfull_bar = bars + 3 * C::STAGES;      // [2] accumulator complete (multicast commit)
+  uint64_t* tempty_bar = tfull_bar + 2;            // [2] even CTA only: accumulator drained by both CTAs' epilogues
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int CS = (int)cluster_nctarank(), r = (int)cluster_ctarank();
+  const int S = CS >> 1, p = r >> 1, h = r & 1;
+  const int pair_tiles_n = (a.tiles_n + 1) >> 1;
+  const int n_tiles = pair_tiles_n * a.tiles_m;
+  const int n_clusters = (int)gridDim.x / CS, cluster_id = (int)blockIdx.x / CS;   // S > 1: n_clusters == n_tiles
+  const int kb0 = (int)(((int64_t)p * a.kb_total) / S), kb1 = (int)(((int64_t)(p + 1) * a.kb_total) / S);
+  constexpr int NG = BN / 8;
+  constexpr int TCOLS = 2 * BN;
+  // bring-up / profiling switch (LLMSS_GEMM_PAIR_DEBUG; results are WRONG unless 0): 2 = no MMAs (load pipeline
+  // alone), 3 = no loads (MMA issue rate alone)
+  const int dbg_mode = a.tm_rot;
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) LLMSS_STAMP(0);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_x);
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&peer_full_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 8);   // one arrive per epilogue warp of either CTA
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {   // warp 1 of BOTH CTAs: the pair allocates together and gets the same columns
+    tmem_alloc_pair(tmem_slot, TCOLS);
+    tmem_relinquish_pair();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  cluster_sync_relaxed();  // barriers (fence.mbarrier_init above) and tensor memory of both CTAs exist before anything arrives remotely
+  const uint32_t tmem_base = *tmem_slot;
+  float4* staging = reinterpret_cast<float4*>(smem);  // split-K: [NG*2][128] float4, reuses the drained TMA ring
+  pdl_wait();
+  if (threadIdx.x == 0) LLMSS_STAMP(1);
+
+  if (warp == 0) {
+    const uint64_t pol_w = l2_policy_evict_first();
+    const uint64_t pol_x = l2_policy_evict_last();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = cluster_id; tile < n_tiles && dbg_mode != 3; tile += n_clusters) {
+      // token tile fastest: the pairs running at the same time share ONE weight tile (streamed from HBM once, L2 hits
+      // for the others) and sweep the activation, which stays L2-resident across the weight tiles
+      const int tn = (tile / a.tiles_m) * 2 + h;        // this CTA's 128-feature tile (may lie past N: zero-filled, unstored)
+      const int xrow = (tile % a.tiles_m) * BN + (h ^ (a.aligned & 1)) * C::XH;   // a.aligned: bring-up switch for the half order
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1, 60);
+        uint8_t* sw = smem + stage * C::STAGE_BYTES;
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * BK, tn * BM, pol_w);
+          tma_load_2d(sw + C::W_BYTES, &tmap_x, &full_bar[stage], kb * BK, xrow, pol_x);
+        }
+        __syncwarp();
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1 && h == 0) {
+    // ---- issuer (even CTA): one MMA of 256 features x 256 tokens x 16 per instruction, over both CTAs' stages
+    const uint32_t idesc = umma_idesc_f16(a.dtype == LLMSS_BF16 ? 1 : 0, 2 * BM, BN);
+    const uint32_t smem_base = smem_u32(smem);
+    const uint16_t pair_mask = (uint16_t)(3u << (r & ~1));
+    int stage = 0, as = 0;
+    uint32_t phase = 0, aphase = 0;
+    for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+      mbar_wait(&tempty_bar[as], aphase ^ 1, 65);   // both CTAs' epilogues have drained this accumulator
+      tcgen05_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (dbg_mode != 3) {
+          mbar_wait(&full_bar[stage], phase, 61);
+          mbar_wait(&peer_full_bar[stage], phase, 62);
+        }
+        if (lane == 0 && a.dbg != nullptr && a.dbg[(size_t)blockIdx.x * 8 + 3] == 0) LLMSS_STAMP(3);
+        tcgen05_fence_after();
+        const uint32_t sw = smem_base + stage * C::STAGE_BYTES;
+        const uint32_t sx = sw + C::W_BYTES;
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            if (dbg_mode != 2)
+              umma_f16_ss_pair(d_tmem, umma_desc_k_sw128(sw + k * 32), umma_desc_k_sw128(sx + k * 32), idesc,
+                               (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit_pair(&empty_bar[stage], pair_mask);   // frees this stage in both CTAs
+        }
+        __syncwarp();
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (elect_one()) umma_commit_pair(&tfull_bar[as], pair_mask);
+      __syncwarp();
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (lane == 0) LLMSS_STAMP(4);
+  } else if (warp == 1) {
+    // ---- forwarder (odd CTA): tell the issuer that this CTA's half of the stage has landed
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t leader = (uint32_t)(r & ~1);
+    for (int tile = cluster_id; tile < n_tiles && dbg_mode != 3; tile += n_clusters) {
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase, 63);
+        if (elect_one()) mbar_arrive_remote(mapa_shared(smem_u32(&peer_full_bar[stage]), leader));
+        __syncwarp();
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int f = quarter * 32 + lane;
+    const T* bias = reinterpret_cast<const T*>(a.bias);
+    int as = 0;
+    uint32_t aphase = 0;
+    const uint32_t tempty_leader = mapa_shared(smem_u32(&tempty_bar[0]), (uint32_t)(r & ~1));
+    for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+      const int tn = (tile / a.tiles_m) * 2 + h, tm = tile % a.tiles_m;
+      const int n = tn * BM + f, m0 = tm * BN;
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN);
+      mbar_wait(&tfull_bar[as], aphase, 64);  // all MMAs of the tile retired => its stages of BOTH CTAs have been consumed
+      tcgen05_fence_after();
+      if (threadIdx.x == 64) LLMSS_STAMP(5);
+      if (S == 1) {
+        // ---- straight out of tensor memory, CH groups of 8 token columns at a time (residuals fetched ahead)
+        constexpr int CH = 4;
+        const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+#pragma unroll 1
+        for (int cg0 = 0; cg0 < NG; cg0 += CH) {
+          float v[CH][8], rv[CH][8];
+#pragma unroll
+          for (int u = 0; u < CH; ++u) epilogue_load_res8<T>(a, rv[u], n, m0 + (cg0 + u) * 8, lane, a.M);
+          {
+            // one 32-column load and ONE wait per chunk: a tensor-memory round trip is ~0.3 us, and paying it per 8
+            // columns made the epilogue of a 128 x 256 tile 11 us (measured) instead of ~3
+            uint32_t q[32];
+            tmem_ld_32x32b_x32(t_addr + cg0 * 8, q);
+            tmem_ld_wait();
+#pragma unroll
+            for (int u = 0; u < CH; ++u)
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[u][j] = __uint_as_float(q[u * 8 + j]);
+          }
+          if (cg0 + CH >= NG) {   // accumulator fully read: hand the buffer back before the stores
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_remote(tempty_leader + (uint32_t)(as * 8));
+          }
+          store_chunk<T, CH>(a, v, rv, n, m0 + cg0 * 8, lane, bval, a.M);
+        }
+      } else {
+        // ---- split-K: park the partial accumulator in shared memory: [(cg*2 + half)][feature] float4, conflict-free
+#pragma unroll 1
+        for (int cg0 = 0; cg0 < NG; cg0 += 4) {
+          uint32_t q[32];
+          tmem_ld_32x32b_x32(t_addr + cg0 * 8, q);
+          tmem_ld_wait();
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            staging[((cg0 + (u >> 1)) * 2 + (u & 1)) * BM + f] = make_float4(
+                __uint_as_float(q[u * 4 + 0]), __uint_as_float(q[u * 4 + 1]), __uint_as_float(q[u * 4 + 2]), __uint_as_float(q[u * 4 + 3]));
+        }
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+  if (S > 1) {   // cluster-uniform: one tile per cluster, partials parked above
+    tcgen05_fence_before();
+    __syncwarp();
+    cluster_sync_all();  // every CTA's partial tile is parked and visible cluster-wide
+    if (threadIdx.x == 64) LLMSS_STAMP(2);
+    if (warp >= 2) {
+      const int tile = cluster_id;
+      const int tn = (tile / a.tiles_m) * 2 + h, tm = tile % a.tiles_m;
+      const int epi_tid = threadIdx.x - 64;
+      const int total_items = NG * BM;
+      const int per = ((total_items + S - 1) / S + 31) / 32 * 32;   // (column group, feature) items finished by each pair
+      const int my_items = max(0, min(per, total_items - p * per));
+      const T* bias = reinterpret_cast<const T*>(a.bias);
+      const uint32_t stage_u32 = smem_u32(staging);
+#pragma unroll 1
+      for (int it0 = epi_tid; it0 < my_items; it0 += 256) {
+        const bool two = it0 + 128 < my_items;
+        float vv[2][8];
+        dsmem_reduce_pair(stage_u32, S, p * per + it0, p * per + (two ? it0 + 128 : it0), two, vv[0], vv[1], 2, h);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (u == 1 && !two) break;
+          const int item = p * per + it0 + u * 128;
+          const int cg = item / BM, f = item % BM;
+          const int n = tn * BM + f;
+          float v[1][8], rv[1][8];
+          epilogue_load_res8<T>(a, rv[0], n, tm * BN + cg * 8, lane, a.M);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[0][j] = vv[u][j];
+          const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
+          store_chunk<T, 1>(a, v, rv, n, tm * BN + cg * 8, lane, bval, a.M);
+        }
+      }
+    }
+  }
+  if (threadIdx.x == 64) LLMSS_STAMP(6);
+  tcgen05_fence_before();
+  __syncwarp();
+  cluster_sync_relaxed();  // nobody may exit (or free tensor memory) while a peer still reads its shared memory / issues into it
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc_pair(tmem_base, TCOLS);
+  }
+  if (threadIdx.x == 0) LLMSS_STAMP(7);
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1216,6 +1490,59 @@ int launch_cluster(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs&
               : launch_cluster_ar<T, BN, false>(tw, tx, a, tiles, split, stream);
 }
 
+template <typename T>
+int launch_pair(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& a, int clusters, int split,
+                cudaStream_t stream) {
+  static PerDeviceSmem configured;
+  auto kern = gemm_pair_kernel<T>;
+  LLMSS_CHECK_CUDA(configured.ensure(kern, PCfg2::SMEM_BYTES));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(clusters * 2 * split);
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = PCfg2::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2 * split;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = llmss_pdl_enabled() ? 2 : 1;
+  LLMSS_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, a));
+  return 0;
+}
+
+// CTA-pair kernel: -1 = environment (LLMSS_GEMM_PAIR: off | auto (default) | 1 | 2 | 4), 0 = off, 1 / 2 / 4 = pairs per
+// cluster (1 = persistent, 2 / 4 = split-K depth), 8 = auto.  llmss_gemm_set_pair() overrides the environment (A/B measurements inside one process).
+int g_pair_mode = -1;
+int pair_mode() {
+  if (g_pair_mode >= 0) return g_pair_mode;
+  static int env_mode = -1;
+  if (env_mode < 0) {
+    const char* e = getenv("LLMSS_GEMM_PAIR");
+    env_mode = 8;  // default: automatic (pick_pair_split)
+    if (e != nullptr) env_mode = strcmp(e, "off") == 0 ? 0 : strcmp(e, "auto") == 0 ? 8 : atoi(e);
+    if (env_mode != 0 && env_mode != 1 && env_mode != 2 && env_mode != 4 && env_mode != 8) env_mode = 8;
+  }
+  return env_mode;
+}
+// Pairs per cluster for a plain GEMM with a 256-token tile, 0 = keep the single-CTA kernels.  Deepest split-K that
+// still fits the machine in one wave and leaves every pair at least two k-blocks.
+int pick_pair_split(int M, int N, int kb_total, int sms) {
+  const int mode = pair_mode();
+  if (mode == 0 || M <= 128) return 0;
+  const int pair_tiles = ((N + 2 * BM - 1) / (2 * BM)) * ((M + 255) / 256);
+  if (mode == 1 || mode == 2 || mode == 4) return mode <= kb_total ? mode : 1;
+  // automatic: persistent pairs from 40 pair tiles upwards (N >= 10240 at M <= 256, every prefill GEMM); with fewer
+  // tiles the machine is not filled without split-K, and the split-K schedule of this kernel (S = 2 / 4) loses to the
+  // single-CTA cluster kernel there (profiles/bench_gemm_pair.md)
+  (void)sms;
+  return pair_tiles >= 40 ? 1 : 0;
+}
+
 // Largest cluster size (2..8) for which all `tiles` clusters are co-resident (one wave) and every CTA still
 // streams >= 2 k-blocks; 0 = use the stream-K persistent kernel.  LLMSS_GEMM_MODE=streamk|cluster forces one.
 template <typename T, int BN>
@@ -1303,6 +1630,10 @@ int pick_bn(int M) {
 // Profiling aid: when non-null, every CTA of the following llmss_gemm launches writes 8 globaltimer
 // stamps (entry, prologue done, last TMA issued, first stage landed, last MMA issued, first
 // accumulator ready, epilogue done, exit) to buf[cta*8 .. cta*8+7].  buf must be zeroed by the caller.
+LLMSS_API int llmss_gemm_set_pair(int mode) {
+  g_pair_mode = mode;
+  return 0;
+}
 LLMSS_API int llmss_gemm_set_debug(unsigned long long* buf) {
   g_dbg = buf;
   return 0;
@@ -1454,6 +1785,41 @@ LLMSS_API int llmss_gemm_ex(const void* x, int64_t ldx, const void* w, int64_t l
     const size_t need = (size_t)p.tiles * BM * p.bn * 2;  // nranks sources x (tiles / nranks) owned tiles
     LLMSS_REQUIRE(need <= ws->lam_bytes, "gemm: fused reduce-scatter needs %zu bytes of Lamport buffer (have %zu)", need,
                   ws->lam_bytes);
+  }
+  if (collective == 0) {
+    // token tiles of 129..256 rows: two CTAs share one 256 x 256 MMA, each loading half of the activation tile
+    const int ps = pick_pair_split(M, N, p.kb_total, max_ctas > 0 ? max_ctas : num_sms());
+    if (ps > 0) {
+      CUtensorMap pw, px;
+      if (int e = make_tmap(&pw, w, dtype, N, K, ldw, BM)) return e;
+      if (int e = make_tmap(&px, x, dtype, M, K, ldx, PCfg2::XH)) return e;
+      GemmArgs a;
+      memset(&a, 0, sizeof(a));
+      a.M = M; a.N = N; a.K = K;
+      a.tiles_n = (N + BM - 1) / BM;
+      a.tiles_m = (M + PCfg2::BN - 1) / PCfg2::BN;
+      a.kb_total = p.kb_total;
+      a.dtype = dtype;
+      a.bias = bias; a.residual = residual; a.ldr = ldr;
+      a.out = out; a.ldo = ldo; a.out_f32 = out_f32;
+      a.act = act; a.act_start = act_start; a.gated = gated;
+      a.epi = gated ? EPI_GATED : (out_f32 ? EPI_F32 : (act != LLMSS_ACT_NONE ? EPI_ACT : EPI_PLAIN));
+      static const int flip = getenv("LLMSS_GEMM_PAIR_FLIP") ? atoi(getenv("LLMSS_GEMM_PAIR_FLIP")) : 0;
+      a.aligned = flip;
+      { const char* d = getenv("LLMSS_GEMM_PAIR_DEBUG"); a.tm_rot = d ? atoi(d) : 0; }
+      a.dbg = g_dbg;
+      const int pair_tiles = ((a.tiles_n + 1) / 2) * a.tiles_m;
+      // split-K: one tile per cluster; otherwise persistent pairs, as many as the machine holds (balanced over the tiles)
+      int clusters = pair_tiles;
+      if (ps == 1) {
+        int max_pairs = (max_ctas > 0 ? max_ctas : num_sms()) / 2;
+        if (max_pairs < 1) max_pairs = 1;
+        const int rounds = (pair_tiles + max_pairs - 1) / max_pairs;
+        clusters = (pair_tiles + rounds - 1) / rounds;
+      }
+      return dtype == LLMSS_F16 ? launch_pair<__half>(pw, px, a, clusters, ps, stream)
+                                : launch_pair<__nv_bfloat16>(pw, px, a, clusters, ps, stream);
+    }
   }
   CUtensorMap tw, tx;
   AgMaps ag_maps;  // all-gather mode only

@@ -94,6 +94,9 @@ typedef struct llmss_gemm_plan {
   int64_t sk_counters;
   int64_t ar_bytes;
 } llmss_gemm_plan;
+/* CTA-pair kernel (tcgen05 cta_group::2) for token tiles of 129..256 rows: -1 = environment (LLMSS_GEMM_PAIR =
+ * off | auto | 1 | 2 | 4), 0 = off, 1 / 2 / 4 = pairs per cluster (split-K depth), 8 = automatic */
+int llmss_gemm_set_pair(int mode);
 int llmss_gemm_set_debug(unsigned long long* per_cta_stamps); /* profiling aid: 8 globaltimer stamps per CTA */
 int llmss_gemm_plan_query(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, llmss_gemm_plan* p);
 int llmss_gemm_plan_query2(int M, int N, int K, int nranks, int elem_bytes, int max_ctas, int dtype, llmss_gemm_plan* p);

@@ -71,6 +71,7 @@ _SIGS = {
                                       c_void_p, c_void_p, c_void_p, c_void_p]),
     "llmss_allgather_cols": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "llmss_gemm_set_debug": (c_int, [c_void_p]),
+    "llmss_gemm_set_pair": (c_int, [c_int]),
     "llmss_gemm_plan_query": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, C.POINTER(GemmPlan)]),
     "llmss_gemm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
                            c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -100,6 +100,43 @@ def test_gemm_gated_and_f32_out_and_strided_input():
     _close(z, R.linear(x, w, out_dtype=torch.float32), 5e-3, 1e-2, "f32 out")
 
 
+@pytest.mark.parametrize("mode", [8, 1, 2, 4])
+def test_gemm_cta_pair_kernel(mode):
+    """tcgen05 cta_group::2 kernel (two CTAs share one 256 x 256 MMA): the automatic choice (persistent pairs from 40
+    pair tiles upwards) and the forced schedules (1 = persistent, 2 / 4 = split-K over 2 / 4 pairs per cluster), every
+    epilogue flavour, ragged rows / odd feature-tile counts / K tails, against the fp32 oracle and the single-CTA kernels."""
+    from llmss_b200.ops import _lib
+
+    cu = _cu()
+    lib = _lib.load()
+    cases = [(256, 12288, 512, torch.bfloat16), (700, 10240 + 128, 320, torch.bfloat16), (129, 10496, 1088, torch.float16)]
+    if mode != 8:
+        cases += [(256, 512, 512, torch.bfloat16), (200, 4224, 4160, torch.bfloat16)]
+    try:
+        for M, N, K, dt in cases:
+            torch.manual_seed(M + N + K + mode)
+            x = torch.randn(M, K, device="cuda", dtype=dt)
+            w = torch.randn(N, K, device="cuda", dtype=dt) / math.sqrt(K)
+            b = torch.randn(N, device="cuda", dtype=dt)
+            res = torch.randn(M, N, device="cuda", dtype=dt)
+            flavours = [dict(), dict(bias=b, act=R.ACT_GELU_TANH, act_start=(N // 256) * 128), dict(bias=b, residual=res),
+                        dict(act=R.ACT_SILU, gated=True), dict(out_dtype=torch.float32)]
+            for kw in flavours:
+                lib.llmss_gemm_set_pair(mode)
+                y = cu.linear(x, w, **kw)
+                y_again = cu.linear(x, w, **kw)
+                lib.llmss_gemm_set_pair(0)
+                y_single = cu.linear(x, w, **kw)
+                torch.cuda.synchronize()
+                ref = R.linear(x, w, **{**kw, "out_dtype": torch.float32})
+                tag = f"pair mode {mode} {M}x{N}x{K} {sorted(kw)}"
+                _close(y, ref, 4e-2 if dt == torch.bfloat16 else 8e-3, 2e-2, tag)
+                assert torch.equal(y, y_again), tag + ": not repeatable"
+                assert (y.float() - y_single.float()).abs().max().item() <= 0.05 * max(1.0, ref.abs().max().item()), tag
+    finally:
+        lib.llmss_gemm_set_pair(-1)
+
+
 # ------------------------------------------------------------------ norm
 @pytest.mark.parametrize("dtype", DT)
 @pytest.mark.parametrize("kind", [R.NORM_LAYER, R.NORM_RMS])

@@ -24,6 +24,7 @@ PICK = [
     ("gemm_swapab_bf16_bn256", r"gemm_swapab_kernel<__nv_bfloat16, 256, false>"),
     ("gemm_cluster_bf16_bn64", r"gemm_cluster_kernel<__nv_bfloat16, 64, false>"),
     ("gemm_cluster_allreduce_bf16_bn64", r"gemm_cluster_kernel<__nv_bfloat16, 64, true>"),
+    ("gemm_pair_2cta_bf16", r"gemm_pair_kernel<__nv_bfloat16>"),
     ("attn_decode_tc_bf16_d256_r1", r"attn_decode_tc_kernel<__nv_bfloat16, 256, 1>"),
     ("attn_decode_tc_bf16_d128_r4", r"attn_decode_tc_kernel<__nv_bfloat16, 128, 4>"),
     ("attn_decode_cudacore_bf16_d256", r"attn_decode_kernel<__nv_bfloat16, 256, 1, 4>"),

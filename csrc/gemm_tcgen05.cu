@@ -1566,11 +1566,13 @@ int pick_pair_split(int M, int N, int kb_total, int sms) {
   if (mode == 0 || M <= 128) return 0;
   const int pair_tiles = ((N + 2 * BM - 1) / (2 * BM)) * ((M + 255) / 256);
   if (mode == 1 || mode == 2 || mode == 4) return mode <= kb_total ? mode : 1;
-  // automatic: persistent pairs from 40 pair tiles upwards (N >= 10240 at M <= 256, every prefill GEMM); with fewer
-  // tiles the machine is not filled without split-K, and the split-K schedule of this kernel (S = 2 / 4) loses to the
-  // single-CTA cluster kernel there (profiles/bench_gemm_pair.md)
-  (void)sms;
-  return pair_tiles >= 40 ? 1 : 0;
+  // automatic (profiles/bench_gemm_pair.md): persistent pairs from 38 pair tiles upwards (N >= 9728 at M <= 256, every
+  // prefill GEMM); 24..37 pair tiles: two pairs per cluster split K, which fills the machine (4 CTAs per tile) and beat
+  // both the persistent form and the single-CTA kernels on every measured shape; below that the single-CTA cluster
+  // kernel with its deeper split wins.
+  if (pair_tiles >= 38) return 1;
+  if (pair_tiles >= 24 && pair_tiles * 4 <= sms && kb_total >= 4) return 2;
+  return 0;
 }
 
 // Largest cluster size (2..8) for which all `tiles` clusters are co-resident (one wave) and every CTA still

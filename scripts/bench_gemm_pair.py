@@ -92,6 +92,8 @@ def bench(M, N, K, dtype=torch.bfloat16):
 
 if __name__ == "__main__":
     ok = True
+    if "--threshold" in sys.argv:
+        check = lambda *a, **k: True  # noqa: E731 - correctness of this build is covered by tests/test_gpu_kernels.py
     for split in (1, 2, 4):
         ok &= check(256, 512, 512, split)
     for flavour in ("bias_gelu_from", "gated", "residual", "f32"):
@@ -103,6 +105,12 @@ if __name__ == "__main__":
     if "--check-only" in sys.argv or not ok:
         sys.exit(0 if ok else 1)
     rows = []
+    if "--threshold" in sys.argv:   # where does the persistent pair schedule start to pay? (pair tiles: 16 .. 48)
+        for M, N, K in ((512, 2048, 4096), (256, 6144, 4096), (512, 3584, 4096), (256, 8192, 4096), (512, 4096, 4096),
+                        (256, 10240, 4096), (384, 5120, 5120), (768, 4096, 4096), (256, 8192, 8192), (512, 4096, 11008)):
+            rows.append(bench(M, N, K))
+        json.dump(rows, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1) if "--json" in sys.argv else None
+        sys.exit(0)
     for M in ((256,) if "--large" in sys.argv else (256, 192)):
         for N, K in (((12288, 4096), (28672, 4096)) if "--large" in sys.argv else
                      ((4096, 4096), (12288, 4096), (16384, 4096), (4096, 16384), (28672, 4096), (3584, 4096), (4096, 2560),

@@ -112,6 +112,8 @@ def test_gemm_cta_pair_kernel(mode):
     cases = [(256, 12288, 512, torch.bfloat16), (700, 10240 + 128, 320, torch.bfloat16), (129, 10496, 1088, torch.float16)]
     if mode != 8:
         cases += [(256, 512, 512, torch.bfloat16), (200, 4224, 4160, torch.bfloat16)]
+    else:
+        cases += [(256, 6144, 512, torch.bfloat16)]     # 24 pair tiles: the automatic choice splits K over two pairs
     try:
         for M, N, K, dt in cases:
             torch.manual_seed(M + N + K + mode)

@@ -288,6 +288,60 @@ __device__ __forceinline__ void store_chunk_plain_full(const GemmArgs& a, const 
   }
 }
 
+// The same for the activation and gated flavours (the whole warp's 32 features in range: the gated form shuffles).
+template <typename T, int CH, int EPI, int ACT>
+__device__ __forceinline__ void store_chunk_full_t(const GemmArgs& a, const float (&v)[CH][8], int n, int mb0, int lane, float bval) {
+  const bool has_res = a.residual != nullptr;
+  if constexpr (EPI == EPI_GATED) {
+    // rows of w interleave (gate, up): even lane holds gate_j, odd lane up_j of output feature n/2
+    T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb0 * a.ldo + (n >> 1);
+    const T* r = reinterpret_cast<const T*>(a.residual) + (int64_t)mb0 * a.ldr + (n >> 1);
+    const bool writer = (lane & 1) == 0;
+#pragma unroll
+    for (int u = 0; u < CH; ++u)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float y = v[u][j] + bval;
+        const float other = __shfl_xor_sync(0xffffffffu, y, 1);
+        if (writer) *o = from_f32<T>(act_t<ACT>(y, a.act) * other + (has_res ? to_f32(*r) : 0.f));
+        o += a.ldo;
+        r += a.ldr;
+      }
+  } else {
+    T* o = reinterpret_cast<T*>(a.out) + (int64_t)mb0 * a.ldo + n;
+    const T* r = reinterpret_cast<const T*>(a.residual) + (int64_t)mb0 * a.ldr + n;
+    const bool do_act = n >= a.act_start;
+#pragma unroll
+    for (int u = 0; u < CH; ++u)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x = v[u][j] + bval;
+        const float y = do_act ? act_t<ACT>(x, a.act) : x;
+        *o = from_f32<T>(y + (has_res ? to_f32(*r) : 0.f));
+        o += a.ldo;
+        r += a.ldr;
+      }
+  }
+}
+// Dispatch of the full-chunk stores; false = flavour without a fast form (fp32 output): use store_chunk.
+template <typename T, int CH>
+__device__ __forceinline__ bool store_chunk_full(const GemmArgs& a, const float (&v)[CH][8], int n, int mb0, int lane, float bval) {
+  if (a.epi == EPI_PLAIN) {
+    store_chunk_plain_full<T, CH>(a, v, n, mb0, bval);
+  } else if (a.epi == EPI_ACT) {
+    if (a.act == LLMSS_ACT_GELU_TANH) store_chunk_full_t<T, CH, EPI_ACT, LLMSS_ACT_GELU_TANH>(a, v, n, mb0, lane, bval);
+    else if (a.act == LLMSS_ACT_SILU) store_chunk_full_t<T, CH, EPI_ACT, LLMSS_ACT_SILU>(a, v, n, mb0, lane, bval);
+    else store_chunk_full_t<T, CH, EPI_ACT, ACT_RUNTIME>(a, v, n, mb0, lane, bval);
+  } else if (a.epi == EPI_GATED) {
+    if (a.act == LLMSS_ACT_SILU) store_chunk_full_t<T, CH, EPI_GATED, LLMSS_ACT_SILU>(a, v, n, mb0, lane, bval);
+    else if (a.act == LLMSS_ACT_GELU_TANH) store_chunk_full_t<T, CH, EPI_GATED, LLMSS_ACT_GELU_TANH>(a, v, n, mb0, lane, bval);
+    else store_chunk_full_t<T, CH, EPI_GATED, ACT_RUNTIME>(a, v, n, mb0, lane, bval);
+  } else {
+    return false;
+  }
+  return true;
+}
+
 // ---- thread-block-cluster helpers (split-K kernel) ----
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -1303,7 +1357,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         // ---- straight out of tensor memory, CH groups of 8 token columns at a time (residuals fetched ahead)
         constexpr int CH = 4;
         const float bval = (bias != nullptr && n < a.N) ? to_f32(bias[n]) : 0.f;
-        const bool plain_ok = a.epi == EPI_PLAIN && n < a.N;   // per lane; the row test below is per chunk
+        // fast stores need the warp's 32 features in range (warp-uniform: the gated flavour shuffles) and a flavour that
+        // has one; the row test below is per chunk
+        const bool plain_ok = a.epi != EPI_F32 && tn * BM + quarter * 32 + 32 <= a.N;
 #pragma unroll 1
         for (int cg0 = 0; cg0 < NG; cg0 += CH) {
           float v[CH][8], rv[CH][8];
@@ -1328,7 +1384,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             __syncwarp();
             if (lane == 0) mbar_arrive_remote(tempty_leader + (uint32_t)(as * 8));
           }
-          if (fast) store_chunk_plain_full<T, CH>(a, v, n, m0 + cg0 * 8, bval);
+          if (fast) store_chunk_full<T, CH>(a, v, n, m0 + cg0 * 8, lane, bval);
           else store_chunk<T, CH>(a, v, rv, n, m0 + cg0 * 8, lane, bval, a.M);
         }
       } else {

@@ -35,6 +35,8 @@ def get_args(argv=None):
     parser.add_argument("--use_cache", action="store_true")
     parser.add_argument("--dtype", type=str, default="float16", choices=["float16", "bfloat16", "float32"])
     parser.add_argument("--seed", type=int, default=0)
+    parser.add_argument("--sliding_window", action="store_true",
+                        help="keep generating past the model's context over the most recent tokens (rotary-position models)")
     return parser.parse_args(argv)
 
 
@@ -58,7 +60,7 @@ def main(argv=None):
 
     engine = Engine.from_pretrained(args.pretrained_model_path, dtype=getattr(torch, args.dtype), device=device,
                                     process_group=process_group, max_batch=max(1, len(args.prompts)),
-                                    eos_token_id=None)
+                                    eos_token_id=None, sliding_window=args.sliding_window)
     max_len = engine.runner.max_seq_len
 
     # rank 0 tokenises; ids are shared with one broadcast (reference N5, generate.py:73-85)

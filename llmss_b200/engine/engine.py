@@ -56,12 +56,13 @@ class Engine:
                  block_size: Optional[int] = None,
                  num_blocks: Optional[int] = None, use_cuda_graph: Optional[bool] = None,
                  max_prefill_tokens: int = 16384, eos_token_id: Optional[int] = None,
-                 prefill_chunk: Optional[int] = None):
+                 prefill_chunk: Optional[int] = None, sliding_window: bool = False):
         self.model = model
         self.core = model.core if hasattr(model, "core") else model
         self.comm = self.core.comm
         self.runner = ModelRunner(self.core, max_batch=max_batch, max_seq_len=max_seq_len, block_size=block_size,
-                                  num_blocks=num_blocks, use_cuda_graph=use_cuda_graph, prefill_chunk=prefill_chunk)
+                                  num_blocks=num_blocks, use_cuda_graph=use_cuda_graph, prefill_chunk=prefill_chunk,
+                                  sliding_window=sliding_window)
         self.max_batch = max_batch
         self.max_prefill_tokens = max_prefill_tokens
         self.eos_token_id = eos_token_id
@@ -156,7 +157,7 @@ class Engine:
     def _is_done(self, s: SeqState, tok: int) -> bool:
         return (len(s.output) >= s.params.max_new_tokens
                 or (s.eos is not None and tok == s.eos)
-                or len(s.prompt) + len(s.output) >= self.runner.max_seq_len)
+                or (not self.runner.sliding and len(s.prompt) + len(s.output) >= self.runner.max_seq_len))
 
     def _finish(self, s: SeqState):
         self.runner.deactivate(s)

@@ -60,7 +60,8 @@ def request_seed(params: "SamplingParams", seq_id: int) -> int:
 
 
 class SeqState:
-    __slots__ = ("seq_id", "prompt", "output", "blocks", "params", "length", "slot", "finished", "eos", "reserved")
+    __slots__ = ("seq_id", "prompt", "output", "blocks", "params", "length", "slot", "finished", "eos", "reserved",
+                 "dropped")
 
     def __init__(self, seq_id, prompt, params, eos=None):
         self.seq_id, self.prompt, self.params = seq_id, list(prompt), params
@@ -71,17 +72,25 @@ class SeqState:
         self.finished = False
         self.eos = eos
         self.reserved = 0        # cache blocks promised to this sequence at admission (worst case)
+        self.dropped = 0         # sliding window: tokens (whole blocks) already evicted from the front of the cache
 
 
 class ModelRunner:
     def __init__(self, core: DecoderLM, max_batch: int = 64, max_seq_len: Optional[int] = None,
                  block_size: Optional[int] = None, num_blocks: Optional[int] = None,
-                 use_cuda_graph: Optional[bool] = None, prefill_chunk: Optional[int] = None):
+                 use_cuda_graph: Optional[bool] = None, prefill_chunk: Optional[int] = None,
+                 sliding_window: bool = False):
         self.core, self.spec = core, core.spec
         self.device, self.dtype = core.device, core.dtype
         self.max_batch = max_batch
         self.prefill_chunk = prefill_chunk   # tokens per sequence and prefill round (None: whole prompts at once)
         self.max_seq_len = min(max_seq_len or self.spec.max_pos, self.spec.max_pos)
+        # Sliding window (the working form of what the reference attempts at generate.py:133-144, quirk Q7): a sequence
+        # that reaches max_seq_len keeps generating over its most recent tokens; the cache evicts whole blocks from the
+        # front (block table shifted left, block returned to the pool) and positions stay absolute, which rotary
+        # embeddings allow (keys keep the rotation of the position they were written at).  Families with a learned
+        # position table cannot index past it, so they keep stopping at max_seq_len.
+        self.sliding = bool(sliding_window) and not self.spec.learned_pos
         if block_size is None:
             # 64-token pages = one key tile of the tcgen05 decode-attention kernel (one TMA op per K / V
             # tile); the CPU oracle path and head sizes the kernel does not cover keep 16.
@@ -131,6 +140,7 @@ class ModelRunner:
         self.np_len = np.zeros(B, dtype=np.int64)       # tokens already in the cache, per row
         self.np_nblk = np.zeros(B, dtype=np.int64)      # blocks owned, per row
         self.np_active = np.zeros(B, dtype=bool)
+        self.np_drop = np.zeros(B, dtype=np.int64)      # sliding window: tokens evicted from the front, per row
         self.np_slot[:] = -1
         self.d_in.copy_(self.h_in)
         # sampler parameters (change only when the batch composition changes)
@@ -241,6 +251,7 @@ class ModelRunner:
         self.np_active[:] = False
         self.np_len[:] = 0
         self.np_nblk[:] = 0
+        self.np_drop[:] = 0
         self._all_greedy = all(s.params.is_greedy for s in seqs)
         # vocab-parallel sampling keeps 128 candidates per rank: exact for 1 <= top_k <= 128 (ops/cuda_impl.VP_KS)
         plain = [(not s.params.is_greedy) and s.params.top_k <= 0 and s.params.top_p >= 1.0 for s in seqs]
@@ -257,6 +268,7 @@ class ModelRunner:
             rng[i, 1] = len(s.output)
             self.np_active[i] = not s.finished
             self.np_len[i] = s.length
+            self.np_drop[i] = s.dropped
             self.np_nblk[i] = len(s.blocks)
             self.np_bt[i, :len(s.blocks)] = s.blocks
             if s.output:
@@ -275,19 +287,32 @@ class ModelRunner:
         """Vectorised (numpy on the pinned buffer) metadata for this step of the bound batch."""
         bs = self.block_size
         act = self.np_active
-        pos = self.np_len
+        pos = self.np_len                      # absolute position of the token fed this step (= tokens seen so far)
+        if self.sliding:
+            # window full: evict the oldest block of the row (block-granular, so slot offsets inside blocks stay put)
+            full = act & (pos - self.np_drop + 1 > self.max_seq_len)
+            for i in np.nonzero(full)[0]:
+                s = self.batch_seqs[i]
+                self.alloc.release([s.blocks.pop(0)])
+                s.dropped += bs
+                self.np_drop[i] += bs
+                n = len(s.blocks)
+                self.np_bt[i, :n] = s.blocks
+                self.np_bt[i, n:] = 0
+                self.np_nblk[i] = n
+        w = pos - self.np_drop                 # index inside the cached window
         # rows that step onto a new cache block get one (every block_size steps per sequence)
-        need = act & (pos // bs >= self.np_nblk)
+        need = act & (w // bs >= self.np_nblk)
         for i in np.nonzero(need)[0]:
             s = self.batch_seqs[i]
-            self._grow(s, int(pos[i]) + 1)
+            self._grow(s, int(w[i]) + 1)
             self.np_bt[i, :len(s.blocks)] = s.blocks
             self.np_nblk[i] = len(s.blocks)
         rows = np.arange(self.max_batch)
-        blk = self.np_bt[rows, np.minimum(pos // bs, self.max_blocks_per_seq - 1)]
+        blk = self.np_bt[rows, np.minimum(w // bs, self.max_blocks_per_seq - 1)]
         self.np_pos[:] = np.where(act, pos, 0)
-        self.np_slot[:] = np.where(act, blk * bs + pos % bs, -1)
-        self.np_slen[:] = np.where(act, pos + 1, 0)
+        self.np_slot[:] = np.where(act, blk * bs + w % bs, -1)
+        self.np_slen[:] = np.where(act, w + 1, 0)
 
     def _vp_greedy(self) -> int:
         """Vocab-parallel token choice (no [B, V] logits all-gather) at TP > 1 on CUDA: 1 = every bound request is

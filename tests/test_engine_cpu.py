@@ -127,3 +127,54 @@ def test_no_cache_mode_matches_cached_generation(tmp_path):
     sp = SamplingParams(max_new_tokens=6, top_k=20, top_p=0.9, temperature=0.8, seed=21)
     assert eng.generate_no_cache(prompts, sp) == eng.generate(prompts, sp)
     assert eng.runner.alloc.num_free == eng.runner.alloc.num_blocks - 1
+
+
+def test_sliding_window_matches_block_window_oracle(tmp_path):
+    """Past max_seq_len the engine keeps generating over its most recent tokens: whole cache blocks are evicted from
+    the front, positions stay absolute (reference quirk Q7, generate.py:133-144, done properly).  Oracle: HF GPT-J in
+    ONE pass over the whole token stream with a 4-D mask in which token q sees keys [window_start(q), q] -- exactly what
+    a cache that evicts blocks produces, including the hidden states of tokens computed before an eviction."""
+    import sys
+    from pathlib import Path
+
+    sys.path.insert(0, str(Path(__file__).parent))
+    from tiny import make_tiny
+    from transformers import AutoConfig, AutoModelForCausalLM
+
+    cfg, _ = make_tiny("gptj", tmp_path)
+    hc = AutoConfig.from_pretrained(str(tmp_path))
+    hc.n_positions = hc.max_position_embeddings = 512          # the oracle's rotary table must reach past the window
+    hf = AutoModelForCausalLM.from_pretrained(str(tmp_path), config=hc, torch_dtype=torch.float32, attn_implementation="eager").eval()
+    W, bs, n_new = 64, 16, 70
+    eng = Engine.from_pretrained(str(tmp_path), device="cpu", max_batch=2, max_seq_len=W, block_size=bs, sliding_window=True)
+    assert eng.runner.sliding
+    g = torch.Generator().manual_seed(1)
+    prompts = [torch.randint(1, cfg.vocab_size, (n,), generator=g).tolist() for n in (40, 9)]
+    outs = eng.generate(prompts, SamplingParams(max_new_tokens=n_new, is_greedy=True))
+    assert [len(o) for o in outs] == [n_new, n_new]                      # 110 and 79 tokens through a 64-token window
+    assert eng.runner.alloc.num_free == eng.runner.alloc.num_blocks - 1 and eng.runner._outstanding == 0
+    for p, o in zip(prompts, outs):
+        toks = p + o
+        T = len(toks) - 1
+        q = torch.arange(T)
+        start = torch.clamp(((q + 1 - W + bs - 1) // bs) * bs, min=0)    # first key still cached when token q was fed
+        start[: len(p)] = 0                                              # the prompt is prefilled under plain causal attention
+        k = torch.arange(T)
+        seen = (k[None, :] <= q[:, None]) & (k[None, :] >= start[:, None])
+        neg = torch.finfo(torch.float32).min
+        with torch.no_grad():
+            win = hf(input_ids=torch.tensor([toks[:-1]]), attention_mask=torch.zeros(T, T).masked_fill(~seen, neg)[None, None],
+                     position_ids=q[None]).logits[0]
+            full = hf(input_ids=torch.tensor([toks[:-1]]), position_ids=q[None]).logits[0]
+        rows = win[len(p) - 1:]
+        for i, t in enumerate(o):
+            gap = (rows[i].max() - rows[i][t]).item()
+            assert gap <= 1e-3 * max(1.0, rows[i].abs().max().item()), (len(p), i, t, int(rows[i].argmax()), gap)
+        assert (win[W + 1:] - full[W + 1:]).abs().max().item() > 1e-3      # the window is not a no-op
+    # without the switch a sequence stops at max_seq_len; learned-position families never slide
+    stop = Engine.from_pretrained(str(tmp_path), device="cpu", max_batch=2, max_seq_len=W, block_size=bs)
+    assert len(stop.generate([prompts[0]], SamplingParams(max_new_tokens=n_new, is_greedy=True))[0]) == W - len(prompts[0])
+    cfg2, _ = make_tiny("gpt2", tmp_path / "gpt2")
+    learned = Engine.from_pretrained(str(tmp_path / "gpt2"), device="cpu", max_batch=1, max_seq_len=32, block_size=bs, sliding_window=True)
+    assert not learned.runner.sliding
+    assert len(learned.generate([prompts[1]], SamplingParams(max_new_tokens=n_new, is_greedy=True))[0]) == 32 - len(prompts[1])

@@ -207,7 +207,9 @@ int llmss_vp_merge_sample(const float* recs_all, int nranks, int ks, int B, int 
                           int* out_tokens, long long* out_tokens64, llmss_stream_t stream);
 
 /* ---- K11 fused sampler (G15, G16, N6; generate.py:109-144) ----
- * rng_state: [B][2] = (request seed, tokens sampled so far); the draw depends on nothing else (not on the row). */
+ * rng_state: [B][2] = (request seed, tokens sampled so far); the draw depends on nothing else (not on the row).
+ * top_k = 0 with top_p < 1: the nucleus is searched among the 1024 most probable tokens (a wider nucleus is cut there);
+ * top_k = 0 with top_p = 1 samples the whole distribution. */
 int llmss_sample(const float* logits, int64_t ld, int B, int vocab, const int* greedy, const float* temperature,
                  const int* top_k, const float* top_p, uint32_t* rng_state, int* out_tokens,
                  long long* out_tokens64, llmss_stream_t stream);

@@ -141,3 +141,34 @@ def test_weight_files_local_and_missing(ckpt, tmp_path):
     empty.mkdir()
     with pytest.raises(FileNotFoundError):
         weight_files(str(empty))
+
+
+def test_fused_allreduce_mode_selection():
+    """Which exchange a row-parallel GEMM fuses into its epilogue (ops._fused_ar_mode): pure host logic, pinned here
+    with a stand-in for the GEMM planner.  Thresholds are the measured ones (profiles/bench_gemm_ar.md)."""
+    from types import SimpleNamespace
+
+    from llmss_b200 import ops
+
+    def plan_for(split, bn=64):
+        def gemm_plan(M, N, K, nranks):
+            tiles = -(-N // 128) * -(-M // bn)
+            return SimpleNamespace(split=split, tiles=tiles, bn=bn, ar_bytes=nranks * tiles * 128 * bn * 2)
+        return SimpleNamespace(gemm_plan=gemm_plan)
+
+    def symm(t, lam=64 << 20):
+        return SimpleNamespace(nranks=t, lam_bytes=lam)
+
+    cluster, streamk = plan_for(4), plan_for(0)
+    # stream-K shapes never fuse (measured slower fused than unfused)
+    assert ops._fused_ar_mode(streamk, symm(8), 64, 4096, 2560, 2) == 0
+    # TP=8, GPT-J out+down, M=64: 512 KB message -> two-shot Lamport exchange; M=16 (128 KB) -> one-shot push
+    assert ops._fused_ar_mode(cluster, symm(8), 64, 4096, 2560, 2) == 6
+    assert ops._fused_ar_mode(cluster, symm(8), 16, 4096, 2560, 2) == 5
+    # two ranks: the one-shot push up to 1 MB, two-shot from there
+    assert ops._fused_ar_mode(cluster, symm(2), 64, 4096, 10240, 2) == 5
+    assert ops._fused_ar_mode(cluster, symm(2), 128, 4096, 10240, 2) == 6
+    # a Lamport area too small for either form -> plain GEMM + standalone collective
+    assert ops._fused_ar_mode(cluster, symm(8, lam=1 << 20), 64, 4096, 2560, 2) == 0
+    # prefill-sized messages (above LLMSS_FUSED_TWOSHOT_MAX_BYTES) are left to the standalone all-reduce
+    assert ops._fused_ar_mode(plan_for(4, bn=256), symm(8), 8192, 4096, 2560, 2) == 0

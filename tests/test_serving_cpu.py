@@ -218,3 +218,28 @@ def test_failure_detection_heartbeat_and_error_replies(engine):
         dropped = engine.abort_all()          # leave the shared engine clean: blocks back, nothing bound
         assert len(dropped) == 3 and not engine.has_work()
         assert engine.runner._outstanding == 0
+
+
+def test_wait_reply_timeout_grace_and_late_answer():
+    """serving/health.wait_reply: plain timeout while the consumer is alive, ConsumerDown after the grace period without
+    a heartbeat, and an answer that was pushed just before the `failed` marker is still delivered."""
+    from llmss_b200.serving import health
+
+    broker = InProcBroker()
+    health.beat(broker, "ok", tp=1)
+    t0 = time.monotonic()
+    assert health.wait_reply(broker, "nobody", timeout_s=0.3, poll_s=0.05) is None          # alive, just slow
+    assert 0.25 <= time.monotonic() - t0 < 3
+    health.clear(broker)
+    with pytest.raises(health.ConsumerDown, match="no heartbeat"):
+        health.wait_reply(broker, "nobody", timeout_s=5, poll_s=0.05, down_grace_s=0.2)
+    broker.lpush("mine", "answer")
+    health.beat(broker, "failed", error="boom")
+    assert health.wait_reply(broker, "mine", timeout_s=5, poll_s=0.05) == ("mine", "answer")
+    with pytest.raises(health.ConsumerDown, match="boom"):
+        health.wait_reply(broker, "mine", timeout_s=5, poll_s=0.05)
+    # SET without EX clears an earlier time to live (Redis semantics)
+    broker.set("k", "v", ex=1)
+    broker.set("k", "w")
+    time.sleep(1.2)
+    assert broker.get("k") == "w"

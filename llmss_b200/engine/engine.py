@@ -56,13 +56,13 @@ class Engine:
                  block_size: Optional[int] = None,
                  num_blocks: Optional[int] = None, use_cuda_graph: Optional[bool] = None,
                  max_prefill_tokens: int = 16384, eos_token_id: Optional[int] = None,
-                 prefill_chunk: Optional[int] = None, sliding_window: bool = False):
+                 prefill_chunk: Optional[int] = None, sliding_window: bool = False, prefix_cache: bool = False):
         self.model = model
         self.core = model.core if hasattr(model, "core") else model
         self.comm = self.core.comm
         self.runner = ModelRunner(self.core, max_batch=max_batch, max_seq_len=max_seq_len, block_size=block_size,
                                   num_blocks=num_blocks, use_cuda_graph=use_cuda_graph, prefill_chunk=prefill_chunk,
-                                  sliding_window=sliding_window)
+                                  sliding_window=sliding_window, prefix_cache=prefix_cache)
         self.max_batch = max_batch
         self.max_prefill_tokens = max_prefill_tokens
         self.eos_token_id = eos_token_id

@@ -79,7 +79,7 @@ class ModelRunner:
     def __init__(self, core: DecoderLM, max_batch: int = 64, max_seq_len: Optional[int] = None,
                  block_size: Optional[int] = None, num_blocks: Optional[int] = None,
                  use_cuda_graph: Optional[bool] = None, prefill_chunk: Optional[int] = None,
-                 sliding_window: bool = False):
+                 sliding_window: bool = False, prefix_cache: bool = False):
         self.core, self.spec = core, core.spec
         self.device, self.dtype = core.device, core.dtype
         self.max_batch = max_batch
@@ -102,6 +102,16 @@ class ModelRunner:
         self.kv = KVCache(self.spec.n_layers, num_blocks, block_size, core.hkv, core.d, self.dtype, self.device)
         self.alloc = BlockAllocator(num_blocks)
         self._outstanding = 0   # blocks reserved at admission and not yet allocated
+        # Prefix cache: full prompt blocks stay registered after their sequence has gone; a later prompt that starts with
+        # the same tokens re-uses the blocks (reference-counted) and only computes what follows -- the queries then run
+        # over prior context, the paged mode of the prefill attention kernel.  The index is a trie over blocks:
+        # (parent node, the block's tokens) -> (node id, block); node ids are never re-used, so entries below an
+        # evicted block can no longer be reached.
+        self.prefix_enabled = bool(prefix_cache)
+        self._nodes: Dict[tuple, tuple] = {}
+        self._block_key: Dict[int, tuple] = {}
+        self._next_node = 1
+        self.alloc.on_evict = self._forget_block
         self.cuda = self.device.type == "cuda"
         self.use_graph = self.cuda if use_cuda_graph is None else (use_cuda_graph and self.cuda)
         self.graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}   # (padded batch, vocab-parallel greedy) -> graph
@@ -187,6 +197,46 @@ class ModelRunner:
             seq.reserved -= took
             self._outstanding -= took
 
+    def _forget_block(self, block: int):
+        key = self._block_key.pop(block, None)
+        if key is not None:
+            self._nodes.pop(key, None)
+
+    def _attach_cached_prefix(self, seq: SeqState) -> int:
+        """Point the head of `seq`'s block table at cached blocks holding the same prompt prefix; returns the number of
+        prompt tokens covered (a multiple of the block size; at least one prompt token is always left to compute,
+        its logits are needed)."""
+        bs, parent, got = self.block_size, 0, 0
+        for i in range((len(seq.prompt) - 1) // bs):
+            hit = self._nodes.get((parent, tuple(seq.prompt[i * bs:(i + 1) * bs])))
+            if hit is None:
+                break
+            parent, blk = hit
+            self.alloc.share(blk)
+            seq.blocks.append(blk)
+            got += bs
+        took = min(got // bs, seq.reserved)      # these blocks will not be allocated after all
+        seq.reserved -= took
+        self._outstanding -= took
+        self.stats["prefix_hit_tokens"] = self.stats.get("prefix_hit_tokens", 0) + got
+        return got
+
+    def _register_prompt_blocks(self, seq: SeqState):
+        bs, parent = self.block_size, 0
+        for i in range(len(seq.prompt) // bs):
+            key = (parent, tuple(seq.prompt[i * bs:(i + 1) * bs]))
+            hit = self._nodes.get(key)
+            if hit is None:
+                blk = seq.blocks[i]
+                if blk in self._block_key:        # already registered under another chain: cannot happen, be safe
+                    break
+                hit = (self._next_node, blk)
+                self._next_node += 1
+                self._nodes[key] = hit
+                self._block_key[blk] = key
+                self.alloc.keep(blk)
+            parent = hit[0]
+
     def release(self, seq: SeqState):
         self.alloc.release(seq.blocks)
         seq.blocks = []
@@ -201,23 +251,30 @@ class ModelRunner:
         With ``prefill_chunk`` set, prompts are fed in rounds of at most that many tokens per sequence: round r
         attends over the r * chunk tokens already in the cache (multi-token queries over prior context: the paged
         mode of the prefill attention kernel), which bounds the activation memory of very long prompts."""
+        have = []   # prompt tokens already in the cache per sequence (prefix cache hits; else 0)
         for s in seqs:
             s.prompt = s.prompt[-(self.max_seq_len - 1):]  # left-truncate like the reference tokenizer call
+            have.append(self._attach_cached_prefix(s) if self.prefix_enabled and not s.blocks else 0)
             self._grow(s, len(s.prompt))
-        chunk = self.prefill_chunk or max(len(s.prompt) for s in seqs)
-        rounds = -(-max(len(s.prompt) for s in seqs) // chunk)
+        todo = [len(s.prompt) - h for s, h in zip(seqs, have)]
+        chunk = self.prefill_chunk or max(todo)
+        rounds = -(-max(todo) // chunk)
         final_logits = [None] * len(seqs)
         for r in range(rounds):
-            live = [(i, s) for i, s in enumerate(seqs) if len(s.prompt) > r * chunk]
-            batch = BatchInput.build([s.prompt[r * chunk:(r + 1) * chunk] for _, s in live], [r * chunk] * len(live),
+            live = [(i, s) for i, s in enumerate(seqs) if todo[i] > r * chunk]
+            batch = BatchInput.build([s.prompt[have[i] + r * chunk:have[i] + (r + 1) * chunk] for i, s in live],
+                                     [have[i] + r * chunk for i, _ in live],
                                      [s.blocks for _, s in live], self.block_size, self.device,
                                      max_blocks=self.max_blocks_per_seq,
                                      pad_to=self.core.tp * 16 if self.core.tp > 1 else 1)
             logits = self.core.forward(batch, self.kv, last_only=True)
             for row, (i, s) in enumerate(live):
-                if len(s.prompt) <= (r + 1) * chunk:
+                if todo[i] <= (r + 1) * chunk:
                     final_logits[i] = logits[row]
             self.stats["prefill_tokens"] += int(batch.tokens.numel())
+        if self.prefix_enabled:
+            for s in seqs:
+                self._register_prompt_blocks(s)
         logits = torch.stack(final_logits)
         dev = self.device
         greedy = torch.tensor([int(s.params.is_greedy) for s in seqs], dtype=torch.int32, device=dev)

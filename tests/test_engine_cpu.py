@@ -178,3 +178,40 @@ def test_sliding_window_matches_block_window_oracle(tmp_path):
     learned = Engine.from_pretrained(str(tmp_path / "gpt2"), device="cpu", max_batch=1, max_seq_len=32, block_size=bs, sliding_window=True)
     assert not learned.runner.sliding
     assert len(learned.generate([prompts[1]], SamplingParams(max_new_tokens=n_new, is_greedy=True))[0]) == 32 - len(prompts[1])
+
+
+def test_prefix_cache_reuses_prompt_blocks(tmp_path):
+    """Prompts that start with the same tokens share the cache blocks of that prefix (reference-counted, LRU-evicted);
+    only the rest is computed -- queries over prior context -- and the tokens are those of an engine without the cache."""
+    from llmss_b200.utils.checkpoint import write_random_checkpoint
+
+    path = str(write_random_checkpoint(tmp_path, "gptj-tiny", dtype=torch.float32, device="cpu", std=0.08))
+    g = torch.Generator().manual_seed(9)
+    system = torch.randint(1, 500, (40,), generator=g).tolist()                     # 2.5 blocks of 16
+    tails = [torch.randint(1, 500, (n,), generator=g).tolist() for n in (7, 1, 30, 12)]
+    prompts = [system + t for t in tails] + [system[:32], system[:16] + tails[2]]   # incl. a prompt that IS a cached prefix
+    sp = SamplingParams(max_new_tokens=6, is_greedy=True)
+    plain = Engine.from_pretrained(path, device="cpu", max_batch=4, max_seq_len=128, block_size=16)
+    want = [plain.generate([p], sp)[0] for p in prompts]
+    eng = Engine.from_pretrained(path, device="cpu", max_batch=4, max_seq_len=128, block_size=16, prefix_cache=True)
+    r = eng.runner
+    got = [eng.generate([p], sp)[0] for p in prompts]                               # one after the other: later ones hit
+    assert got == want
+    # 2 blocks of the system prompt for requests 2-4, 1 block for system[:32] (its own last block is recomputed) and for the last
+    assert r.stats["prefix_hit_tokens"] == 3 * 32 + 16 + 16
+    assert r.stats["prefill_tokens"] == sum(len(p) for p in prompts) - r.stats["prefix_hit_tokens"]
+    assert r.alloc.num_free == r.alloc.num_blocks - 1 and r._outstanding == 0 and len(r.alloc.evictable) > 0
+    # all at once: requests admitted together compute the prefix once each (nothing to hit yet) but stay correct,
+    # and a second wave hits what the first registered
+    both = eng.generate(prompts[:4], sp) + eng.generate(prompts[:4], sp)
+    assert both == want[:4] + want[:4]
+    # chunked prefill on top of a cached prefix
+    ch = Engine.from_pretrained(path, device="cpu", max_batch=4, max_seq_len=128, block_size=16, prefix_cache=True, prefill_chunk=8)
+    assert [ch.generate([p], sp)[0] for p in prompts] == want
+    # a cache too small to keep everything: least recently used prefixes are evicted, results stay right
+    small = Engine.from_pretrained(path, device="cpu", max_batch=2, max_seq_len=128, block_size=16, prefix_cache=True, num_blocks=8)
+    other = [torch.randint(1, 500, (50,), generator=g).tolist() for _ in range(3)]
+    seq = [prompts[0], other[0], other[1], prompts[2], other[2], prompts[0]]
+    assert [small.generate([p], sp)[0] for p in seq] == [plain.generate([p], sp)[0] for p in seq]
+    a = small.runner.alloc
+    assert a.num_free == a.num_blocks - 1 and all(x == 0 for x in a.ref) and len(small.runner._nodes) == len(a.kept)

@@ -176,3 +176,27 @@ def test_sliding_window_on_gpu(tmp_path):
     same = sum(int(a == b) for o, c in zip(got, cpu) for a, b in zip(o, c))
     assert same >= 0.7 * 270, (same, got, cpu)
     assert got[2][:40] == cpu[2][:40], (got[2][:40], cpu[2][:40])   # prompt of 100: evictions from token 29 on
+
+
+def test_prefix_cache_on_gpu(tmp_path):
+    """Prefix cache through the CUDA path: the tail of a prompt whose head is cached runs as queries over prior context
+    (paged mode of the prefill attention kernel, or the decode kernel when one token is left); tokens must be those of
+    an engine without the cache (same kernels for the decode steps, so equality is demanded up to a late near-tie)."""
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+    from llmss_b200.utils.checkpoint import write_random_checkpoint
+
+    path = str(write_random_checkpoint(tmp_path, "gptj-tiny", dtype=torch.float32, device="cpu", std=0.08))
+    g = torch.Generator().manual_seed(9)
+    system = torch.randint(1, 500, (150,), generator=g).tolist()                    # 2 full pages of 64 + 22 tokens
+    prompts = [system + torch.randint(1, 500, (n,), generator=g).tolist() for n in (7, 1, 60)] + [system[:129]]
+    sp = SamplingParams(max_new_tokens=8, is_greedy=True)
+    kw = dict(dtype=torch.bfloat16, device="cuda", max_batch=4, max_seq_len=256)
+    plain = Engine.from_pretrained(path, **kw)
+    want = [plain.generate([p], sp)[0] for p in prompts]
+    eng = Engine.from_pretrained(path, prefix_cache=True, **kw)
+    got = [eng.generate([p], sp)[0] for p in prompts]
+    assert eng.runner.stats["prefix_hit_tokens"] == 3 * 128
+    assert sum(a[:4] == b[:4] for a, b in zip(got, want)) >= 3 and sum(a == b for a, b in zip(got, want)) >= 2, (got, want)
+    a = eng.runner.alloc
+    assert a.num_free == a.num_blocks - 1 and all(x == 0 for x in a.ref)

@@ -21,6 +21,7 @@ import torch
 
 from .. import ops
 from ..models.decoder import DecoderLM
+from ..utils.metrics import METRICS
 from .batch import BatchInput
 from .kv_cache import BlockAllocator, KVCache
 
@@ -219,6 +220,8 @@ class ModelRunner:
         seq.reserved -= took
         self._outstanding -= took
         self.stats["prefix_hit_tokens"] = self.stats.get("prefix_hit_tokens", 0) + got
+        if got:
+            METRICS.inc("prefix_hit_tokens", got)
         return got
 
     def _register_prompt_blocks(self, seq: SeqState):
@@ -351,6 +354,7 @@ class ModelRunner:
             for i in np.nonzero(full)[0]:
                 s = self.batch_seqs[i]
                 self.alloc.release([s.blocks.pop(0)])
+                METRICS.inc("sliding_window_evicted_blocks")
                 s.dropped += bs
                 self.np_drop[i] += bs
                 n = len(s.blocks)

@@ -231,3 +231,43 @@ def test_indivisible_head_count_is_padded(family, tmp_path):
         assert torch.allclose(got["logits"], ref.logits, atol=3e-4, rtol=1e-4), (family, r)
         assert torch.allclose(got["step"], ref_step.logits, atol=3e-4, rtol=1e-4), (family, r)
         assert got["toks"] == ref_toks, (family, r)
+
+
+# ------------------------------------------------------------------------------------------------
+# engine options on real ranks: prefix cache + sliding window take the same decisions on every rank
+def _engine_options_worker(rank, world, port, path, prompts, out_file):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    os.environ.pop("DEBUG", None)
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+    from llmss_b200.utils.dist import initialize_torch_distributed
+
+    pg, _, _ = initialize_torch_distributed()
+    eng = Engine.from_pretrained(path, device="cpu", process_group=pg, max_batch=2, max_seq_len=64, block_size=16,
+                                 prefix_cache=True, sliding_window=True)
+    sp = SamplingParams(max_new_tokens=40, is_greedy=True)
+    toks = [eng.generate([p], sp)[0] for p in prompts]
+    r = eng.runner
+    torch.save({"toks": toks, "hits": r.stats.get("prefix_hit_tokens", 0), "free": r.alloc.num_free,
+                "blocks": r.alloc.num_blocks}, f"{out_file}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_prefix_cache_and_sliding_window_on_two_ranks(tmp_path):
+    from tiny import make_tiny
+
+    from llmss_b200.engine.engine import Engine
+    from llmss_b200.engine.runner import SamplingParams
+
+    cfg, _ = make_tiny("gptj", tmp_path)
+    g = torch.Generator().manual_seed(4)
+    head = torch.randint(1, cfg.vocab_size, (36,), generator=g).tolist()
+    prompts = [head + torch.randint(1, cfg.vocab_size, (n,), generator=g).tolist() for n in (3, 9, 1)]   # 39..45 + 40 new > 64
+    single = Engine.from_pretrained(str(tmp_path), device="cpu", max_batch=2, max_seq_len=64, block_size=16, sliding_window=True)
+    want = [single.generate([p], SamplingParams(max_new_tokens=40, is_greedy=True))[0] for p in prompts]
+    out_file = str(tmp_path / "out")
+    mp.spawn(_engine_options_worker, args=(2, _free_port(), str(tmp_path), prompts, out_file), nprocs=2, join=True)
+    got = [torch.load(f"{out_file}.{r}") for r in range(2)]
+    assert got[0]["toks"] == got[1]["toks"] == want
+    assert got[0]["hits"] == got[1]["hits"] == 2 * 32 and got[0]["free"] == got[0]["blocks"] - 1

@@ -215,3 +215,30 @@ def test_prefix_cache_reuses_prompt_blocks(tmp_path):
     assert [small.generate([p], sp)[0] for p in seq] == [plain.generate([p], sp)[0] for p in seq]
     a = small.runner.alloc
     assert a.num_free == a.num_blocks - 1 and all(x == 0 for x in a.ref) and len(small.runner._nodes) == len(a.kept)
+
+
+def test_block_allocator_refcounts_and_lru():
+    from llmss_b200.engine.kv_cache import BlockAllocator
+
+    evicted = []
+    a = BlockAllocator(6)                       # blocks 1..5 usable, 0 is the padding target
+    a.on_evict = evicted.append
+    x = a.alloc(3)
+    assert 0 not in x and a.num_free == 2 and [a.ref[b] for b in x] == [1, 1, 1]
+    a.keep(x[0]); a.keep(x[1])                  # registered in a prefix index
+    a.share(x[0])                               # a second sequence holds it
+    a.release(x)                                # first holder leaves: x[0] still held, x[1] evictable, x[2] free
+    assert a.ref[x[0]] == 1 and x[1] in a.evictable and x[2] in a.free and a.num_free == 4
+    a.release([x[0]])
+    assert list(a.evictable) == [x[1], x[0]] and a.num_free == 5          # least recently used first
+    a.share(x[1])                               # a hit revives an evictable block
+    assert x[1] not in a.evictable and a.num_free == 4
+    y = a.alloc(4)                              # drains the free list, then evicts x[0]
+    assert evicted == [x[0]] and x[0] in y and x[0] not in a.kept and a.num_free == 0
+    try:
+        a.alloc(1)
+        raise AssertionError("expected MemoryError")
+    except MemoryError:
+        pass
+    a.release(y); a.release([x[1]])
+    assert a.num_free == 5 and all(r == 0 for r in a.ref)

@@ -245,7 +245,7 @@ def _engine_options_worker(rank, world, port, path, prompts, out_file):
     pg, _, _ = initialize_torch_distributed()
     eng = Engine.from_pretrained(path, device="cpu", process_group=pg, max_batch=2, max_seq_len=64, block_size=16,
                                  prefix_cache=True, sliding_window=True)
-    sp = SamplingParams(max_new_tokens=40, is_greedy=True)
+    sp = SamplingParams(max_new_tokens=28, is_greedy=True)
     toks = [eng.generate([p], sp)[0] for p in prompts]
     r = eng.runner
     torch.save({"toks": toks, "hits": r.stats.get("prefix_hit_tokens", 0), "free": r.alloc.num_free,
@@ -263,9 +263,9 @@ def test_prefix_cache_and_sliding_window_on_two_ranks(tmp_path):
     cfg, _ = make_tiny("gptj", tmp_path)
     g = torch.Generator().manual_seed(4)
     head = torch.randint(1, cfg.vocab_size, (36,), generator=g).tolist()
-    prompts = [head + torch.randint(1, cfg.vocab_size, (n,), generator=g).tolist() for n in (3, 9, 1)]   # 39..45 + 40 new > 64
+    prompts = [head + torch.randint(1, cfg.vocab_size, (n,), generator=g).tolist() for n in (3, 9, 1)]   # 37..45 + 28 new > 64
     single = Engine.from_pretrained(str(tmp_path), device="cpu", max_batch=2, max_seq_len=64, block_size=16, sliding_window=True)
-    want = [single.generate([p], SamplingParams(max_new_tokens=40, is_greedy=True))[0] for p in prompts]
+    want = [single.generate([p], SamplingParams(max_new_tokens=28, is_greedy=True))[0] for p in prompts]
     out_file = str(tmp_path / "out")
     mp.spawn(_engine_options_worker, args=(2, _free_port(), str(tmp_path), prompts, out_file), nprocs=2, join=True)
     got = [torch.load(f"{out_file}.{r}") for r in range(2)]

@@ -246,6 +246,7 @@ class Engine:
         outs: List[List[int]] = [[] for _ in prompts]
         live = list(range(len(prompts)))
         step = 0
+        keep_prefix, r.prefix_enabled = r.prefix_enabled, False   # "no cache" means none: every step recomputes everything
         while live:
             seqs = []
             for i in live:
@@ -263,5 +264,6 @@ class Engine:
                     nxt.append(i)
             live = nxt
             step += 1
+        r.prefix_enabled = keep_prefix
         self._next_id += len(prompts)
         return outs

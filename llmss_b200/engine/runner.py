@@ -224,10 +224,11 @@ class ModelRunner:
             METRICS.inc("prefix_hit_tokens", got)
         return got
 
-    def _register_prompt_blocks(self, seq: SeqState):
+    def _register_blocks(self, seq: SeqState, tokens: Sequence[int]):
+        """Enter the full blocks of `tokens` (whose keys / values are in `seq`'s first blocks) into the prefix index."""
         bs, parent = self.block_size, 0
-        for i in range(len(seq.prompt) // bs):
-            key = (parent, tuple(seq.prompt[i * bs:(i + 1) * bs]))
+        for i in range(min(len(tokens) // bs, len(seq.blocks))):
+            key = (parent, tuple(tokens[i * bs:(i + 1) * bs]))
             hit = self._nodes.get(key)
             if hit is None:
                 blk = seq.blocks[i]
@@ -241,6 +242,9 @@ class ModelRunner:
             parent = hit[0]
 
     def release(self, seq: SeqState):
+        if self.prefix_enabled and seq.blocks and seq.dropped == 0 and seq.length > len(seq.prompt):
+            # multi-turn reuse: what was generated is cached too (the last token's keys are not written until it is fed)
+            self._register_blocks(seq, (seq.prompt + seq.output)[:seq.length])
         self.alloc.release(seq.blocks)
         seq.blocks = []
         self._outstanding -= seq.reserved
@@ -277,7 +281,7 @@ class ModelRunner:
             self.stats["prefill_tokens"] += int(batch.tokens.numel())
         if self.prefix_enabled:
             for s in seqs:
-                self._register_prompt_blocks(s)
+                self._register_blocks(s, s.prompt)
         logits = torch.stack(final_logits)
         dev = self.device
         greedy = torch.tensor([int(s.params.is_greedy) for s in seqs], dtype=torch.int32, device=dev)

@@ -242,3 +242,24 @@ def test_block_allocator_refcounts_and_lru():
         pass
     a.release(y); a.release([x[1]])
     assert a.num_free == 5 and all(r == 0 for r in a.ref)
+
+
+def test_prefix_cache_covers_generated_tokens_for_follow_up_turns(tmp_path):
+    """A follow-up prompt that repeats the previous turn (prompt + answer) and adds to it finds the answer's blocks in
+    the cache as well: finished sequences register the full blocks of everything whose keys / values they wrote."""
+    from llmss_b200.utils.checkpoint import write_random_checkpoint
+
+    path = str(write_random_checkpoint(tmp_path, "gptj-tiny", dtype=torch.float32, device="cpu", std=0.08))
+    g = torch.Generator().manual_seed(21)
+    first = torch.randint(1, 500, (40,), generator=g).tolist()
+    kw = dict(device="cpu", max_batch=2, max_seq_len=160, block_size=16)
+    plain, eng = Engine.from_pretrained(path, **kw), Engine.from_pretrained(path, prefix_cache=True, **kw)
+    a1 = eng.generate([first], SamplingParams(max_new_tokens=30, is_greedy=True))[0]
+    assert a1 == plain.generate([first], SamplingParams(max_new_tokens=30, is_greedy=True))[0]
+    follow = first + a1 + torch.randint(1, 500, (5,), generator=g).tolist()          # 75 tokens: 69 of them were cached
+    hits0 = eng.runner.stats.get("prefix_hit_tokens", 0)
+    a2 = eng.generate([follow], SamplingParams(max_new_tokens=10, is_greedy=True))[0]
+    assert eng.runner.stats["prefix_hit_tokens"] - hits0 == 64                      # 4 full blocks: prompt AND answer
+    assert a2 == plain.generate([follow], SamplingParams(max_new_tokens=10, is_greedy=True))[0]
+    a = eng.runner.alloc
+    assert a.num_free == a.num_blocks - 1 and all(x == 0 for x in a.ref)

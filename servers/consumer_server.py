@@ -19,6 +19,8 @@ def get_args():
     consumer_group.add_argument("--dtype", type=str, default="float16", choices=["float16", "bfloat16", "float32"])
     consumer_group.add_argument("--max_batch", type=int, default=64)
     consumer_group.add_argument("--max_seq_len", type=int, default=None)
+    consumer_group.add_argument("--prefill_chunk", type=int, default=None,
+                                help="feed prompts into the cache this many tokens per sequence and round (bounds activation memory)")
     consumer_group.add_argument("--prefix_cache", action="store_true",
                                 help="prompts that start with the same tokens share the KV blocks of the common prefix")
     consumer_group.add_argument("--sliding_window", action="store_true",
@@ -47,7 +49,8 @@ def main():
         tokenizer = AutoTokenizer.from_pretrained(args.pretrained_model_path, padding_side="left", truncation_side="left")
     engine = Engine.from_pretrained(args.pretrained_model_path, dtype=getattr(torch, args.dtype),
                                     process_group=process_group, max_batch=args.max_batch, max_seq_len=args.max_seq_len,
-                                    sliding_window=args.sliding_window, prefix_cache=args.prefix_cache)
+                                    sliding_window=args.sliding_window, prefix_cache=args.prefix_cache,
+                                    prefill_chunk=args.prefill_chunk)
     engine.comm.barrier()
     ConsumerLoop(engine, tokenizer, broker).run_forever()
 

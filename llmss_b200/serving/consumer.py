@@ -44,7 +44,7 @@ class _Live:
     __slots__ = ("req", "ids", "text_len", "tokens")
 
     def __init__(self, req: GenerateRequest):
-        self.req, self.tokens, self.text_len = req, [], 0
+        self.req, self.tokens, self.text_len, self.ids = req, [], 0, 0   # ids: number of prompt tokens
 
 
 class ConsumerLoop:
@@ -147,6 +147,7 @@ class ConsumerLoop:
                 rid = self._next_rid
                 self._next_rid += 1
                 self.live[rid] = _Live(req)
+                self.live[rid].ids = len(ids)
                 sp = req.sampling()
                 flat += [rid, len(ids), sp.max_new_tokens, int(sp.is_greedy), sp.top_k, _f2i(sp.temperature),
                          _f2i(sp.top_p), -1 if sp.seed is None else (sp.seed & 0x7FFFFFFF)]
@@ -224,7 +225,7 @@ class ConsumerLoop:
                     st = self.engine.stats.get(o.request_id)
                     text = self.tok.decode(lv.tokens)
                     self._reply(lv.req, GenerateResponse(
-                        prompt=lv.req.prompt, continuation=text, done=True, num_tokens=len(lv.tokens),
+                        prompt=lv.req.prompt, continuation=text, done=True, num_tokens=len(lv.tokens), prompt_tokens=lv.ids,
                         ttft_ms=None if st is None or st.ttft is None else round(1e3 * st.ttft, 3),
                         tpot_ms=None if st is None or st.tpot is None else round(1e3 * st.tpot, 3)))
                     del self.live[o.request_id]

@@ -62,6 +62,7 @@ class GenerateResponse:
     done: bool = True
     delta: Optional[str] = None
     num_tokens: Optional[int] = None
+    prompt_tokens: Optional[int] = None
     ttft_ms: Optional[float] = None
     tpot_ms: Optional[float] = None
 

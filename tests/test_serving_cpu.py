@@ -119,6 +119,14 @@ def test_http_and_grpc_front_ends(engine):
         assert client.post("/generate", json={**body, "top_p": 1.5}).status_code == 422
         assert client.get("/health").json()["status"] == "ok"
         assert "llmss_b200_requests_total" in client.get("/metrics").text
+        # OpenAI-style completions on the same path: greedy at temperature 0, one choice per prompt, token usage
+        oa = client.post("/v1/completions", json={"model": "tiny", "prompt": ["hi there", "p1"], "max_tokens": 5, "temperature": 0})
+        assert oa.status_code == 200, oa.text
+        oa = oa.json()
+        assert oa["object"] == "text_completion" and [c["index"] for c in oa["choices"]] == [0, 1]
+        assert oa["choices"][0]["text"] == r.json()["continuation"] and oa["choices"][0]["finish_reason"] == "length"
+        assert oa["usage"] == {"prompt_tokens": len("hi there") + len("p1"), "completion_tokens": 10, "total_tokens": 20}
+        assert client.post("/v1/completions", json={"prompt": 3}).status_code == 422
         # concurrent clients each get their own answer (reference quirk Q14)
         outs = {}
 

@@ -206,6 +206,10 @@ class Engine:
         t1 = now()
         METRICS.observe("decode_step_seconds", t1 - t0)
         METRICS.set("batch_occupancy", len(self.running))
+        a = self.runner.alloc
+        METRICS.set("kv_blocks_free", a.num_free)               # free list + evictable cached blocks
+        METRICS.set("kv_blocks_cached", len(a.kept))            # blocks registered in the prefix index
+        METRICS.set("requests_waiting", len(self.waiting))
         n_active = 0
         for s, t in zip(self.running, toks):
             if s.finished:
